@@ -1,0 +1,44 @@
+"""Synthetic multichannel PCM used by the parity tests and bench.py.
+
+Follows the reference repo's own stimulus definition
+(/root/reference/sim/scripts/generate_test_vectors.py:94-130): a fundamental plus three harmonics
+(0.5/0.3/0.2/0.1), Gaussian noise sigma 0.01, 10 ms linear fade-in, scaled to full range and
+clipped.  Streams are de-correlated as SURVEY.md section 8d states: f_s = 200 + (37 s mod 3000) Hz,
+amplitude 0.1 + 0.9 ((7919 s) mod 1000)/1000, noise seed 1234 + s; every 8th stream is digital
+silence for its first 50 frames (exercises the all-zero spectrum paths).
+"""
+import numpy as np
+
+
+def make_streams(n_streams, n_samples, fs, frame_len, bits=16, first_stream=0, silence_frames=50):
+    """Return int16 (bits=16) or int32 (bits=24) array [n_streams, n_samples]."""
+    t = np.arange(n_samples, dtype=np.float64) / fs
+    out = np.empty((n_streams, n_samples), dtype=np.int16 if bits == 16 else np.int32)
+    full = 32767.0 if bits == 16 else 8388607.0
+    fade = int(0.01 * fs)
+    env = np.ones(n_samples)
+    env[:min(fade, n_samples)] = np.linspace(0, 1, fade)[:min(fade, n_samples)]
+    for i in range(n_streams):
+        s = first_stream + i
+        f = 200.0 + (37 * s) % 3000
+        amp = 0.1 + 0.9 * ((s * 7919) % 1000) / 1000.0
+        rng = np.random.RandomState(1234 + s)
+        x = (0.5 * np.sin(2 * np.pi * f * t) + 0.3 * np.sin(2 * np.pi * 2 * f * t)
+             + 0.2 * np.sin(2 * np.pi * 3 * f * t) + 0.1 * np.sin(2 * np.pi * 4 * f * t))
+        x = (x + rng.normal(0, 0.01, n_samples)) * env * amp
+        if s % 8 == 7:
+            x[:min(silence_frames * frame_len, n_samples)] = 0.0
+        out[i] = np.clip(x * full, -full - 1, full).astype(out.dtype)
+    return out
+
+
+def make_streams_fast(n_streams, n_samples, fs, frame_len, bits=16, n_unique=64):
+    """Large batches for timing: n_unique distinct streams from make_streams(), tiled with a
+    per-copy circular shift so that no two streams are sample-identical."""
+    base = make_streams(min(n_unique, n_streams), n_samples, fs, frame_len, bits)
+    if n_streams <= base.shape[0]:
+        return base
+    out = np.empty((n_streams, n_samples), dtype=base.dtype)
+    for i in range(n_streams):
+        out[i] = np.roll(base[i % base.shape[0]], (i // base.shape[0]) * 97)
+    return out

@@ -1,0 +1,141 @@
+"""ctypes access to the two CPU checkers (TEST INFRASTRUCTURE ONLY):
+
+  * RefEnc    -- the unmodified ETSI fixed-point encoder compiled from /root/reference into
+                 oracle/_ref/liblc3ref.so (API: fx/lc3.h:170-309)
+  * OracleEnc -- our plain-C restatement, oracle/liblc3oracle.so (API: oracle/lc3o.h)
+
+Both expose encode(pcm[ch][n_frames*N]) -> bytes [n_frames, nbytes].
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF_SO = os.path.join(ROOT, "oracle", "_ref", "liblc3ref.so")
+ORACLE_SO = os.path.join(ROOT, "oracle", "liblc3oracle.so")
+
+_ref = None
+_ora = None
+
+
+def have_ref():
+    return os.path.exists(REF_SO)
+
+
+def ref_lib():
+    global _ref
+    if _ref is None:
+        _ref = C.CDLL(REF_SO)
+        _ref.lc3_enc_get_size.restype = C.c_int
+    return _ref
+
+
+def oracle_lib():
+    global _ora
+    if _ora is None:
+        _ora = C.CDLL(ORACLE_SO)
+        _ora.lc3o_enc_new.restype = C.c_void_p
+        _ora.lc3o_enc_free.argtypes = [C.c_void_p]
+        for n in ("lc3o_enc_set_frame_dms", "lc3o_enc_set_bitrate", "lc3o_enc_set_bandwidth"):
+            getattr(_ora, n).argtypes = [C.c_void_p, C.c_int]
+        for n in ("lc3o_enc_get_input_samples", "lc3o_enc_get_num_bytes", "lc3o_enc_get_delay",
+                  "lc3o_enc_get_real_bitrate"):
+            getattr(_ora, n).argtypes = [C.c_void_p]
+        for n in ("lc3o_enc16", "lc3o_enc24"):
+            getattr(_ora, n).argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        _ora.lc3o_enc16_trace.argtypes = [C.c_void_p] * 5
+    return _ora
+
+
+class _Base:
+    def encode(self, pcm, bits=16, bfi=None):
+        """pcm: [channels, n_frames*N] int16/int32 -> uint8 [n_frames, nbytes]"""
+        pcm = np.ascontiguousarray(pcm)
+        if pcm.ndim == 1:
+            pcm = pcm[None, :]
+        assert pcm.shape[0] == self.channels
+        N = self.frame_len
+        nf = pcm.shape[1] // N
+        nb = self.num_bytes
+        out = np.zeros((nf, nb), dtype=np.uint8)
+        ct = C.c_int16 if bits == 16 else C.c_int32
+        assert pcm.dtype == (np.int16 if bits == 16 else np.int32)
+        ptrs = (C.c_void_p * 2)()
+        for f in range(nf):
+            for c in range(self.channels):
+                ptrs[c] = pcm[c, f * N:].ctypes.data
+            n = C.c_int(-1 if (bfi is not None and bfi[f]) else 0)
+            r = self._enc(bits, ptrs, out[f].ctypes.data, C.byref(n))
+            assert r == 0, r
+            assert n.value == nb
+        return out
+
+
+class RefEnc(_Base):
+    def __init__(self, fs, channels=1, dms=100, bitrate=None):
+        L = ref_lib()
+        self.channels = channels
+        self._mem = C.create_string_buffer(L.lc3_enc_get_size(fs, channels) + 16)
+        self.h = C.c_void_p((C.addressof(self._mem) + 15) & ~15)
+        r = L.lc3_enc_init(self.h, fs, channels)
+        assert r == 0, r
+        r = L.lc3_enc_set_frame_dms(self.h, dms)
+        assert r == 0, r
+        self._scratch = C.create_string_buffer(L.lc3_enc_get_scratch_size(self.h) + 64)
+        if bitrate is not None:
+            assert self.set_bitrate(bitrate) == 0
+
+    def set_bitrate(self, br):
+        return ref_lib().lc3_enc_set_bitrate(self.h, br)
+
+    def set_bandwidth(self, bw):
+        return ref_lib().lc3_enc_set_bandwidth(self.h, bw)
+
+    @property
+    def frame_len(self):
+        return ref_lib().lc3_enc_get_input_samples(self.h)
+
+    @property
+    def num_bytes(self):
+        return ref_lib().lc3_enc_get_num_bytes(self.h)
+
+    def _enc(self, bits, ptrs, out, n):
+        L = ref_lib()
+        return (L.lc3_enc16 if bits == 16 else L.lc3_enc24)(self.h, ptrs, C.c_void_p(out), n, self._scratch)
+
+
+class OracleEnc(_Base):
+    def __init__(self, fs, channels=1, dms=100, bitrate=None):
+        L = oracle_lib()
+        self.channels = channels
+        self.h = C.c_void_p(L.lc3o_enc_new(fs, channels))
+        assert self.h.value
+        r = L.lc3o_enc_set_frame_dms(self.h, dms)
+        assert r == 0, r
+        if bitrate is not None:
+            assert self.set_bitrate(bitrate) == 0
+
+    def __del__(self):
+        try:
+            oracle_lib().lc3o_enc_free(self.h)
+        except Exception:
+            pass
+
+    def set_bitrate(self, br):
+        return oracle_lib().lc3o_enc_set_bitrate(self.h, br)
+
+    def set_bandwidth(self, bw):
+        return oracle_lib().lc3o_enc_set_bandwidth(self.h, bw)
+
+    @property
+    def frame_len(self):
+        return oracle_lib().lc3o_enc_get_input_samples(self.h)
+
+    @property
+    def num_bytes(self):
+        return oracle_lib().lc3o_enc_get_num_bytes(self.h)
+
+    def _enc(self, bits, ptrs, out, n):
+        L = oracle_lib()
+        return (L.lc3o_enc16 if bits == 16 else L.lc3o_enc24)(self.h, ptrs, C.c_void_p(out), n)

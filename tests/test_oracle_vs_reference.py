@@ -1,0 +1,98 @@
+"""Pins the oracle (oracle/*.c) against the UNMODIFIED reference compiled from /root/reference
+(oracle/_ref/liblc3ref.so) and against the reference's own known-answer vectors
+(ETSI testvec/md5_bin.txt, EP0 lines; hashes are stored without their first hex digit,
+testvecCheck.pl:212).  Needs /root/reference (this container); skipped on the GPU box."""
+import hashlib
+import os
+import struct
+import wave
+
+import numpy as np
+import pytest
+
+import lc3ref
+from audio_codec_b200.synth import make_streams
+
+ETSI = "/root/reference/LC3plus_ETSI_src_v17171_20200723"
+needs_ref = pytest.mark.skipif(not (lc3ref.have_ref() and os.path.isdir(ETSI)), reason="reference tree absent")
+
+VEC = [(8, 32000), (16, 32000), (24, 48000), (32, 48000), (44, 64000), (48, 64000)]
+
+
+def _read_wav(path):
+    with wave.open(path, "rb") as w:
+        assert w.getnchannels() == 1 and w.getsampwidth() == 2
+        return w.getframerate(), np.frombuffer(w.readframes(w.getnframes()), dtype=np.int16)
+
+
+@needs_ref
+@pytest.mark.parametrize("tag,br", VEC)
+def test_etsi_md5_vectors(tag, br):
+    fs, x = _read_wav(f"{ETSI}/testvec/input/thetest{tag}.wav")
+    md5 = {}
+    for line in open(f"{ETSI}/testvec/md5_bin.txt"):
+        k, v = line.strip().split(":")
+        md5[k] = v
+    want = md5[f"thetest{tag}_{br}_EP0.lc3plus"]
+    enc = lc3ref.OracleEnc(fs, 1, 100, br)
+    N = enc.frame_len
+    nf = (len(x) + N - 1) // N
+    xp = np.zeros(nf * N, dtype=np.int16)
+    xp[:len(x)] = x
+    frames = enc.encode(xp)
+    # header fields: fx/codec_exe.c:736-746 (frame_ms*100 = dms*10)
+    hdr = struct.pack("<9H", 0xcc1c, 18, fs // 100, br // 100, 1, 100 * 10, 0, len(x) & 0xffff, len(x) >> 16)
+    blob = hdr + b"".join(struct.pack("<H", frames.shape[1]) + f.tobytes() for f in frames)
+    got = hashlib.md5(blob).hexdigest()
+    assert got[1:] == want, (got, want)
+
+
+CASES = [
+    # fs, ch, dms, bitrate, bits
+    (48000, 1, 100, 128000, 16), (48000, 1, 100, 64000, 16), (48000, 1, 100, 320000, 16),
+    (16000, 1, 50, 32000, 16), (48000, 2, 25, 256000, 16), (8000, 1, 25, 64000, 16),
+    (24000, 1, 50, 48000, 16), (32000, 1, 100, 80000, 16), (44100, 1, 100, 96000, 16),
+    (44100, 1, 50, 128000, 16), (32000, 2, 25, 192000, 16), (8000, 1, 100, 16000, 16),
+    (48000, 1, 100, 128000, 24), (16000, 1, 50, 32000, 24), (48000, 2, 25, 256000, 24),
+    (24000, 1, 100, 16000, 16), (48000, 1, 50, 48000, 16),
+]
+
+
+@needs_ref
+@pytest.mark.parametrize("fs,ch,dms,br,bits", CASES)
+def test_oracle_equals_reference(fs, ch, dms, br, bits):
+    ref = lc3ref.RefEnc(fs, ch, dms, br)
+    ora = lc3ref.OracleEnc(fs, ch, dms, br)
+    N = ref.frame_len
+    assert ora.frame_len == N and ora.num_bytes == ref.num_bytes
+    nf = 60
+    for s0 in (0, 7, 13):  # stream 7 starts with digital silence
+        pcm = make_streams(ch, nf * N, fs, N, bits, first_stream=s0, silence_frames=20)
+        a = ref.encode(pcm, bits)
+        b = ora.encode(pcm, bits)
+        assert np.array_equal(a, b), f"first differing frame {np.nonzero((a != b).any(1))[0][:1]}"
+
+
+@needs_ref
+def test_oracle_bitrate_switching_and_bfi():
+    fs, dms = 48000, 100
+    ref = lc3ref.RefEnc(fs, 1, dms, 128000)
+    ora = lc3ref.OracleEnc(fs, 1, dms, 128000)
+    N = ref.frame_len
+    pcm = make_streams(1, 40 * N, fs, N, 16, first_stream=3)
+    for k, br in enumerate([128000, 32000, 320000, 96000, 64000]):
+        assert ref.set_bitrate(br) == ora.set_bitrate(br) == 0
+        seg = pcm[:, k * 8 * N:(k + 1) * 8 * N]
+        bfi = [0, 0, 1, 0, 0, 0, 1, 0]
+        assert np.array_equal(ref.encode(seg, 16, bfi), ora.encode(seg, 16, bfi))
+
+
+@needs_ref
+def test_oracle_error_codes():
+    R, O = lc3ref.ref_lib(), lc3ref.oracle_lib()
+    ref = lc3ref.RefEnc(16000, 1, 100)
+    ora = lc3ref.OracleEnc(16000, 1, 100)
+    for br in (1000, 15999, 16000, 320000, 320001, 10**6):
+        assert ref.set_bitrate(br) == ora.set_bitrate(br), br
+    assert R.lc3_enc_set_frame_dms(ref.h, 50) == O.lc3o_enc_set_frame_dms(ora.h, 50) == 15
+    assert O.lc3o_enc_set_frame_dms(ora.h, 30) == 10
