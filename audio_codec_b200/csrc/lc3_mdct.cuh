@@ -1,0 +1,88 @@
+// Low-delay MDCT of one frame per lane: window + time-domain aliasing fold (fx/mdct_fx.c:17-96),
+// block normalisation, then DCT-IV = pre-twiddle -> complex FFT(N/2) -> post-twiddle
+// (fx/dct4_fx.c:16-138; twiddle tables fx/rom_basop_util.c:590-670).
+#pragma once
+#include "lc3_fft.cuh"
+#include "lc3_math.cuh"
+
+namespace lc3k {
+
+// (a + jb)(c + jd), every product halved before the add (cplxMpy32_32_16_2, fx/basop_mpy.h:45-50)
+LC3_HD void cmul_half(i32 &re, i32 &im, i32 a, i32 b, i32 c, i32 d)
+{
+    re = l_sub(mpy32x16(a, c) >> 1, mpy32x16(b, d) >> 1);
+    im = l_add(mpy32x16(a, d) >> 1, mpy32x16(b, c) >> 1);
+}
+
+template <int L> struct TwSlot {
+    static constexpr int v = L == 20 ? 0 : L == 40 ? 1 : L == 60 ? 2 : L == 80 ? 3 : L == 120 ? 4 : L == 160 ? 5 : L == 240 ? 6 : L == 320 ? 7 : 8;
+};
+
+// XS(i): scaled 16-bit input sample i of this frame, i in [-memLen, N) (negative = previous frame).
+// y: N words, receives the spectrum.  w: N words of scratch.  Returns the block exponent.
+template <int N, class XS, class A, class B>
+LC3_HD i32 mdct_frame(XS xs, i32 x_exp, const i16 *win, int wLen, int memLen, A y, B w)
+{
+    constexpr int m = N >> 1;
+    const int z = 2 * N - wLen;
+    Range rg; range_init(rg);
+    int i;
+    for (i = 0; i < m; i++) {
+        i32 v = l_msu0(l_mult0(xs(i - memLen), win[i]), xs(2 * m - 1 - i - memLen), win[2 * m - 1 - i]);
+        y[m + i] = v; range_add(rg, v);
+    }
+    for (i = 0; i < z; i++) {
+        i32 v = l_mult0(xs(2 * m - memLen + i), win[2 * m + i]);
+        y[m - 1 - i] = v; range_add(rg, v);
+    }
+    for (; i < m; i++) {
+        i32 v = l_mac0(l_mult0(xs(2 * m - memLen + i), win[2 * m + i]), xs(4 * m - memLen - 1 - i), win[4 * m - 1 - i]);
+        y[m - 1 - i] = v; range_add(rg, v);
+    }
+    const i32 s = imax(0, range_headroom32(rg, 0));
+    i32 y_e = s_sub(s_sub(x_exp, 2), s);
+    if (N <= 20) y_e = s_add(y_e, 2);
+    else if (N <= 120) y_e = s_add(y_e, 1);
+
+    // ---- DCT-IV (fx/dct4_fx.c:16-138); the block shift is applied as the pre-twiddle loads
+    constexpr int M = N >> 1;
+    const i16 *tw = &rom_dct4_twiddle[rom_dct4_twiddle_off[TwSlot<N>::v]];
+    const i16 *sn = (N % 3 == 0) ? rom_sin480 : rom_sin320;
+    constexpr int step = (N % 3 == 0) ? 960 / N : 640 / N;
+    i32 a1, a2, a3, a4;
+    for (int k = 0, lo = 0, hi = N - 2; k < M - 1; k += 2, lo += 2, hi -= 2) {
+        i32 p0 = l_shl_p(y[lo], s), p1 = l_shl_p(y[lo + 1], s), q0 = l_shl_p(y[hi], s), q1 = l_shl_p(y[hi + 1], s);
+        cmul_half(a1, a2, q1, p0, tw[2 * k], tw[2 * k + 1]);
+        cmul_half(a3, a4, q0, p1, tw[2 * k + 2], tw[2 * k + 3]);
+        y[lo] = a2; y[lo + 1] = a1;
+        y[hi] = a4; y[hi + 1] = l_neg(a3);
+    }
+    y_e = s_add(y_e, cfft<M>(y, w));
+
+    int lo = 0, hi = N - 2, idx = step;
+    constexpr int M2 = ((M + 1) >> 1) - 1;
+    cmul_half(a3, a4, y[hi], y[hi + 1], sn[2 * idx], sn[2 * idx + 1]);
+    y[hi + 1] = l_neg(y[lo + 1] >> 1);
+    y[lo] = y[lo] >> 1;
+    for (int k = 1; k < M2; k++) {
+        y[lo + 1] = a3; y[hi] = a4;
+        lo += 2; hi -= 2;
+        cmul_half(a1, a2, y[lo + 1], y[lo], sn[2 * idx], sn[2 * idx + 1]);
+        idx += step;
+        cmul_half(a3, a4, y[hi], y[hi + 1], sn[2 * idx], sn[2 * idx + 1]);
+        y[hi + 1] = l_neg(a1);
+        y[lo] = a2;
+    }
+    y[lo + 1] = a3; y[hi] = a4;
+    lo += 2; hi -= 2;
+    cmul_half(a3, a4, y[lo + 1], y[lo], sn[2 * idx], sn[2 * idx + 1]);
+    a1 = mpy32x16k(y[hi], 23170) >> 1;
+    a2 = mpy32x16k(y[hi + 1], 23170) >> 1;
+    y[hi] = l_add(a1, a2);
+    y[lo + 1] = l_sub(a1, a2);
+    y[hi + 1] = l_neg(a3);
+    y[lo] = a4;
+    return s_add(y_e, 2);
+}
+
+} // namespace lc3k

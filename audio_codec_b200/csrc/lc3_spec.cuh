@@ -1,0 +1,104 @@
+// Per-band energy (fx/per_band_energy_fx.c:17-228) and bandwidth detector
+// (fx/detect_cutoff_warped_fx.c:15-118), one frame per lane.
+#pragma once
+#include "lc3_math.cuh"
+
+namespace lc3k {
+
+LC3_HD i32 sq_hi(i32 v, i32 sh) { i32 t = hi16(l_shl(v, sh)); return l_mult0(t, t); }
+LC3_HD i32 hr15(i32 v, i32 cur) { return v != 0 ? imin(cur, l_norm(v)) : cur; }
+
+// en[0..nbands) mantissas on the common exponent returned.  bo: bands_offset table of this config.
+template <class A> LC3_HD i32 band_energy(i32 *en, A d, i32 d_exp, const i16 *bo, int fs_idx, int nbands, int dms_idx)
+{
+    i16 be[64];
+    const int maxbin = 400 >> dms_idx;
+    const int one = rom_bands_one_max[dms_idx * 5 + fs_idx], two = rom_bands_two_max[dms_idx * 5 + fs_idx];
+    int band = 0, i;
+    i32 smax = -31;
+
+    for (; band < one; band++) { // width-1 bands
+        i32 v = d[band];
+        i32 s2 = hr15(v, 15);
+        en[band] = sq_hi(v, s2);
+        i32 e = s_sub(1, s_shl(s2, 1));
+        be[band] = (i16)e; smax = imax(smax, e);
+    }
+    i = one;
+    for (; band < two; band++, i += 2) { // width-2 bands
+        i32 e;
+        if (i + 1 >= maxbin) {
+            if (i >= maxbin) {
+                en[band] = 0;
+                e = 1 - 30;
+            } else { // the reference reads d[band] here, not d[i] (per_band_energy_fx.c:117-128)
+                i32 v = d[band];
+                i32 s2 = hr15(v, 15);
+                en[band] = sq_hi(v, s2);
+                e = s_sub(1, s_shl(s2, 1));
+            }
+        } else {
+            i32 v0 = d[i], v1 = d[i + 1];
+            i32 s2 = hr15(v1, hr15(v0, 15));
+            i32 a = imin(sq_hi(v0, s2), 0x3FFFFFFF);
+            i32 t = hi16(l_shl(v1, s2));
+            en[band] = l_mac0(a, t, t) >> 1;
+            e = s_sub(1, s_shl(s2, 1));
+        }
+        be[band] = (i16)e; smax = imax(smax, e);
+    }
+    for (; band < nbands; band++) { // wider bands
+        const int stop = imin(bo[band + 1], maxbin);
+        i32 s1 = 15;
+        for (int k = i; k < stop; k++) s1 = hr15(d[k], s1);
+        int w = bo[band + 1] - bo[band];
+        w = w < 0 ? 0 : (w > 31 ? 31 : w);
+        i32 s2 = s_sub(s1, rom_bands_nrg_scale[w]);
+        i32 a = 0;
+        for (; i < stop; i++) {
+            i32 t = hi16(l_shl(d[i], s2));
+            a = l_mac0(a, t, t);
+        }
+        i = bo[band + 1];
+        a = mpy32x16(a, rom_inv_int[w]);
+        i32 s = l_norm(a);
+        en[band] = l_shl(a, s);
+        i32 e = s_sub(1, s_add(s_shl(s2, 1), s));
+        be[band] = (i16)e; smax = imax(smax, e);
+    }
+    for (band = 0; band < nbands; band++) en[band] = en[band] >> imin(s_sub(smax, be[band]), 31);
+    return s_add(s_shl(d_exp, 1), smax);
+}
+
+// fx/detect_cutoff_warped_fx.c:15-118 (called only for fs_idx > 0)
+LC3_HD i32 bw_detect(const i32 *en, i32 en_exp, int fs_idx, int dms_idx)
+{
+    const i16 *ws = &rom_bw_warp_start[(dms_idx * 4 + fs_idx - 1) * 4];
+    const i16 *we = &rom_bw_warp_stop[(dms_idx * 4 + fs_idx - 1) * 4];
+    const i16 *dist = &rom_bw_brickwall_dist[dms_idx * 4];
+    int c = fs_idx;
+    i32 below;
+    do {
+        c--;
+        if (c < 0) break;
+        int b = ws[c];
+        i32 sm = en[b];
+        i32 se = en_exp;
+        for (b++; b <= we[c]; b++) sm = m_add_me(en[b], en_exp, sm, se, &se);
+        i32 mean = mpy32x16(sm, rom_inv_int[we[c] - ws[c] + 1]);
+        below = m_cmp_me(rom_bw_thresh_quiet[c], rom_bw_thresh_quiet_exp[0], mean, se);
+    } while (below > 0);
+
+    i32 bw = c + 1;
+    if (fs_idx - bw > 0) { // brick-wall check just above the detected edge
+        int brick = 0, stop = ws[c + 1] + 1, dd = dist[c + 1];
+        for (int b = stop; b >= stop - dd; b--) {
+            i32 de = l_sub(mpy32x16(en[b - dd], rom_bw_thresh_brickwall[c + 1]), en[b]);
+            if (de > 0) { brick = 1; break; }
+        }
+        if (!brick) bw = fs_idx;
+    }
+    return bw;
+}
+
+} // namespace lc3k
