@@ -16,9 +16,11 @@
 #if defined(__CUDACC__)
 #define LC3_HD __device__ __forceinline__
 #define LC3_HDN __device__ __noinline__
+#define LC3_HDM __device__ __forceinline__
 #else
 #define LC3_HD static inline
 #define LC3_HDN static
+#define LC3_HDM inline
 #endif
 
 namespace lc3k {

@@ -1,0 +1,111 @@
+// Frame-parallel passes: one lane encodes the spectral half of one channel-frame.
+#pragma once
+#include "lc3_stages.cuh"
+
+namespace lc3k {
+
+// ---- spectral front end: fx/enc_lc3.c:83-84, :119-175 (+ the state-free half of :181-185)
+template <int N, int BITS> LC3_HD void front_body(const LC3K_Batch &b, int f, int tile, int lane)
+{
+    const int li = tile * LC3K_LANES + lane;
+    if (li >= b.n_lanes) return;
+    const int slot = b.slot[li];
+    SV<const i32> cfg = slot_view(b.cfg, slot, CFG_N);
+    const size_t ft = frame_tile(b, f, tile);
+    SV<const i32> po = tile_view((const i32 *)b.pout, ft, PO_N, lane);
+    const i32 x_exp = po[PO_X_EXP], attack = po[PO_ATTACK];
+    PcmView<BITS> xs = pcm_view<BITS>(b, tile, lane, f, x_exp);
+    SV<i32> d = tile_view(b.spec, ft, N, lane);
+    const i16 *bands = &rom_bands_offset[b.bands_off];
+
+    i32 w[N];
+    const i32 d_exp = mdct_frame<N>(xs, x_exp, &rom_win[b.W_off], b.W_len, b.mdct_mem_len, d, w);
+
+    i32 en[64];
+    const i32 en_exp = band_energy(en, d, d_exp, bands, b.fs_idx, b.nbands, b.dms_idx);
+    i32 bw = b.fs_idx > 0 ? bw_detect(en, en_exp, b.fs_idx, b.dms_idx) : 0;
+
+    i16 scf[16], scf_q[16], g[64], g_exp[64];
+    i32 scf_idx[7];
+    sns_compute(en, en_exp, b.fs_idx, b.nbands, scf, attack, 16384);
+    sns_quantize(scf, scf_idx, scf_q);
+    sns_interp(scf_q, g, g_exp, b.nbands);
+    mdct_shape(d, g, g_exp, bands, b.nbands);
+
+    const int cut = cfg[CFG_BW_CUTOFF_BIN];
+    if (cut) { // lc3_enc_set_bandwidth was used (fx/cutoff_bandwidth.c:14-28, fx/enc_lc3.c:164-168)
+        if (b.yLen > cut) {
+            for (int i = -1; i < 3; i++) d[cut + i] = d[cut + i] >> (i + 2);
+            for (int i = cut + 3; i < b.yLen; i++) d[i] = 0;
+        }
+        bw = imin(bw, cfg[CFG_BW_INDEX]);
+    }
+
+    TnsOut tns;
+    if (b.dms_idx == 0) tns_coder<8>(tns, d, bw, cfg[CFG_LPC_WEIGHTING], b.nsub, b.dms_idx);
+    else tns_coder<4>(tns, d, bw, cfg[CFG_LPC_WEIGHTING], b.nsub, b.dms_idx);
+
+    SV<i32> en4 = tile_view(b.en4, ft, N / 4, lane);
+    const i32 x_max = gain_energies(d, d_exp, b.yLen, en4);
+
+    SV<i32> fo = tile_view(b.fout, ft, FO_N, lane);
+    fo[FO_D_EXP] = d_exp; fo[FO_BW] = bw; fo[FO_TNS_BITS] = tns.bits; fo[FO_TNS_NFILT] = tns.nfilt;
+    fo[FO_TNS_ORDER0] = tns.order[0]; fo[FO_TNS_ORDER1] = tns.order[1]; fo[FO_X_MAX] = x_max;
+    for (int i = 0; i < 16; i++) fo[FO_TNS_IDX + i] = tns.idx[i];
+    for (int i = 0; i < 7; i++) fo[FO_SCF + i] = scf_idx[i];
+}
+
+// ---- back end: fx/enc_lc3.c:196-242 (adjust gain, final quantisation, residual, noise factor, entropy coding)
+LC3_HD void back_body(const LC3K_Batch &b, int f, int tile, int lane, const AriTabs &T, const uint16_t *ari_bitstab)
+{
+    const int li = tile * LC3K_LANES + lane;
+    if (li >= b.n_lanes) return;
+    const int slot = b.slot[li];
+    SV<const i32> cfg = slot_view(b.cfg, slot, CFG_N);
+    const size_t ft = frame_tile(b, f, tile);
+    SV<const i32> po = tile_view((const i32 *)b.pout, ft, PO_N, lane);
+    SV<const i32> fo = tile_view((const i32 *)b.fout, ft, FO_N, lane);
+    SV<const i32> ro = tile_view((const i32 *)b.rout, ft, RO_N, lane);
+    SV<const i32> d = tile_view((const i32 *)b.spec, ft, b.N, lane);
+    const i32 target_bytes = cfg[CFG_TARGET_BYTES], total_bits = cfg[CFG_TOTAL_BITS], qgain_off = cfg[CFG_QGAIN_OFF];
+    const i32 lpc_weighting = cfg[CFG_LPC_WEIGHTING];
+    const i32 d_exp = fo[FO_D_EXP], bw = fo[FO_BW], tbits_quant = ro[RO_TBITS_QUANT];
+
+    i32 qgain = ro[RO_QGAIN], gain, gain_e;
+    gain_from_index(s_add(qgain, qgain_off), gain, gain_e);
+    const int change = adjust_gain(qgain, ro[RO_QGAIN_MIN], qgain_off, gain, gain_e, tbits_quant, ro[RO_NBITS1], b.fs_idx);
+
+    i16 xq[LC3K_MAX_N], cd[3 * LC3K_MAX_N / 2];
+    QuantOut q;
+    quantize<true>(q, d, d_exp, gain, gain_e, xq, b.yLen, tbits_quant, total_bits, b.fs_idx, cd, change ? 0 : -1,
+                   T.lut, ari_bitstab);
+
+    u32 res[LC3K_MAX_N / 32 + 1], lsbs[2 * LC3K_MAX_N / 32 + 1];
+    i32 nres = 0;
+    if (q.lsbMode == 0) nres = residual_bits(d_exp, d, xq, gain, gain_e, b.yLen, tbits_quant, q.nBits2, res);
+    const i32 fac_ns = noise_factor(d_exp, d, xq, gain, gain_e, bw, b.dms, target_bytes);
+
+    SideInfo si;
+    si.bw = bw; si.bw_bits = b.bw_bits; si.lastnz = q.lastnz; si.lsbMode = q.lsbMode; si.gg = qgain;
+    TnsOut tns;
+    tns.nfilt = si.nfilt = fo[FO_TNS_NFILT];
+    tns.order[0] = si.tns_order[0] = fo[FO_TNS_ORDER0];
+    tns.order[1] = si.tns_order[1] = fo[FO_TNS_ORDER1];
+    tns.bits = fo[FO_TNS_BITS];
+    for (int i = 0; i < 16; i++) tns.idx[i] = (i16)fo[FO_TNS_IDX + i];
+    si.ltpf_idx[0] = po[PO_LTPF_IDX0]; si.ltpf_idx[1] = po[PO_LTPF_IDX1]; si.ltpf_idx[2] = po[PO_LTPF_IDX2];
+    si.fac_ns = fac_ns;
+    si.bfi_ext = b.bfi ? b.bfi[(size_t)f * b.n_lanes + li] : 0;
+    for (int i = 0; i < 7; i++) si.scf[i] = fo[FO_SCF + i];
+
+    u8 bytes[440];
+    for (int i = 0; i < target_bytes; i++) bytes[i] = 0;
+    BackWriter w;
+    side_info(w, bytes, total_bits, b.yLen, si, b.fs_idx);
+    ari_encode(bytes, w, total_bits, xq, tns, q.lastnz, cd, res, nres, q.lsbMode, lpc_weighting, T, lsbs);
+
+    u8 *dst = b.out + b.out_off[li] + (size_t)f * b.out_stride[li];
+    for (int i = 0; i < target_bytes; i++) dst[i] = bytes[i];
+}
+
+} // namespace lc3k

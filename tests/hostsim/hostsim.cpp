@@ -1,0 +1,134 @@
+// TEST TOOLING (not product code): compiles the kernel bodies of audio_codec_b200/csrc for the host and
+// runs them lane by lane, so that the stage code can be debugged against the oracle in a container without
+// a GPU.  The product library (liblc3plus_b200.so) never contains or calls this; it has the CUDA build only.
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+extern "C" {
+#include "lc3_config.h"
+}
+#include "lc3_body_serial.cuh"
+#include "lc3_body_frame.cuh"
+
+using namespace lc3k;
+
+template <int BITS> static void run_front(const LC3K_Batch &b, int f, int tile, int lane)
+{
+    switch (b.N) {
+    case 20: front_body<20, BITS>(b, f, tile, lane); break;
+    case 40: front_body<40, BITS>(b, f, tile, lane); break;
+    case 60: front_body<60, BITS>(b, f, tile, lane); break;
+    case 80: front_body<80, BITS>(b, f, tile, lane); break;
+    case 120: front_body<120, BITS>(b, f, tile, lane); break;
+    case 160: front_body<160, BITS>(b, f, tile, lane); break;
+    case 240: front_body<240, BITS>(b, f, tile, lane); break;
+    case 320: front_body<320, BITS>(b, f, tile, lane); break;
+    case 480: front_body<480, BITS>(b, f, tile, lane); break;
+    }
+}
+
+struct Sim {
+    LC3Cfg cfg;
+    int n_streams, n_slots;
+    std::vector<int32_t> slot, cfgw, st32;
+    std::vector<int16_t> st16, hist16;
+    std::vector<int32_t> hist32;
+};
+
+extern "C" void *hostsim_new(int fs, int dms, int n_streams)
+{
+    Sim *s = new Sim;
+    if (lc3cfg_init(&s->cfg, fs, 1) || lc3cfg_set_frame_dms(&s->cfg, dms)) { delete s; return 0; }
+    s->n_streams = n_streams;
+    int nt = (n_streams + 31) / 32;
+    s->n_slots = nt * 32;
+    s->slot.resize(n_streams);
+    for (int i = 0; i < n_streams; i++) s->slot[i] = i;
+    s->cfgw.assign((size_t)s->n_slots * CFG_N, 0);
+    s->st32.assign((size_t)s->n_slots * ST32_N, 0);
+    s->st16.assign((size_t)s->n_slots * ST16_N, 0);
+    s->hist16.assign((size_t)s->n_slots * LC3K_MAX_N, 0);
+    s->hist32.assign((size_t)s->n_slots * LC3K_MAX_N, 0);
+    for (int i = 0; i < s->n_slots; i++) {
+        slot_view(s->st32.data(), i, ST32_N)[ST_X_EXP] = 15;
+        slot_view(s->st32.data(), i, ST32_N)[ST_RESAMP_EXP] = 17;
+    }
+    return s;
+}
+extern "C" void hostsim_free(void *p) { delete (Sim *)p; }
+
+extern "C" int hostsim_set_bitrate(void *p, int bitrate)
+{
+    Sim *s = (Sim *)p;
+    int r = lc3cfg_set_bitrate(&s->cfg, bitrate);
+    if (r) return r;
+    for (int i = 0; i < s->n_slots; i++) {
+        for (int k = 0; k < CFG_N; k++) slot_view(s->cfgw.data(), i, CFG_N)[k] = s->cfg.ch[0][k];
+        if (s->cfg.attack_reset[0])
+            for (int k = ST_ATT_F0; k <= ST_ATT_ACC; k++) slot_view(s->st32.data(), i, ST32_N)[k] = 0;
+    }
+    s->cfg.attack_reset[0] = 0;
+    return 0;
+}
+extern "C" int hostsim_frame_len(void *p) { return ((Sim *)p)->cfg.N; }
+extern "C" int hostsim_num_bytes(void *p) { return lc3cfg_num_bytes(&((Sim *)p)->cfg); }
+
+// pcm: [n_streams][n_frames*N] (int16 or int32), out: [n_streams][n_frames][nbytes]
+extern "C" int hostsim_encode(void *p, const void *pcm, int bits, int n_frames, uint8_t *out, const uint8_t *bfi)
+{
+    Sim *s = (Sim *)p;
+    LC3K_Batch b;
+    memset(&b, 0, sizeof(b));
+    lc3cfg_fill_batch(&s->cfg, &b);
+    const int N = b.N, nb = lc3cfg_num_bytes(&s->cfg);
+    b.bits = bits;
+    b.n_lanes = s->n_streams; b.n_tiles = (s->n_streams + 31) / 32; b.n_frames = n_frames;
+    b.slot = s->slot.data(); b.cfg = s->cfgw.data(); b.st32 = s->st32.data(); b.st16 = s->st16.data();
+    b.hist16 = s->hist16.data(); b.hist32 = s->hist32.data();
+    std::vector<int64_t> out_off(s->n_streams);
+    std::vector<int32_t> out_stride(s->n_streams, nb);
+    for (int i = 0; i < s->n_streams; i++) out_off[i] = (int64_t)i * n_frames * nb;
+    b.out = out; b.out_off = out_off.data(); b.out_stride = out_stride.data(); b.bfi = bfi;
+    const size_t ftl = (size_t)n_frames * b.n_tiles * 32;
+    std::vector<int32_t> pcm_t((size_t)b.n_tiles * (n_frames + 1) * N * 32, 0); // int32 storage covers both widths
+    std::vector<int32_t> pout(ftl * PO_N), spec(ftl * N), fout(ftl * FO_N), en4(ftl * (N / 4)), rout(ftl * RO_N);
+    b.pcm_t = pcm_t.data(); b.pout = pout.data(); b.spec = spec.data(); b.fout = fout.data(); b.en4 = en4.data();
+    b.rout = rout.data();
+
+    // staging (what the stage kernel does): history prefix from the state, frames from the caller, new history
+    for (int li = 0; li < s->n_streams; li++) {
+        int tile = li >> 5, lane = li & 31, slot = s->slot[li];
+        size_t per_tile = (size_t)(n_frames + 1) * N;
+        if (bits == 16) {
+            SV<i16> t = tile_view((i16 *)b.pcm_t, tile, per_tile, lane);
+            SV<i16> h = slot_view(b.hist16, slot, LC3K_MAX_N);
+            const int16_t *src = (const int16_t *)pcm + (size_t)li * n_frames * N;
+            for (int i = 0; i < N; i++) t[i] = h[i];
+            for (int i = 0; i < n_frames * N; i++) t[N + i] = src[i];
+            for (int i = 0; i < N; i++) h[i] = t[n_frames * N + i];
+        } else {
+            SV<i32> t = tile_view((i32 *)b.pcm_t, tile, per_tile, lane);
+            SV<i32> h = slot_view(b.hist32, slot, LC3K_MAX_N);
+            const int32_t *src = (const int32_t *)pcm + (size_t)li * n_frames * N;
+            for (int i = 0; i < N; i++) t[i] = h[i];
+            for (int i = 0; i < n_frames * N; i++) t[N + i] = src[i];
+            for (int i = 0; i < N; i++) h[i] = t[n_frames * N + i];
+        }
+    }
+    AriTabs T = {(const u8 *)rom_ari_lookup, rom_ari_cumfreq, rom_ari_freq};
+    for (int tile = 0; tile < b.n_tiles; tile++)
+        for (int lane = 0; lane < 32; lane++) {
+            if (bits == 16) pitch_body<16>(b, tile, lane); else pitch_body<24>(b, tile, lane);
+        }
+    for (int f = 0; f < n_frames; f++)
+        for (int tile = 0; tile < b.n_tiles; tile++)
+            for (int lane = 0; lane < 32; lane++) {
+                if (bits == 16) run_front<16>(b, f, tile, lane); else run_front<24>(b, f, tile, lane);
+            }
+    for (int tile = 0; tile < b.n_tiles; tile++)
+        for (int lane = 0; lane < 32; lane++) rate_body(b, tile, lane, (const u8 *)rom_ari_lookup, rom_ari_bits);
+    for (int f = 0; f < n_frames; f++)
+        for (int tile = 0; tile < b.n_tiles; tile++)
+            for (int lane = 0; lane < 32; lane++) back_body(b, f, tile, lane, T, rom_ari_bits);
+    return 0;
+}
