@@ -1,0 +1,170 @@
+"""ctypes mirror of include/lc3plus_b200.h (same names, argument meaning and error codes as fx/lc3.h).
+
+`Encoder` wraps one LC3_Enc block; `enc_batch` wraps lc3plus_enc_batch.  Buffers may be numpy arrays (host)
+or integer device addresses (e.g. torch_tensor.data_ptr()).  Loading fails loudly if the CUDA library has
+not been built; encoding fails (LC3Error) if there is no CUDA device -- there is no fallback.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+ERRORS = {0: "LC3_OK", 1: "LC3_ERROR", 3: "LC3_NULL_ERROR", 4: "LC3_SAMPLERATE_ERROR", 5: "LC3_CHANNELS_ERROR",
+          6: "LC3_BITRATE_ERROR", 9: "LC3_EPMODE_ERROR", 10: "LC3_FRAMEMS_ERROR", 11: "LC3_ALIGN_ERROR",
+          12: "LC3_EPMR_ERROR", 14: "LC3_BITRATE_UNSET_ERROR", 15: "LC3_BITRATE_SET_ERROR", 18: "LC3_BW_WARNING"}
+
+
+class LC3Error(RuntimeError):
+    def __init__(self, code, what=""):
+        self.code = code
+        super().__init__(f"{ERRORS.get(code, code)} {what} {last_error()}".strip())
+
+
+def library_path():
+    return os.path.join(_HERE, "liblc3plus_b200.so")
+
+
+def load_library():
+    global _LIB
+    if _LIB is None:
+        p = library_path()
+        if not os.path.exists(p):
+            raise ImportError(f"{p} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                              "(make -C audio_codec_b200/csrc); there is no CPU fallback")
+        L = C.CDLL(p)
+        L.lc3_enc_get_size.argtypes = [C.c_int, C.c_int]
+        for n in ("lc3_enc_init",):
+            getattr(L, n).argtypes = [C.c_void_p, C.c_int, C.c_int]
+        for n in ("lc3_enc_set_bitrate", "lc3_enc_set_frame_dms", "lc3_enc_set_bandwidth", "lc3_enc_set_ep_mode",
+                  "lc3_enc_set_ep_mode_request"):
+            getattr(L, n).argtypes = [C.c_void_p, C.c_int]
+        for n in ("lc3_enc_get_scratch_size", "lc3_enc_get_input_samples", "lc3_enc_get_num_bytes",
+                  "lc3_enc_get_real_bitrate", "lc3_enc_get_delay", "lc3plus_enc_release"):
+            getattr(L, n).argtypes = [C.c_void_p]
+        for n in ("lc3_enc16", "lc3_enc24"):
+            getattr(L, n).argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.lc3plus_enc_batch.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p,
+                                        C.c_size_t, C.c_void_p]
+        L.lc3plus_kernel_launches.restype = C.c_longlong
+        L.lc3plus_last_error.restype = C.c_char_p
+        L.lc3plus_set_chunk_frames.argtypes = [C.c_int]
+        L.lc3plus_enc_release.restype = None
+        _LIB = L
+    return _LIB
+
+
+def last_error():
+    return load_library().lc3plus_last_error().decode() if _LIB is not None else ""
+
+
+def kernel_launches():
+    return int(load_library().lc3plus_kernel_launches())
+
+
+def profile_enable(on=True):
+    load_library().lc3plus_profile_enable(1 if on else 0)
+
+
+def profile_read():
+    """dict of accumulated kernel milliseconds since profile_enable()"""
+    ms = (C.c_double * 8)()
+    load_library().lc3plus_profile_read(ms)
+    return dict(zip(("stage", "pitch", "front", "rate", "back", "span", "calls", "chunks"), list(ms)))
+
+
+def set_chunk_frames(n):
+    load_library().lc3plus_set_chunk_frames(int(n))
+
+
+class Encoder:
+    """One LC3_Enc: lc3_enc_init -> lc3_enc_set_frame_dms -> lc3_enc_set_bitrate -> lc3_enc16/24 (fx/codec_exe.c:192-205)."""
+
+    def __init__(self, samplerate, channels=1, frame_dms=100, bitrate=None):
+        L = load_library()
+        size = L.lc3_enc_get_size(samplerate, channels)
+        self._mem = C.create_string_buffer(max(size, 64) + 16)
+        self.h = C.c_void_p((C.addressof(self._mem) + 15) & ~15)
+        self.channels = channels
+        self._live = False
+        r = L.lc3_enc_init(self.h, samplerate, channels)
+        if r:
+            raise LC3Error(r, "lc3_enc_init")
+        self._live = True
+        r = L.lc3_enc_set_frame_dms(self.h, frame_dms)
+        if r:
+            raise LC3Error(r, "lc3_enc_set_frame_dms")
+        if bitrate is not None:
+            self.set_bitrate(bitrate)
+
+    def close(self):
+        if self._live:
+            load_library().lc3plus_enc_release(self.h)
+            self._live = False
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_bitrate(self, bitrate, check=True):
+        r = load_library().lc3_enc_set_bitrate(self.h, bitrate)
+        if r and check:
+            raise LC3Error(r, "lc3_enc_set_bitrate")
+        return r
+
+    def set_frame_dms(self, dms):
+        return load_library().lc3_enc_set_frame_dms(self.h, dms)
+
+    def set_bandwidth(self, bw):
+        return load_library().lc3_enc_set_bandwidth(self.h, bw)
+
+    @property
+    def frame_len(self):
+        return load_library().lc3_enc_get_input_samples(self.h)
+
+    @property
+    def num_bytes(self):
+        return load_library().lc3_enc_get_num_bytes(self.h)
+
+    @property
+    def real_bitrate(self):
+        return load_library().lc3_enc_get_real_bitrate(self.h)
+
+    @property
+    def delay(self):
+        return load_library().lc3_enc_get_delay(self.h)
+
+    def enc(self, frame, bits=16, lost=False):
+        """frame: [channels, N] -> bytes of one frame (lc3_enc16 / lc3_enc24)."""
+        L = load_library()
+        frame = np.ascontiguousarray(frame, dtype=np.int16 if bits == 16 else np.int32)
+        if frame.ndim == 1:
+            frame = frame[None, :]
+        ptrs = (C.c_void_p * 2)()
+        for c in range(self.channels):
+            ptrs[c] = frame[c].ctypes.data
+        out = np.zeros(870, dtype=np.uint8)
+        n = C.c_int(-1 if lost else 0)
+        r = (L.lc3_enc16 if bits == 16 else L.lc3_enc24)(self.h, ptrs, out.ctypes.data, C.byref(n), None)
+        if r:
+            raise LC3Error(r, "lc3_enc")
+        return out[:n.value].copy()
+
+
+def _addr(x):
+    return x.ctypes.data if isinstance(x, np.ndarray) else int(x)
+
+
+def enc_batch(encoders, n_frames, pcm, stream_stride_bytes, bits, out, out_stream_stride_bytes, num_bytes=None):
+    """lc3plus_enc_batch.  pcm/out: numpy arrays or device addresses.  num_bytes: optional int32 array [S*n_frames]."""
+    L = load_library()
+    arr = (C.c_void_p * len(encoders))(*[e.h.value for e in encoders])
+    nb = num_bytes.ctypes.data if num_bytes is not None else None
+    r = L.lc3plus_enc_batch(arr, len(encoders), n_frames, _addr(pcm), stream_stride_bytes, bits, _addr(out),
+                            out_stream_stride_bytes, nb)
+    if r:
+        raise LC3Error(r, "lc3plus_enc_batch")

@@ -95,7 +95,7 @@ LC3_HD void back_body(const LC3K_Batch &b, int f, int tile, int lane, const AriT
     for (int i = 0; i < 16; i++) tns.idx[i] = (i16)fo[FO_TNS_IDX + i];
     si.ltpf_idx[0] = po[PO_LTPF_IDX0]; si.ltpf_idx[1] = po[PO_LTPF_IDX1]; si.ltpf_idx[2] = po[PO_LTPF_IDX2];
     si.fac_ns = fac_ns;
-    si.bfi_ext = b.bfi ? b.bfi[(size_t)f * b.n_lanes + li] : 0;
+    si.bfi_ext = b.bfi ? b.bfi[(size_t)(b.frame0 + f) * b.n_lanes + li] : 0;
     for (int i = 0; i < 7; i++) si.scf[i] = fo[FO_SCF + i];
 
     u8 bytes[440];
@@ -104,7 +104,7 @@ LC3_HD void back_body(const LC3K_Batch &b, int f, int tile, int lane, const AriT
     side_info(w, bytes, total_bits, b.yLen, si, b.fs_idx);
     ari_encode(bytes, w, total_bits, xq, tns, q.lastnz, cd, res, nres, q.lsbMode, lpc_weighting, T, lsbs);
 
-    u8 *dst = b.out + b.out_off[li] + (size_t)f * b.out_stride[li];
+    u8 *dst = b.out + b.out_off[li] + (size_t)(b.frame0 + f) * b.out_stride[li];
     for (int i = 0; i < target_bytes; i++) dst[i] = bytes[i];
 }
 

@@ -28,6 +28,9 @@ template <int BITS> LC3_HD void pitch_body(const LC3K_Batch &b, int tile, int la
     ps.ltpf_on = st[ST_LTPF_ON]; ps.ltpf_pitch = st[ST_LTPF_PITCH];
     as.filter_mem[0] = st[ST_ATT_F0]; as.filter_mem[1] = st[ST_ATT_F1]; as.detected = st[ST_ATT_DET];
     as.position = st[ST_ATT_POS]; as.scaling = st[ST_ATT_SCAL]; as.acc_energy = st[ST_ATT_ACC];
+    if (!attack_handling) { // the reference clears the detector whenever set_bitrate switches it off (setup_enc_lc3.c:252-275)
+        as.filter_mem[0] = as.filter_mem[1] = 0; as.detected = as.position = as.scaling = as.acc_energy = 0;
+    }
     i32 x_exp = st[ST_X_EXP], resamp_exp = st[ST_RESAMP_EXP];
 
     const int len = 32 * (b.dms / 25);

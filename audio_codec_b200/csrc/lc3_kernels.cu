@@ -1,0 +1,154 @@
+// sm_100a kernels of the batched LC3plus encoder and their launchers (C ABI towards lc3_api.c).
+//
+// Thread mapping: 32 lanes of a warp = 32 channel-streams of one tile (per-stream passes) or the same
+// 32 channel-streams at one frame index (frame-parallel passes), so every per-lane array access with a
+// warp-uniform index is one coalesced request into the tile-interleaved buffers (lc3_layout.h).
+// No tensor cores: the arithmetic is saturating 16/32-bit fixed point (see lc3_basop.cuh).
+#include <cuda_runtime.h>
+#include "lc3_body_serial.cuh"
+#include "lc3_body_frame.cuh"
+
+using namespace lc3k;
+
+// ---- staging: caller's PCM (sample-major per stream) -> tile-interleaved, history frame first
+template <class T> __global__ void __launch_bounds__(256) k_stage(LC3K_Batch b)
+{
+    __shared__ T sm[32][33];
+    const int tile = blockIdx.x, tx = threadIdx.x & 31, ty = threadIdx.x >> 5; // 32 x 8
+    const int N = b.N, total = b.n_frames * N;
+    const size_t per_tile = (size_t)(b.n_frames + 1) * N;
+    T *dst = (T *)b.pcm_t + (size_t)tile * per_tile * LC3K_LANES;
+    T *hist_pool = sizeof(T) == 2 ? (T *)b.hist16 : (T *)b.hist32;
+
+    // history prefix (lane = tx)
+    const int li_h = tile * 32 + tx;
+    const int slot_h = li_h < b.n_lanes ? b.slot[li_h] : -1;
+    if (slot_h >= 0) {
+        SV<T> h = slot_view(hist_pool, slot_h, LC3K_MAX_N);
+        for (int i = ty; i < N; i += 8) dst[(size_t)i * 32 + tx] = h[i];
+    }
+    // body: 32 lanes x 32 samples per step through shared memory
+    for (int c0 = 0; c0 < total; c0 += 32) {
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            const int lane = ty + 8 * r, li = tile * 32 + lane, i = c0 + tx;
+            T v = 0;
+            if (li < b.n_lanes && i < total) v = ((const T *)b.pcm)[b.pcm_off[li] + (size_t)b.frame0 * N + i];
+            sm[lane][tx] = v;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            const int s = ty + 8 * r, i = c0 + s;
+            if (i < total) dst[(size_t)(N + i) * 32 + tx] = sm[tx][s];
+        }
+        __syncthreads();
+    }
+    // new history = last frame of the chunk
+    if (slot_h >= 0) {
+        SV<T> h = slot_view(hist_pool, slot_h, LC3K_MAX_N);
+        for (int i = ty; i < N; i += 8) h[i] = dst[(size_t)(total + i) * 32 + tx];
+    }
+}
+
+template <int BITS> __global__ void __launch_bounds__(32) k_pitch(LC3K_Batch b) { pitch_body<BITS>(b, blockIdx.x, threadIdx.x); }
+
+template <int N, int BITS> __global__ void __launch_bounds__(128) k_front(LC3K_Batch b)
+{
+    const int warp = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (warp >= b.n_frames * b.n_tiles) return;
+    front_body<N, BITS>(b, warp / b.n_tiles, warp % b.n_tiles, lane);
+}
+
+__global__ void __launch_bounds__(32) k_rate(LC3K_Batch b)
+{
+    __shared__ u8 lut[4096];
+    __shared__ uint16_t bits[1088];
+    for (int i = threadIdx.x; i < 4096; i += 32) lut[i] = (u8)rom_ari_lookup[i];
+    for (int i = threadIdx.x; i < 1088; i += 32) bits[i] = rom_ari_bits[i];
+    __syncthreads();
+    rate_body(b, blockIdx.x, threadIdx.x, lut, bits);
+}
+
+__global__ void __launch_bounds__(128) k_back(LC3K_Batch b)
+{
+    __shared__ u8 lut[4096];
+    __shared__ uint16_t cum[1088], freq[1088], bits[1088];
+    for (int i = threadIdx.x; i < 4096; i += 128) lut[i] = (u8)rom_ari_lookup[i];
+    for (int i = threadIdx.x; i < 1088; i += 128) { cum[i] = rom_ari_cumfreq[i]; freq[i] = rom_ari_freq[i]; bits[i] = rom_ari_bits[i]; }
+    __syncthreads();
+    const int warp = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (warp >= b.n_frames * b.n_tiles) return;
+    AriTabs T = {lut, cum, freq};
+    back_body(b, warp / b.n_tiles, warp % b.n_tiles, lane, T, bits);
+}
+
+__global__ void k_reset(i32 *st32, i16 *st16, i16 *hist16, i32 *hist32, const i32 *slots, int n)
+{
+    const int k = blockIdx.x;
+    if (k >= n) return;
+    const int slot = slots[k];
+    SV<i32> a = slot_view(st32, slot, ST32_N);
+    SV<i16> c = slot_view(st16, slot, ST16_N);
+    SV<i16> h = slot_view(hist16, slot, LC3K_MAX_N);
+    SV<i32> g = slot_view(hist32, slot, LC3K_MAX_N);
+    for (int i = threadIdx.x; i < ST32_N; i += blockDim.x) a[i] = i == ST_X_EXP ? 15 : (i == ST_RESAMP_EXP ? 17 : 0);
+    for (int i = threadIdx.x; i < ST16_N; i += blockDim.x) c[i] = 0;
+    for (int i = threadIdx.x; i < LC3K_MAX_N; i += blockDim.x) { h[i] = 0; g[i] = 0; }
+}
+
+// ---- launchers
+static int done() { return (int)cudaGetLastError(); }
+
+extern "C" int lc3k_launch_reset(int32_t *st32, int16_t *st16, int16_t *hist16, int32_t *hist32, const int32_t *slots, int n, void *stream)
+{
+    if (n <= 0) return 0;
+    k_reset<<<n, 64, 0, (cudaStream_t)stream>>>(st32, st16, hist16, hist32, slots, n);
+    return done();
+}
+extern "C" int lc3k_launch_stage(const LC3K_Batch *b, void *stream)
+{
+    if (b->bits == 16) k_stage<int16_t><<<b->n_tiles, 256, 0, (cudaStream_t)stream>>>(*b);
+    else k_stage<int32_t><<<b->n_tiles, 256, 0, (cudaStream_t)stream>>>(*b);
+    return done();
+}
+extern "C" int lc3k_launch_pitch(const LC3K_Batch *b, void *stream)
+{
+    if (b->bits == 16) k_pitch<16><<<b->n_tiles, 32, 0, (cudaStream_t)stream>>>(*b);
+    else k_pitch<24><<<b->n_tiles, 32, 0, (cudaStream_t)stream>>>(*b);
+    return done();
+}
+template <int N> static void front_n(const LC3K_Batch *b, cudaStream_t s)
+{
+    const int warps = b->n_frames * b->n_tiles, blocks = (warps + 3) / 4;
+    if (b->bits == 16) k_front<N, 16><<<blocks, 128, 0, s>>>(*b);
+    else k_front<N, 24><<<blocks, 128, 0, s>>>(*b);
+}
+extern "C" int lc3k_launch_front(const LC3K_Batch *b, void *stream)
+{
+    cudaStream_t s = (cudaStream_t)stream;
+    switch (b->N) {
+    case 20: front_n<20>(b, s); break;
+    case 40: front_n<40>(b, s); break;
+    case 60: front_n<60>(b, s); break;
+    case 80: front_n<80>(b, s); break;
+    case 120: front_n<120>(b, s); break;
+    case 160: front_n<160>(b, s); break;
+    case 240: front_n<240>(b, s); break;
+    case 320: front_n<320>(b, s); break;
+    case 480: front_n<480>(b, s); break;
+    default: return (int)cudaErrorInvalidValue;
+    }
+    return done();
+}
+extern "C" int lc3k_launch_rate(const LC3K_Batch *b, void *stream)
+{
+    k_rate<<<b->n_tiles, 32, 0, (cudaStream_t)stream>>>(*b);
+    return done();
+}
+extern "C" int lc3k_launch_back(const LC3K_Batch *b, void *stream)
+{
+    const int warps = b->n_frames * b->n_tiles, blocks = (warps + 3) / 4;
+    k_back<<<blocks, 128, 0, (cudaStream_t)stream>>>(*b);
+    return done();
+}

@@ -57,6 +57,7 @@ typedef struct {
     int fs_idx, dms, dms_idx, N, yLen, nbands, fs, W_off, W_len, mdct_mem_len, bands_off, nsub, ltpf_mem_in_len,
         r12k8_mem_in_len, bw_bits, bits /* 16 | 24 */;
     int n_lanes, n_tiles, n_frames;
+    int frame0;               /* index of this chunk's first frame within the caller's batch */
     /* state pool */
     const int32_t *slot;      /* [n_lanes] */
     const int32_t *cfg;       /* pool, CFG_N words per slot */
@@ -89,9 +90,8 @@ int lc3k_launch_pitch(const LC3K_Batch *b, void *stream);
 int lc3k_launch_front(const LC3K_Batch *b, void *stream);
 int lc3k_launch_rate(const LC3K_Batch *b, void *stream);
 int lc3k_launch_back(const LC3K_Batch *b, void *stream);
-/* ROM scalars the host setup needs (same tables the kernels use) */
-void lc3k_rom_geometry(int fs_idx, int dms_idx, int *W_off, int *W_len, int *la_zeroes, int *bands_off, int *nbands,
-                       int *bw_bits);
+/* set the listed state slots to their power-on values (fx/setup_enc_lc3.c:38-66) */
+int lc3k_launch_reset(int32_t *st32, int16_t *st16, int16_t *hist16, int32_t *hist32, const int32_t *slots, int n, void *stream);
 #ifdef __cplusplus
 }
 #endif

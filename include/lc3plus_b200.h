@@ -1,0 +1,118 @@
+/* liblc3plus_b200 -- C ABI of the B200-native batched LC3plus encoder.
+ *
+ * Drop-in for the ENCODER half of the ETSI reference API (fx/lc3.h, file:line cited per function below;
+ * fx/ = LC3plus_ETSI_src_v17171_20200723/src/fixed_point/ of the reference repository), plus one new entry
+ * point, lc3plus_enc_batch, that encodes many independent streams and many frames per stream in one call.
+ * Every function is exported under the reference's `lc3_` name and under the `lc3plus_` prefix used by
+ * later ETSI releases; signatures are identical.  Output bytes are identical to the reference encoder's.
+ *
+ * Differences a caller must know:
+ *   - The encoder block the caller allocates (lc3_enc_get_size bytes) holds configuration and a handle;
+ *     the per-channel signal state lives in device memory owned by the library.  Call lc3plus_enc_release
+ *     when an encoder is no longer needed (the reference has no such call because it owns no memory).
+ *   - `scratch` is accepted and ignored.
+ *   - There is no CPU fallback: every encode call needs a CUDA device and returns LC3_ERROR if the
+ *     device path fails.
+ *   - Error protection (lc3_enc_set_ep_mode with a mode other than LC3_EP_OFF) is not implemented and
+ *     returns LC3_EPMODE_ERROR.
+ */
+#ifndef LC3PLUS_B200_H
+#define LC3PLUS_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LC3_VERSION_INT(major, minor, micro) (((major) << 16) | ((minor) << 8) | (micro))
+#define LC3_VERSION LC3_VERSION_INT(1, 4, 10)           /* fx/lc3.h:39-42 */
+#define LC3_MAX_CHANNELS 2                               /* fx/lc3.h:46 */
+#define LC3_MAX_SAMPLES 480                              /* fx/lc3.h:49 */
+#define LC3_MAX_BYTES 870                                /* fx/lc3.h:52 */
+#define LC3_ENC_MAX_SIZE 7064                            /* fx/lc3.h:55 */
+#define LC3_ENC_MAX_SCRATCH_SIZE 6784                    /* fx/lc3.h:61 */
+
+typedef enum { /* fx/lc3.h:102-126 */
+    LC3_OK = 0, LC3_ERROR = 1, LC3_DECODE_ERROR = 2, LC3_NULL_ERROR = 3, LC3_SAMPLERATE_ERROR = 4,
+    LC3_CHANNELS_ERROR = 5, LC3_BITRATE_ERROR = 6, LC3_NUMBYTES_ERROR = 7, LC3_PLCMODE_ERROR = 8,
+    LC3_EPMODE_ERROR = 9, LC3_FRAMEMS_ERROR = 10, LC3_ALIGN_ERROR = 11, LC3_EPMR_ERROR = 12, LC3_HRMODE_ERROR = 13,
+    LC3_BITRATE_UNSET_ERROR = 14, LC3_BITRATE_SET_ERROR = 15, LC3_BFI_EXT_ERROR = 16,
+    LC3_WARNING = 17, LC3_BW_WARNING = 18
+} LC3_Error;
+
+typedef enum { LC3_EP_OFF = 0, LC3_EP_ZERO = 1, LC3_EP_LOW = 2, LC3_EP_MEDIUM = 3, LC3_EP_HIGH = 4 } LC3_EpMode; /* fx/lc3.h:74-82 */
+typedef enum { LC3_EPMR_ZERO = 0, LC3_EPMR_LOW = 1, LC3_EPMR_MEDIUM = 2, LC3_EPMR_HIGH = 3 } LC3_EpModeRequest; /* fx/lc3.h:85-99 */
+
+typedef struct LC3_Enc LC3_Enc;                          /* fx/lc3.h:128 */
+
+int lc3_version(void);                                   /* fx/lc3.h:135 */
+int lc3_channels_supported(int channels);                /* fx/lc3.h:142 */
+int lc3_samplerate_supported(int samplerate);            /* fx/lc3.h:149 */
+LC3_Error lc3_enc_init(LC3_Enc *encoder, int samplerate, int channels);                                /* fx/lc3.h:170 */
+LC3_Error lc3_enc16(LC3_Enc *encoder, int16_t **input_samples, void *output_bytes, int *num_bytes, void *scratch); /* fx/lc3.h:191 */
+LC3_Error lc3_enc24(LC3_Enc *encoder, int32_t **input_samples, void *output_bytes, int *num_bytes, void *scratch); /* fx/lc3.h:198 */
+int lc3_enc_get_size(int samplerate, int channels);      /* fx/lc3.h:207 */
+int lc3_enc_get_scratch_size(const LC3_Enc *encoder);    /* fx/lc3.h:216 */
+int lc3_enc_get_input_samples(const LC3_Enc *encoder);   /* fx/lc3.h:223 */
+int lc3_enc_get_real_bitrate(const LC3_Enc *encoder);    /* fx/lc3.h:231 */
+int lc3_enc_get_num_bytes(const LC3_Enc *encoder);       /* fx/lc3.h:239 */
+LC3_Error lc3_enc_set_bitrate(LC3_Enc *encoder, int bitrate);                                           /* fx/lc3.h:258 */
+int lc3_enc_get_delay(const LC3_Enc *encoder);           /* fx/lc3.h:266 */
+LC3_Error lc3_enc_set_frame_dms(LC3_Enc *encoder, int frame_ms);                                        /* fx/lc3.h:277 */
+LC3_Error lc3_enc_set_ep_mode(LC3_Enc *encoder, LC3_EpMode epmode);                                     /* fx/lc3.h:288 */
+LC3_Error lc3_enc_set_ep_mode_request(LC3_Enc *encoder, LC3_EpModeRequest epmr);                        /* fx/lc3.h:300 */
+LC3_Error lc3_enc_set_bandwidth(LC3_Enc *encoder, int bandwidth);                                       /* fx/lc3.h:309 */
+
+/* `lc3plus_` spellings of the same functions (north-star names) */
+LC3_Error lc3plus_enc_init(LC3_Enc *encoder, int samplerate, int channels);
+LC3_Error lc3plus_enc16(LC3_Enc *encoder, int16_t **input_samples, void *output_bytes, int *num_bytes, void *scratch);
+LC3_Error lc3plus_enc24(LC3_Enc *encoder, int32_t **input_samples, void *output_bytes, int *num_bytes, void *scratch);
+LC3_Error lc3plus_enc_set_bitrate(LC3_Enc *encoder, int bitrate);
+LC3_Error lc3plus_enc_set_frame_dms(LC3_Enc *encoder, int frame_ms);
+LC3_Error lc3plus_enc_set_bandwidth(LC3_Enc *encoder, int bandwidth);
+int lc3plus_enc_get_size(int samplerate, int channels);
+int lc3plus_enc_get_input_samples(const LC3_Enc *encoder);
+int lc3plus_enc_get_num_bytes(const LC3_Enc *encoder);
+int lc3plus_enc_get_real_bitrate(const LC3_Enc *encoder);
+int lc3plus_enc_get_delay(const LC3_Enc *encoder);
+
+/* NEW (no reference counterpart; replaces the caller's loop fx/codec_exe.c:332-500 around lc3_enc16/24).
+ * Encodes n_frames consecutive frames of each of n_streams encoders.  Equivalent, byte for byte and in
+ * its effect on every encoder's state, to calling lc3_enc16/lc3_enc24 n_frames times on each encoder.
+ *
+ *   pcm                 samples of stream s start at (char*)pcm + s*stream_stride_bytes; within a stream
+ *                       the channels are planar: channel c occupies n_frames*N samples starting at sample
+ *                       c*n_frames*N (N = lc3_enc_get_input_samples).  int16_t for bitdepth 16, int32_t
+ *                       (24-bit, sign-extended) for bitdepth 24.
+ *   out                 frame f of stream s is written at (uint8_t*)out + s*out_stream_stride_bytes +
+ *                       f*lc3_enc_get_num_bytes(enc[s]); channel payloads are concatenated inside a frame
+ *                       exactly as lc3_enc16 does (fx/enc_lc3.c:279-299).
+ *   num_bytes           optional [n_streams*n_frames], stream-major.  On entry -1 marks "signal this frame as
+ *                       lost" (the reference's in/out quirk, fx/lc3.c:253); on return the byte count.
+ *   pcm / out may be host or device pointers (detected with cudaPointerGetAttributes); device pointers
+ *   avoid the copies.  Encoders may differ in sample rate, frame size, bitrate and channel count; they are
+ *   bucketed internally.  An encoder may appear only once per call.
+ */
+LC3_Error lc3plus_enc_batch(LC3_Enc *const *encoders, int n_streams, int n_frames, const void *pcm,
+                            size_t stream_stride_bytes, int bitdepth, void *out, size_t out_stream_stride_bytes,
+                            int *num_bytes);
+
+/* NEW: returns the device state of an encoder to the library's pool. */
+void lc3plus_enc_release(LC3_Enc *encoder);
+/* NEW: number of kernels launched by this process so far (for benchmarks' gpu_launches). */
+long long lc3plus_kernel_launches(void);
+/* NEW: per-kernel device timing with CUDA events on the library's launching stream.  After enable(1), every
+ * batch call accumulates into ms[8] = {stage, pitch, front, rate, back kernel ms, first-launch-to-last-kernel
+ * span ms, calls, chunks}; enable() also clears the accumulators. */
+void lc3plus_profile_enable(int on);
+void lc3plus_profile_read(double *ms);
+/* NEW: last CUDA error string seen by the library ("" if none). */
+const char *lc3plus_last_error(void);
+/* NEW: upper bound on channel-frames processed per internal chunk (default 524288); tuning knob. */
+void lc3plus_set_chunk_frames(int channel_frames);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
