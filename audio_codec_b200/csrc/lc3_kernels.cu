@@ -7,6 +7,8 @@
 #include <cuda_runtime.h>
 #include "lc3_body_serial.cuh"
 #include "lc3_body_frame.cuh"
+#include "lc3_pitch_warp.cuh"
+#include "lc3_rate_warp.cuh"
 
 using namespace lc3k;
 
@@ -51,7 +53,13 @@ template <class T> __global__ void __launch_bounds__(256) k_stage(LC3K_Batch b)
     }
 }
 
-template <int BITS> __global__ void __launch_bounds__(32) k_pitch(LC3K_Batch b) { pitch_body<BITS>(b, blockIdx.x, threadIdx.x); }
+// per-stream passes: one warp per channel-stream, 4 streams per block
+template <int BITS> __global__ void __launch_bounds__(128) k_pitch(LC3K_Batch b)
+{
+    __shared__ PitchShared sh[4];
+    const int w = threadIdx.x >> 5;
+    pitch_warp_body<BITS>(b, blockIdx.x * 4 + w, sh[w]);
+}
 
 template <int N, int BITS> __global__ void __launch_bounds__(128) k_front(LC3K_Batch b)
 {
@@ -60,14 +68,16 @@ template <int N, int BITS> __global__ void __launch_bounds__(128) k_front(LC3K_B
     front_body<N, BITS>(b, warp / b.n_tiles, warp % b.n_tiles, lane);
 }
 
-__global__ void __launch_bounds__(32) k_rate(LC3K_Batch b)
+__global__ void __launch_bounds__(128) k_rate(LC3K_Batch b)
 {
+    __shared__ RateShared sh[4];
     __shared__ u8 lut[4096];
     __shared__ uint16_t bits[1088];
-    for (int i = threadIdx.x; i < 4096; i += 32) lut[i] = (u8)rom_ari_lookup[i];
-    for (int i = threadIdx.x; i < 1088; i += 32) bits[i] = rom_ari_bits[i];
+    for (int i = threadIdx.x; i < 4096; i += 128) lut[i] = (u8)rom_ari_lookup[i];
+    for (int i = threadIdx.x; i < 1088; i += 128) bits[i] = rom_ari_bits[i];
     __syncthreads();
-    rate_body(b, blockIdx.x, threadIdx.x, lut, bits);
+    const int w = threadIdx.x >> 5;
+    rate_warp_body(b, blockIdx.x * 4 + w, sh[w], lut, bits);
 }
 
 __global__ void __launch_bounds__(128) k_back(LC3K_Batch b)
@@ -114,8 +124,9 @@ extern "C" int lc3k_launch_stage(const LC3K_Batch *b, void *stream)
 }
 extern "C" int lc3k_launch_pitch(const LC3K_Batch *b, void *stream)
 {
-    if (b->bits == 16) k_pitch<16><<<b->n_tiles, 32, 0, (cudaStream_t)stream>>>(*b);
-    else k_pitch<24><<<b->n_tiles, 32, 0, (cudaStream_t)stream>>>(*b);
+    const int blocks = (b->n_lanes + 3) / 4;
+    if (b->bits == 16) k_pitch<16><<<blocks, 128, 0, (cudaStream_t)stream>>>(*b);
+    else k_pitch<24><<<blocks, 128, 0, (cudaStream_t)stream>>>(*b);
     return done();
 }
 template <int N> static void front_n(const LC3K_Batch *b, cudaStream_t s)
@@ -143,7 +154,7 @@ extern "C" int lc3k_launch_front(const LC3K_Batch *b, void *stream)
 }
 extern "C" int lc3k_launch_rate(const LC3K_Batch *b, void *stream)
 {
-    k_rate<<<b->n_tiles, 32, 0, (cudaStream_t)stream>>>(*b);
+    k_rate<<<(b->n_lanes + 3) / 4, 128, 0, (cudaStream_t)stream>>>(*b);
     return done();
 }
 extern "C" int lc3k_launch_back(const LC3K_Batch *b, void *stream)

@@ -1,0 +1,483 @@
+// Time-domain pass, ONE WARP PER CHANNEL-STREAM (fx/enc_lc3.c:65-114): [24-bit block scaling
+// fx/scale_signal24_fx.c:13-92] 12.8 kHz resampler + 50 Hz high-pass (fx/resamp12k8_fx.c:15-113), open-loop
+// pitch analysis (fx/olpa_fx.c:16-222), LTPF parameter coder (fx/ltpf_coder_fx.c:17-307), attack detector
+// (fx/attack_detector_fx.c:13-119).
+//
+// This is the chain whose state makes frame n+1 wait for frame n, so a stream's frames are walked in order;
+// the parallelism is inside the frame: lanes split the FIR outputs, the correlation lags and the sample
+// loops, with the stream's signal memories resident in the warp's shared-memory block for the whole chunk.
+// Phases and reductions follow lc3_warp.cuh; arithmetic follows the cited reference lines exactly.  Sums of
+// products that the reference accumulates with saturating L_mac0 are reduced across lanes in 64 bits and
+// clamped: operands are block-scaled to |v| <= 2^12 (3 bits of headroom, olpa_fx.c:60-98,
+// ltpf_coder_fx.c:63-79), so no partial sum of <= 256 products can leave the 32-bit range and the result is
+// the same for any summation order.
+#pragma once
+#include "lc3_stages.cuh"
+#include "lc3_warp.cuh"
+
+namespace lc3k {
+
+struct PitchShared {
+    WarpRed red;
+    i32 sum0[20], sum2[20];       // LTPF: cross sums and lagged energies per candidate lag
+    i16 xs[64 + LC3K_MAX_N];      // scaled input; xs[64 + i] = sample i of the frame, i in [-60, N)
+    i16 filt[240];                // polyphase resampler taps of this sample rate
+    i16 s12[24 + 128 + 8];        // [24-sample delay line | new 12.8 kHz samples]
+    i16 fir[128];                 // resampler output before the high-pass
+    i16 m12[4];                   // olpa_mem_s12k8
+    i16 olpa[2][130 + 64 + 2];    // 6.4 kHz history + new samples, ping-pong
+    i16 ltpf[2][264 + 128 + 4];   // 12.8 kHz history + new samples, ping-pong
+    i16 ac[32];                   // LTPF normalised correlations
+    i16 dd[2 + 160 + 2];          // attack detector: decimated signal, two samples of history first
+};
+
+// raw sample i (relative to frame f) of this stream: previous-frame samples of the chunk's first frame come
+// from the staged history prefix, everything else straight from the caller's PCM (coalesced along i)
+template <class T> struct RawPcm {
+    const T *cur;        // caller's PCM at sample 0 of frame f
+    SV<const T> hist;    // staged history frame (tile-interleaved), sample 0 of the previous frame
+    int N, first;
+    LC3_HDM i32 operator()(int i) const { return (i < 0 && first) ? (i32)hist[N + i] : (i32)cur[i]; }
+};
+
+template <int BITS> LC3_HD void pitch_warp_body(const LC3K_Batch &b, int li, PitchShared &sh)
+{
+    typedef typename std::conditional<BITS == 16, i16, i32>::type T;
+    if (li >= b.n_lanes) return;
+    const int tile = li >> 5, tl = li & 31;
+    const int slot = b.slot[li];
+    SV<i32> st = slot_view(b.st32, slot, ST32_N);
+    SV<i16> s16 = slot_view(b.st16, slot, ST16_N);
+    SV<const i32> cfg = slot_view(b.cfg, slot, CFG_N);
+    const i32 ltpf_enable = cfg[CFG_LTPF_ENABLE], attack_handling = cfg[CFG_ATTACK];
+    const int N = b.N, dms = b.dms, rl = b.r12k8_mem_in_len, ml = b.mdct_mem_len;
+    const int len = 32 * (dms / 25), len2 = len >> 1;
+    const int olpa_len = dms == 25 ? 130 : 114, acflen6 = dms == 25 ? len2 + 16 : len2;
+    const int lt_len = b.ltpf_mem_in_len;
+    const int upfac = rom_resamp_params[b.fs_idx * 4 + 0], delay2 = 2 * rom_resamp_params[b.fs_idx * 4 + 1];
+    const int off_int = rom_resamp_params[b.fs_idx * 4 + 2], off_frac = rom_resamp_params[b.fs_idx * 4 + 3];
+
+    // ---- load the stream's state: signal memories to shared memory, scalars to (replicated) registers
+    LC3_LANES(l)
+        for (int k = l; k < 240; k += 32) sh.filt[k] = rom_resamp_filt[b.fs_idx * 240 + k];
+        if (l < 24) sh.s12[l] = s16[S16_MEM_OUT + l];
+        if (l < 3) sh.m12[l] = s16[S16_OLPA_S12 + l];
+        for (int k = l; k < olpa_len; k += 32) sh.olpa[0][k] = s16[S16_OLPA_BUF + k];
+        for (int k = l; k < lt_len; k += 32) sh.ltpf[0][k] = s16[S16_LTPF_BUF + k];
+    LC3_LANES_END
+    i32 m0 = st[ST_MEM50_0], m1 = st[ST_MEM50_1];
+    i32 olpa_exp = st[ST_OLPA_EXP], olpa_pitch = st[ST_OLPA_PITCH];
+    i32 ltpf_exp = st[ST_LTPF_EXP], ltpf_nc = st[ST_LTPF_NC], ltpf_mnc = st[ST_LTPF_MNC], ltpf_on = st[ST_LTPF_ON],
+        ltpf_pitch_mem = st[ST_LTPF_PITCH];
+    AttackState as;
+    as.filter_mem[0] = st[ST_ATT_F0]; as.filter_mem[1] = st[ST_ATT_F1]; as.detected = st[ST_ATT_DET];
+    as.position = st[ST_ATT_POS]; as.scaling = st[ST_ATT_SCAL]; as.acc_energy = st[ST_ATT_ACC];
+    if (!attack_handling) { // cleared whenever set_bitrate switches the detector off (setup_enc_lc3.c:252-275)
+        as.filter_mem[0] = as.filter_mem[1] = 0; as.detected = as.position = as.scaling = as.acc_energy = 0;
+    }
+    i32 x_exp = st[ST_X_EXP], resamp_exp = st[ST_RESAMP_EXP];
+    int ob = 0, lb = 0; // ping-pong selectors of the OLPA / LTPF buffers
+
+    RawPcm<T> raw;
+    raw.N = N;
+    raw.hist = tile_view((const T *)b.pcm_t, (size_t)tile, (size_t)(b.n_frames + 1) * N, tl);
+
+    for (int f = 0; f < b.n_frames; f++) {
+        raw.cur = (const T *)b.pcm + b.pcm_off[li] + (size_t)(b.frame0 + f) * N;
+        raw.first = f == 0;
+
+        // ---- A. input: 24-bit block exponent (scale_signal24_fx.c:13-92), scaled samples to shared memory
+        if (BITS == 24) {
+            i32 e = 7;
+            LC3_LANES(l) // current frame
+                Range r; range_init(r);
+                for (int i = l; i < N; i += 32) range_add(r, raw(i));
+                sh.red.a[l] = r.mx; sh.red.b[l] = r.mn;
+            LC3_LANES_END
+            { Range r = {warp_max(sh.red.a), warp_min(sh.red.b)}; e = s_max(e, s_sub(23, range_headroom32(r, 32))); }
+            LC3_LANES(l) // MDCT memory = last ml samples of the previous frame
+                Range r; range_init(r);
+                for (int i = l - ml; i < 0; i += 32) range_add(r, raw(i));
+                sh.red.a[l] = r.mx; sh.red.b[l] = r.mn;
+            LC3_LANES_END
+            { Range r = {warp_max(sh.red.a), warp_min(sh.red.b)}; e = s_max(e, s_sub(23, range_headroom32(r, 32))); }
+            LC3_LANES(l) // resampler memory = last rl samples of the previous frame
+                Range r; range_init(r);
+                for (int i = l - rl; i < 0; i += 32) range_add(r, raw(i));
+                sh.red.a[l] = r.mx; sh.red.b[l] = r.mn;
+            LC3_LANES_END
+            { Range r = {warp_max(sh.red.a), warp_min(sh.red.b)}; e = s_max(e, s_sub(23, range_headroom32(r, 32))); }
+            { Range r; range_init(r); range_add(r, m0); range_add(r, m1);
+              e = s_max(e, s_sub(s_sub(resamp_exp, 2), range_headroom32(r, 32))); }
+            LC3_LANES(l) // resampler output delay line
+                Range r; range_init(r);
+                if (l < 24) range_add(r, sh.s12[l]);
+                sh.red.a[l] = r.mx; sh.red.b[l] = r.mn;
+            LC3_LANES_END
+            { Range r = {warp_max(sh.red.a), warp_min(sh.red.b)}; e = s_max(e, s_sub(s_sub(resamp_exp, 2), range_headroom16(r, 16))); }
+            { Range r; range_init(r); range_add(r, sh.m12[0]); range_add(r, sh.m12[1]); range_add(r, sh.m12[2]);
+              e = s_max(e, s_sub(s_sub(resamp_exp, 2), range_headroom16(r, 16))); }
+            LC3_SYNC; // every lane has read m12 / s12 before they are rescaled
+            x_exp = e;
+            const i32 shm = s_sub(s_sub(resamp_exp, 2), x_exp);
+            resamp_exp = s_add(x_exp, 2);
+            if (shm) {
+                m0 = l_shl(m0, shm); m1 = l_shl(m1, shm);
+                LC3_LANES(l)
+                    if (l < 24) sh.s12[l] = (i16)s_shl(sh.s12[l], shm);
+                    if (l >= 24 && l < 27) sh.m12[l - 24] = (i16)s_shl(sh.m12[l - 24], shm);
+                LC3_LANES_END
+            }
+        }
+        {
+            const i32 shx = s_sub(23, x_exp);
+            LC3_LANES(l)
+                for (int i = l - rl; i < N; i += 32) sh.xs[64 + i] = (i16)(BITS == 16 ? raw(i) : l_round(l_shl(raw(i), shx)));
+            LC3_LANES_END
+        }
+
+        // ---- B. polyphase FIR to 12.8 kHz (resamp12k8_fx.c:62-86): lane = output sample
+        LC3_LANES(l)
+            for (int n = l; n < len; n += 32) {
+                const int t = n * off_frac, ii = 1 + n * off_int + t / upfac - rl, fr = t % upfac;
+                const i16 *co = &sh.filt[fr * delay2], *in = &sh.xs[64 + ii];
+                i32 acc = l_mult0(in[0], co[0]);
+                for (int m = 1; m < delay2; m++) {
+                    i32 c = co[m];
+                    if (c) acc = l_mac0(acc, in[m], c);
+                }
+                sh.fir[n] = (i16)l_round(acc);
+            }
+        LC3_LANES_END
+
+        // ---- C. 50 Hz high-pass, a true recursion (resamp12k8_fx.c:88-104): every lane runs it redundantly so
+        //         the filter state stays warp-uniform; all lanes store the same value to s12[24 + n]
+        {
+            const i32 n0 = rom_hp50_num[0], n1 = rom_hp50_num[1], n2 = rom_hp50_num[2], d0 = rom_hp50_den[0], d1 = rom_hp50_den[1];
+            for (int n = 0; n < len; n++) {
+                const i32 v = sh.fir[n];
+                const i32 o = l_mac0(m0, n0, v);
+                const i32 t = l_mac0(mpy32x16k(o, d0), n1, v);
+                m0 = l_add(m1, l_shl_p(t, 1));
+                m1 = l_mac0(mpy32x16k(o, d1), n2, v);
+                sh.s12[24 + n] = (i16)l_round(o);
+            }
+        }
+        LC3_SYNC; // s12[0 .. len] is the delayed 12.8 kHz signal of this frame
+
+        // ---- D. OLPA: 2:1 decimation with a 5-tap low-pass (olpa_fx.c:36-58): lane = 6.4 kHz sample.
+        //         v[j] = m12[3 + j] for j < 0, s12[j] otherwise; output k uses v[2k-3 .. 2k+1].
+        i16 *omem = sh.olpa[ob], *s6 = omem + olpa_len;
+        LC3_LANES(l)
+            for (int k = l; k < len2; k += 32) {
+                i32 v[5];
+#pragma unroll
+                for (int j = 0; j < 5; j++) { const int q = 2 * k - 3 + j; v[j] = q < 0 ? sh.m12[3 + q] : sh.s12[q]; }
+                i32 sum = l_mac(l_mac(l_mult(v[0], 4053), v[1], 7712), v[2], 9239);
+                s6[k] = (i16)l_round(l_mac(l_mac(sum, v[3], 7712), v[4], 4053));
+            }
+        LC3_LANES_END
+        LC3_LANES(l)
+            if (l < 3) sh.m12[l] = sh.s12[len - 3 + l];
+            // headroom of the history and of the new samples (olpa_fx.c:60-63)
+            Range rh, rn; range_init(rh); range_init(rn);
+            for (int k = l; k < olpa_len; k += 32) range_add(rh, omem[k]);
+            for (int k = l; k < len2; k += 32) range_add(rn, s6[k]);
+            sh.red.a[l] = rh.mx; sh.red.b[l] = rh.mn; sh.red.c[l] = rn.mx; sh.red.d[l] = rn.mn;
+        LC3_LANES_END
+        i32 pitch, normcorr;
+        {
+            Range rh = {warp_max(sh.red.a), warp_min(sh.red.b)};
+            Range rn = {warp_max(sh.red.c), warp_min(sh.red.d)};
+            const i32 sc0 = s_sub(range_headroom16(rh, 16), 3);
+            olpa_exp = s_sub(olpa_exp, sc0);
+            const i32 sc1 = s_sub(range_headroom16(rn, 16), 3);
+            const i32 s6_exp = s_sub(resamp_exp, sc1);
+            const i32 sc2 = s_sub(olpa_exp, s6_exp);
+            i32 e_new, e_hist;
+            if (sc2 > 0) { e_new = s_sub(sc1, sc2); e_hist = sc0; }
+            else { e_new = sc1; e_hist = s_add(sc0, sc2); olpa_exp = s6_exp; }
+            const i32 t_new = e_new < 0 ? s_shl(-32768, s_max(e_new, -15)) : 0;
+            const i32 t_hist = e_hist < 0 ? s_shl(-32768, s_max(e_hist, -15)) : 0;
+            LC3_LANES(l) // Scale_sig (basop_util.c:571-595) on both parts
+                if (e_new) for (int k = l; k < len2; k += 32) s6[k] = (i16)scale_val(s6[k], e_new, t_new);
+                if (e_hist) for (int k = l; k < olpa_len; k += 32) omem[k] = (i16)scale_val(omem[k], e_hist, t_hist);
+            LC3_LANES_END
+        }
+        {
+            // ---- E. autocorrelation, lags 17..114: lane = lag (olpa_fx.c:101-122, :157-172)
+            const i16 *s = dms == 25 ? s6 - 16 : s6;
+            const i32 lo = s_max(17, s_sub(olpa_pitch, 4)), hi = s_min(114, s_add(olpa_pitch, 4));
+            LC3_LANES(l)
+                i64 kw = LC3_I32_MIN * (i64)4294967296LL, k2 = kw;
+                for (int n = 17 + l; n <= 114; n += 32) {
+                    i32 acc = l_mult0(s[0], s[-n]);
+                    for (int m = 1; m < acflen6; m++) acc = l_mac0(acc, s[m], s[m - n]);
+                    const i64 a = argmax_key(mpy32x16(acc, rom_olpa_weight[n - 17]), n);
+                    kw = a > kw ? a : kw;
+                    if (n >= lo && n <= hi) { const i64 c = argmax_key(acc, n); k2 = c > k2 ? c : k2; }
+                }
+                sh.red.q[l] = kw;
+                sh.red.q2[l] = k2;
+            LC3_LANES_END
+            i32 p = argmax_index(warp_max64(sh.red.q));
+            const i32 p2 = lo > hi ? lo : argmax_index(warp_max64(sh.red.q2));
+
+            // ---- F. normalised correlation at the candidates (olpa_fx.c:126-155, :174-205): lane = sample
+            i32 nc[2] = {0, 0};
+            const int ncand = p != p2 ? 2 : 1;
+            for (int c = 0; c < ncand; c++) {
+                const int lag = c == 0 ? p : p2;
+                LC3_LANES(l)
+                    i32 a0 = 0, a1 = 0, a2 = 0;
+                    for (int m = l; m < acflen6; m += 32) { i32 x = s[m], y = s[m - lag]; a0 += x * y; a1 += y * y; a2 += x * x; }
+                    sh.red.a[l] = a0; sh.red.b[l] = a1; sh.red.c[l] = a2;
+                LC3_LANES_END
+                const i32 s0 = warp_sum(sh.red.a), s1 = warp_sum(sh.red.b) + 1, s2 = warp_sum(sh.red.c) + 1;
+                nc[c] = normcorr_q15(s0, s1, s2, 0, 0);
+            }
+            normcorr = nc[0];
+            if (p != p2 && s_sub(nc[1], s_mult_r(nc[0], 27853)) > 0) { p = p2; normcorr = nc[1]; }
+            olpa_pitch = p;
+            pitch = s_shl(p, 1);
+            // history for the next frame goes to the other buffer
+            i16 *onext = sh.olpa[ob ^ 1];
+            LC3_LANES(l)
+                for (int k = l; k < olpa_len; k += 32) onext[k] = omem[k + len2];
+            LC3_LANES_END
+            ob ^= 1;
+        }
+
+        // ---- G. LTPF (ltpf_coder_fx.c:17-307)
+        i32 ltpf_bits, lt0 = 0, lt1 = 0, lt2 = 0, nc_ltpf, pitch_ltpf = 0, active = 0;
+        {
+            i16 *lmem = sh.ltpf[lb], *x = lmem + lt_len;
+            LC3_LANES(l)
+                for (int k = l; k <= len; k += 32) x[k] = sh.s12[k];
+            LC3_LANES_END
+            LC3_LANES(l)
+                Range rh, rn; range_init(rh); range_init(rn);
+                for (int k = l; k < lt_len; k += 32) range_add(rh, lmem[k]);
+                for (int k = l; k <= len; k += 32) range_add(rn, x[k]);
+                sh.red.a[l] = rh.mx; sh.red.b[l] = rh.mn; sh.red.c[l] = rn.mx; sh.red.d[l] = rn.mn;
+            LC3_LANES_END
+            {
+                Range rh = {warp_max(sh.red.a), warp_min(sh.red.b)};
+                Range rn = {warp_max(sh.red.c), warp_min(sh.red.d)};
+                const i32 sc0 = s_sub(range_headroom16(rh, 16), 3);
+                ltpf_exp = s_sub(ltpf_exp, sc0);
+                const i32 sc1 = s_sub(range_headroom16(rn, 16), 3);
+                const i32 xe = s_sub(resamp_exp, sc1);
+                const i32 sc2 = s_sub(ltpf_exp, xe);
+                i32 e_new, e_hist;
+                if (sc2 > 0) { e_new = s_sub(sc1, sc2); e_hist = sc0; }
+                else { e_new = sc1; e_hist = s_add(sc0, sc2); ltpf_exp = xe; }
+                const i32 t_new = e_new < 0 ? s_shl(-32768, s_max(e_new, -15)) : 0;
+                const i32 t_hist = e_hist < 0 ? s_shl(-32768, s_max(e_hist, -15)) : 0;
+                LC3_LANES(l)
+                    if (e_new) for (int k = l; k <= len; k += 32) x[k] = (i16)scale_val(x[k], e_new, t_new);
+                    if (e_hist) for (int k = l; k < lt_len; k += 32) lmem[k] = (i16)scale_val(lmem[k], e_hist, t_hist);
+                LC3_LANES_END
+            }
+            if (s_sub(normcorr, 19660) > 0) {
+                const i32 min_p = s_max(s_sub(pitch, 4), 32), max_p = s_min(s_add(pitch, 4), 228);
+                const i32 ac_lo = s_sub(min_p, 4), ac_hi = s_add(max_p, 4);
+                const int nlags = ac_hi - ac_lo + 1;
+                const int acflen = dms == 25 ? 2 * len : len;
+                const i16 *xp = dms == 25 ? x - len : x;
+
+                LC3_LANES(l) // energies of the current and of the first lagged window: lane = sample
+                    i64 a1 = 0, a2 = 0;
+                    for (int m = l; m < acflen; m += 32) { i32 u = xp[m], v = xp[m - ac_lo]; a1 += u * u; a2 += v * v; }
+                    sh.red.q[l] = a1; sh.red.q2[l] = a2;
+                LC3_LANES_END
+                i32 sum1 = clamp64(1 + warp_sum64(sh.red.q));
+                const i32 sum2_0 = clamp64(1 + warp_sum64(sh.red.q2));
+                const i32 n1 = l_norm(sum1);
+                sum1 = l_shl(sum1, n1);
+
+                LC3_LANES(l) // lane = candidate lag: cross-correlation, sliding lagged energy, normalisation
+                    if (l < nlags) {
+                        const int n = ac_lo + l;
+                        i32 s0 = l_mac0(0, xp[0], xp[-n]);
+                        for (int m = 1; m < acflen; m++) s0 = l_mac0(s0, xp[m], xp[m - n]);
+                        i32 s2 = sum2_0;
+                        for (int q = ac_lo + 1; q <= n; q++) { // slide the window one sample per lag (ltpf_coder_fx.c:116-120)
+                            const i32 o = xp[acflen - 1 - (q - 1)], w = xp[-q];
+                            s2 = l_msu0(s2, o, o);
+                            s2 = l_mac0(s2, w, w);
+                        }
+                        sh.ac[l] = (i16)normcorr_q15(s0, sum1, s2, 1, n1);
+                    }
+                LC3_LANES_END
+
+                i32 ac_max = sh.ac[min_p - ac_lo], pit = min_p;
+                for (int n = min_p + 1; n <= max_p; n++) {
+                    const i32 v = sh.ac[n - ac_lo];
+                    if (s_sub(v, ac_max) > 0) pit = n;
+                    ac_max = s_max(ac_max, v);
+                }
+                i32 p_int = pit, p_fr = 0, p_idx = s_add(p_int, 283);
+                if (pit < 157) { // fractional refinement
+                    const int res = pit < 127 ? 1 : 2;
+                    int fr0 = pit < 127 ? -3 : -2;
+                    if (pit == min_p) fr0 = 0;
+                    i32 best = LC3_I32_MIN;
+                    for (int fr = fr0; fr < 4; fr += res) {
+                        const i16 *h = &rom_ltpf_ac_interp[(fr + 3) * 9];
+                        i32 s = l_mult0(sh.ac[p_int - ac_lo - 4], h[0]);
+                        for (int k = 1; k < 9; k++) s = l_mac0(s, sh.ac[p_int - ac_lo - 4 + k], h[k]);
+                        if (l_sub(s, best) > 0) p_fr = fr;
+                        best = l_max(best, s);
+                    }
+                    if (p_fr < 0) { p_int = s_sub(p_int, 1); p_fr = s_add(p_fr, 4); }
+                    if (p_int >= 127) p_idx = s_add(s_add(s_shl(p_int, 1), p_fr >> 1), 126);
+                    else p_idx = s_sub(s_add(s_shl(p_int, 2), p_fr), 128);
+                }
+                pitch_ltpf = s_add(s_shl(p_int, 2), p_fr);
+
+                const i16 *f0 = &rom_ltpf_inter_filt[0], *fp = &rom_ltpf_inter_filt[p_fr * 12];
+                const i32 f00 = f0[0], f01 = f0[1], f02 = f0[2], fp0 = fp[0], fp1 = fp[1], fp2 = fp[2], fp3 = fp[3];
+                LC3_LANES(l) // filtered current / predicted frame and their correlation: lane = sample
+                    i64 a0 = 0, a1 = 0, a2 = 0;
+                    for (int n = l; n < acflen; n += 32) {
+                        i32 s = l_mult(xp[n + 1], f00);
+                        s = l_mac(s, xp[n], f01);
+                        const i32 c = s_mac_r(s, xp[n - 1], f02);
+                        s = l_mult(xp[n - p_int + 1], fp0);
+                        s = l_mac(s, xp[n - p_int], fp1);
+                        s = l_mac(s, xp[n - p_int - 1], fp2);
+                        const i32 p = s_mac_r(s, xp[n - p_int - 2], fp3);
+                        a0 += c * p; a1 += p * p; a2 += c * c;
+                    }
+                    sh.red.q[l] = a0; sh.red.q2[l] = a1; sh.red.q3[l] = a2;
+                LC3_LANES_END
+                const i32 s0 = clamp64(warp_sum64(sh.red.q)), s1 = clamp64(1 + warp_sum64(sh.red.q2)),
+                          s2 = clamp64(1 + warp_sum64(sh.red.q3));
+                nc_ltpf = normcorr_q15(s0, s1, s2, 0, 0);
+                if (nc_ltpf < 0) nc_ltpf = 0;
+
+                if (ltpf_enable == 1) {
+                    if ((ltpf_on == 0 && s_sub(ltpf_nc, 30802) > 0 && s_sub(nc_ltpf, 30802) > 0 &&
+                         (dms == 100 || s_sub(ltpf_mnc, 30802) > 0)) ||
+                        (ltpf_on == 1 && s_sub(nc_ltpf, 29491) > 0) ||
+                        (ltpf_on == 1 && s_sub(s_abs(s_sub(pitch_ltpf, ltpf_pitch_mem)), 8) < 0 &&
+                         s_add(s_sub(nc_ltpf, ltpf_nc), 3277) > 0 && s_sub(nc_ltpf, 27525) > 0))
+                        active = 1;
+                }
+                lt0 = 1; lt1 = active; lt2 = p_idx;
+                ltpf_bits = 11;
+            } else {
+                nc_ltpf = normcorr;
+                ltpf_bits = 1;
+            }
+            i16 *lnext = sh.ltpf[lb ^ 1];
+            LC3_LANES(l)
+                for (int k = l; k < lt_len; k += 32) lnext[k] = lmem[k + len];
+            LC3_LANES_END
+            lb ^= 1;
+            ltpf_mnc = ltpf_nc; ltpf_nc = nc_ltpf; ltpf_on = active; ltpf_pitch_mem = pitch_ltpf;
+        }
+
+        // ---- H. attack detector (attack_detector_fx.c:13-119), 10 ms frames at 32/48 kHz only
+        if (attack_handling) {
+            const i32 in_scaling = s_sub(x_exp, 15);
+            LC3_LANES(l)
+                Range r; range_init(r);
+                for (int i = l; i < N; i += 32) range_add(r, sh.xs[64 + i]);
+                sh.red.a[l] = r.mx; sh.red.b[l] = r.mn;
+            LC3_LANES_END
+            Range rg = {warp_max(sh.red.a), warp_min(sh.red.b)};
+            const i32 s0 = s_add(range_headroom16(rg, 0), in_scaling);
+            Range r1; range_init(r1); range_add(r1, as.filter_mem[0]); range_add(r1, as.filter_mem[1]);
+            const i32 s1 = s_add(range_headroom16(r1, 16), as.scaling);
+            Range r2; range_init(r2); range_add(r2, as.acc_energy);
+            const i32 s2 = s_shr(s_add(s_add(range_headroom32(r2, 32), s_shl(as.scaling, 1)), 1), 1);
+            const i32 ns = s_sub(s_min(s0, s_min(s1, s2)), 2);
+            const i32 rs = s_sub(ns, as.scaling);
+            if (rs) {
+                as.filter_mem[0] = s_shl(as.filter_mem[0], rs);
+                as.filter_mem[1] = s_shl(as.filter_mem[1], rs);
+                as.acc_energy = l_shl(as.acc_energy, s_shl(rs, 1));
+            }
+            as.scaling = ns;
+            const int dec = b.fs == 32000 ? 2 : 3;
+            const i32 ds = s_sub(dec - 1, s_sub(ns, in_scaling));
+            const i32 fm0 = as.filter_mem[0], fm1 = as.filter_mem[1];
+            LC3_LANES(l) // decimate to 16 kHz: lane = output sample
+                if (l == 0) { sh.dd[0] = (i16)fm0; sh.dd[1] = (i16)fm1; }
+                for (int i = l; i < 160; i += 32) {
+                    const i16 *in = &sh.xs[64 + dec * i];
+                    i32 d;
+                    if (dec == 2) d = s_add(s_shr(in[0], ds), s_shr(in[1], ds));
+                    else d = s_add(s_shr(in[0], ds), s_add(s_shr(in[1], ds), s_shr(in[2], ds)));
+                    sh.dd[2 + i] = (i16)d;
+                }
+            LC3_LANES_END
+            LC3_LANES(l) // 3-tap high-pass on the unfiltered neighbours, energies of the four 40-sample blocks
+                i64 e[4] = {0, 0, 0, 0};
+                for (int i = l; i < 160; i += 32) {
+                    i32 t = l_mult(sh.dd[2 + i], 12288);
+                    t = l_msu(t, sh.dd[1 + i], 16384);
+                    t = l_mac(t, sh.dd[i], 4096);
+                    const i32 fv = hi16(t);
+                    const i64 sq = l_mult(fv, fv);
+                    const int blk = i / 40;
+#pragma unroll
+                    for (int j = 0; j < 4; j++) if (blk == j) e[j] += sq;
+                }
+                sh.red.q[l] = e[0]; sh.red.q2[l] = e[1]; sh.red.q3[l] = e[2];
+                sh.red.a[l] = (i32)(e[3] >> 32); sh.red.b[l] = (i32)(e[3] & 0xffffffff);
+            LC3_LANES_END
+            i32 be[4];
+            be[0] = clamp64(warp_sum64(sh.red.q)); be[1] = clamp64(warp_sum64(sh.red.q2)); be[2] = clamp64(warp_sum64(sh.red.q3));
+            LC3_LANES(l) sh.red.q[l] = ((i64)sh.red.a[l] << 32) | (u32)sh.red.b[l]; LC3_LANES_END
+            be[3] = clamp64(warp_sum64(sh.red.q));
+            as.filter_mem[0] = sh.dd[2 + 158];
+            as.filter_mem[1] = sh.dd[2 + 159];
+            i32 detected = as.position >= 2, pos = -1, acc = as.acc_energy;
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const i32 lw = lo16(be[j] >> 1) & 0x7fff, hw = hi16(be[j]); // be / 8.5
+                i32 q = l_mult0(lw, 30840) >> 15;
+                q = l_mac0(q, hw, 30840) >> 2;
+                if (q > acc) { pos = j; detected = 1; }
+                acc = l_max(acc >> 2, be[j]);
+            }
+            as.acc_energy = acc; as.detected = detected; as.position = pos;
+            LC3_SYNC; // dd is rewritten next frame
+        }
+
+        // ---- I. per-frame results, delay line for the next frame
+        LC3_LANES(l)
+            if (l < 24) sh.fir[l] = sh.s12[len + l];
+            if (l == 0) {
+                SV<i32> po = tile_view(b.pout, frame_tile(b, f, tile), PO_N, tl);
+                po[PO_LTPF_BITS] = ltpf_bits; po[PO_LTPF_IDX0] = lt0; po[PO_LTPF_IDX1] = lt1; po[PO_LTPF_IDX2] = lt2;
+                po[PO_ATTACK] = as.detected; po[PO_X_EXP] = x_exp;
+            }
+        LC3_LANES_END
+        LC3_LANES(l)
+            if (l < 24) sh.s12[l] = sh.fir[l];
+        LC3_LANES_END
+    }
+
+    // ---- store the state
+    LC3_LANES(l)
+        if (l < 24) s16[S16_MEM_OUT + l] = sh.s12[l];
+        if (l < 3) s16[S16_OLPA_S12 + l] = sh.m12[l];
+        for (int k = l; k < olpa_len; k += 32) s16[S16_OLPA_BUF + k] = sh.olpa[ob][k];
+        for (int k = l; k < lt_len; k += 32) s16[S16_LTPF_BUF + k] = sh.ltpf[lb][k];
+        if (l == 0) {
+            st[ST_MEM50_0] = m0; st[ST_MEM50_1] = m1;
+            st[ST_OLPA_EXP] = olpa_exp; st[ST_OLPA_PITCH] = olpa_pitch;
+            st[ST_LTPF_EXP] = ltpf_exp; st[ST_LTPF_NC] = ltpf_nc; st[ST_LTPF_MNC] = ltpf_mnc;
+            st[ST_LTPF_ON] = ltpf_on; st[ST_LTPF_PITCH] = ltpf_pitch_mem;
+            st[ST_ATT_F0] = as.filter_mem[0]; st[ST_ATT_F1] = as.filter_mem[1]; st[ST_ATT_DET] = as.detected;
+            st[ST_ATT_POS] = as.position; st[ST_ATT_SCAL] = as.scaling; st[ST_ATT_ACC] = as.acc_energy;
+            st[ST_X_EXP] = x_exp; st[ST_RESAMP_EXP] = resamp_exp;
+        }
+    LC3_LANES_END
+}
+
+} // namespace lc3k

@@ -1,0 +1,173 @@
+// Rate-loop pass, ONE WARP PER CHANNEL-STREAM (fx/enc_lc3.c:180-192): the second half of
+// processEstimateGlobalGain_fx (fx/estimate_global_gain_fx.c:44-59, :112-204) and the first quantisation
+// pass' bit count (fx/quantize_spec_fx.c:15-221), which feed targetBitsOff / mem_targetBits / mem_specBits
+// from one frame of a stream to the next.  Lanes split the quadruples, the bins and the 2-tuples.
+//
+// The context of a 2-tuple in the reference, c = ((c & 0xf) << 4) + t(previous tuple), is a pure function of
+// the two previous tuples' magnitudes class t (< 16), so all contexts and table look-ups of a frame are
+// computed in parallel and the bit count is one warp reduction (mode -1 needs no prefix sums).
+#pragma once
+#include "lc3_stages.cuh"
+#include "lc3_warp.cuh"
+#include "lc3_rate.cuh"
+
+namespace lc3k {
+
+struct RateShared {
+    WarpRed red;
+    i32 en[LC3K_MAX_N / 4];      // per-quadruple log-energies of the frame
+    i16 xq[LC3K_MAX_N];
+    u8 tv[LC3K_MAX_N / 2 + 2];   // magnitude class of each tuple, offset by 2 (tv[0] = tv[1] = 0)
+};
+
+LC3_HD void rate_warp_body(const LC3K_Batch &b, int li, RateShared &sh, const u8 *ari_lut, const uint16_t *ari_bitstab)
+{
+    if (li >= b.n_lanes) return;
+    const int tile = li >> 5, tl = li & 31;
+    const int slot = b.slot[li];
+    SV<i32> st = slot_view(b.st32, slot, ST32_N);
+    SV<const i32> cfg = slot_view(b.cfg, slot, CFG_N);
+    const i32 tbits_init = cfg[CFG_TBITS_INIT], total_bits = cfg[CFG_TOTAL_BITS], qgain_off = cfg[CFG_QGAIN_OFF];
+    i32 tbits_off = st[ST_TBITS_OFF], mem_tbits = st[ST_MEM_TBITS], mem_specbits = st[ST_MEM_SPECBITS];
+    const int nt = b.yLen, lg4 = nt >> 2, nt_half = nt >> 1;
+    const i32 rateFlag = s_sub(total_bits, s_add(160, s_imult(b.fs_idx, 160))) > 0 ? 2 << 8 : 0;
+
+    for (int f = 0; f < b.n_frames; f++) {
+        const size_t ft = frame_tile(b, f, tile);
+        SV<const i32> fo = tile_view((const i32 *)b.fout, ft, FO_N, tl);
+        SV<const i32> po = tile_view((const i32 *)b.pout, ft, PO_N, tl);
+        SV<const i32> d = tile_view((const i32 *)b.spec, ft, b.N, tl);
+        SV<const i32> en = tile_view((const i32 *)b.en4, ft, b.N / 4, tl);
+        const i32 x_e = fo[FO_D_EXP];
+        i32 x_max = fo[FO_X_MAX];
+        const i32 tbits_quant = s_sub(tbits_init, s_add(fo[FO_TNS_BITS], po[PO_LTPF_BITS]));
+
+        // ---- rate-loop feedback (estimate_global_gain_fx.c:44-59)
+        if (mem_tbits < 0) {
+            tbits_off = 0;
+        } else {
+            i32 t = l_add(tbits_off, l_dep_h(s_sub(mem_tbits, mem_specbits)));
+            t = l_min(40 << 16, l_max(-(40 << 16), t));
+            tbits_off = l_add(mpy32x16k(tbits_off, 26214), mpy32x16k(t, 6554));
+        }
+        mem_tbits = tbits_quant;
+        const i32 nbitsSQ = s_add(tbits_quant, l_round(tbits_off));
+
+        i32 qgain, qgain_min;
+        if (x_max == 0) {
+            qgain_min = qgain_off;
+            qgain = 0;
+            mem_tbits = -1;
+        } else {
+            x_max = l_add(m_log2(x_max), l_shl_p(x_e, 25));
+            x_max = l_sub(mpy32x32k(x_max, 0x436E439A), 0xFCDD6B4);
+            qgain_min = lo16(l_add(x_max, (1 << 21) + (1 << 11)) >> 21);
+            qgain_min = s_max(qgain_off, s_min(s_add(255, qgain_off), qgain_min));
+
+            // ---- bisection on the gain index (estimate_global_gain_fx.c:127-188): lane = quadruple.
+            // The reference walks the quadruples from the top with an "all zero so far" flag: a quadruple
+            // below the threshold costs 0x3C7AE only if a higher one is above it.  All terms are >= 0, so
+            // the saturating running sum equals the clamped total.
+            i32 offset = l_dep_h(s_add(255, qgain_off));
+            const i32 target = l_shl_p(l_mult(0x7D71, nbitsSQ), 1);
+            i32 fac = 0x1000000;
+            LC3_LANES(l)
+                for (int i = l; i < lg4; i += 32) sh.en[i] = en[i];
+            LC3_LANES_END
+            for (int it = 0; it < 8; it++) {
+                fac = fac >> 1;
+                offset = l_sub(offset, fac);
+                LC3_LANES(l)
+                    i32 top = -1;
+                    for (int i = l; i < lg4; i += 32)
+                        if (l_sub(sh.en[i], offset) >= 0x9CCCD) top = i;
+                    sh.red.a[l] = top;
+                LC3_LANES_END
+                const i32 top = warp_max(sh.red.a);
+                LC3_LANES(l)
+                    i64 est = 0;
+                    for (int i = l; i < lg4; i += 32) {
+                        const i32 t = l_sub(sh.en[i], offset);
+                        if (t < 0x9CCCD) { if (i < top) est += 0x3C7AE; }
+                        else { est += t; const i32 d2 = l_sub(t, 0x460000); if (d2 >= 0) est += d2; }
+                    }
+                    sh.red.q[l] = est;
+                LC3_LANES_END
+                const i32 est = clamp64(warp_sum64(sh.red.q));
+                if (est > target && top >= 0) offset = l_add(offset, fac);
+            }
+            const i32 g = hi16(offset);
+            if (g < qgain_min) mem_tbits = -1;
+            qgain = s_sub(s_max(qgain_min, g), qgain_off);
+        }
+        i32 gain, gain_e;
+        gain_from_index(s_add(qgain, qgain_off), gain, gain_e);
+
+        // ---- first quantisation pass, bit count only (quantize_spec_fx.c:53-221, mode -1): lane = bin, then tuple
+        i32 ge = gain_e;
+        const i32 inv = m_inv16(gain, &ge);
+        const i32 s = s_sub(s_add(x_e, ge), 15);
+        LC3_LANES(l)
+            i32 last = 0;
+            for (int i = l; i < nt; i += 32) {
+                const i32 q = quant_bin(d[i], inv, s);
+                sh.xq[i] = (i16)q;
+                if (q != 0 && i >= 2) last = (i | 1) + 1; // find_last_nz_pair: pairs below bin 2 are not looked at
+            }
+            sh.red.a[l] = last;
+            if (l < 2) sh.tv[l] = 0;
+        LC3_LANES_END
+        const i32 lastnz = imax(warp_max(sh.red.a), 2);
+        LC3_LANES(l) // magnitude class of every tuple (the value the reference folds into the next context)
+            for (int k = 2 * l; k < lastnz; k += 64) {
+                const i32 a1 = s_abs(sh.xq[k]), b1 = s_abs(sh.xq[k + 1]), mx = imax(a1, b1);
+                i32 t;
+                if (mx == 0) t = 1;
+                else if (mx < 4) t = a1 + b1 + 1;
+                else if (mx < 8) t = 2 * ((a1 >> 1) + (b1 >> 1)) + 1;
+                else t = 12 + imin(13 - s_norm(mx), 3);
+                sh.tv[2 + (k >> 1)] = (u8)t;
+            }
+        LC3_LANES_END
+        LC3_LANES(l)
+            i32 nb = 0;
+            for (int k = 2 * l; k < lastnz; k += 64) {
+                const int j = k >> 1;
+                i32 t = ((i32)sh.tv[j] << 4) + sh.tv[j + 1] + rateFlag; // tv[j] = class of tuple j-2, tv[j+1] = of j-1
+                if (k > nt_half) t += 1 << 8;
+                const i32 a1 = s_abs(sh.xq[k]), b1 = s_abs(sh.xq[k + 1]), mx = imax(a1, b1);
+                if (mx == 0) { nb += ari_bits(ari_lut, ari_bitstab, t, 0); continue; }
+                i32 lev, am, bm;
+                if (mx < 4) {
+                    lev = 0; am = a1; bm = b1;
+                } else if (mx < 8) {
+                    lev = 1; am = a1 >> 1; bm = b1 >> 1;
+                    nb += ari_bits(ari_lut, ari_bitstab, t, 16) + (2 << 11);
+                } else {
+                    lev = 13 - s_norm(mx);
+                    for (int q = 0; q < lev; q++) nb += ari_bits(ari_lut, ari_bitstab, t + rom_ari_esc_nb[q < 3 ? q : 3], 16);
+                    nb += lev << 12;
+                    am = a1 >> lev; bm = b1 >> lev;
+                }
+                nb += ari_bits(ari_lut, ari_bitstab, t + (lev ? rom_ari_esc_nb[lev < 3 ? lev : 3] : 0), am + (bm << 2));
+                nb += ((a1 != 0) + (b1 != 0)) << 11;
+            }
+            sh.red.a[l] = nb;
+        LC3_LANES_END
+        const i32 nbq = warp_sum(sh.red.a); // Q11 bits; a frame holds < 2^15 bits, so no 32-bit overflow
+        const i32 nBits = s_add(lo16((nbq - 1) >> 11), 1);
+        mem_specbits = nBits;
+
+        LC3_LANES(l)
+            if (l == 0) {
+                SV<i32> ro = tile_view(b.rout, ft, RO_N, tl);
+                ro[RO_QGAIN] = qgain; ro[RO_QGAIN_MIN] = qgain_min; ro[RO_NBITS1] = nBits; ro[RO_TBITS_QUANT] = tbits_quant;
+            }
+        LC3_LANES_END
+    }
+    LC3_LANES(l)
+        if (l == 0) { st[ST_TBITS_OFF] = tbits_off; st[ST_MEM_TBITS] = mem_tbits; st[ST_MEM_SPECBITS] = mem_specbits; }
+    LC3_LANES_END
+}
+
+} // namespace lc3k

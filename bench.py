@@ -41,6 +41,23 @@ WORKLOAD = "4096 independent 48 kHz mono streams, 10 ms frames, 128 kbps, per GP
 
 
 def clock_sampler(stop, rows, dev):
+    """SM clock and throttle reasons during the timed region, sampled in-process through NVML (spawning
+    nvidia-smi next to the timed loop stalls kernel launches for hundreds of ms)."""
+    try:
+        import pynvml as nv
+        nv.nvmlInit()
+        h = nv.nvmlDeviceGetHandleByIndex(dev)
+        mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+        R = {"hw_slowdown": nv.nvmlClocksThrottleReasonHwSlowdown, "hw_thermal_slowdown": nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+             "sw_thermal_slowdown": nv.nvmlClocksThrottleReasonSwThermalSlowdown, "sw_power_cap": nv.nvmlClocksThrottleReasonSwPowerCap}
+        while not stop.is_set():
+            bits = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+            rows.append([str(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)), str(mx)] +
+                        ["Active" if bits & R[k] else "Not Active" for k in ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")])
+            stop.wait(0.05)
+        return
+    except Exception:
+        pass
     q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
     while not stop.is_set():
@@ -50,7 +67,7 @@ def clock_sampler(stop, rows, dev):
             rows.append([x.strip() for x in o])
         except Exception:
             pass
-        stop.wait(0.2)
+        stop.wait(0.5)
 
 
 def summarize_clocks(rows):

@@ -9,6 +9,8 @@ extern "C" {
 }
 #include "lc3_body_serial.cuh"
 #include "lc3_body_frame.cuh"
+#include "lc3_pitch_warp.cuh"
+#include "lc3_rate_warp.cuh"
 
 using namespace lc3k;
 
@@ -116,17 +118,34 @@ extern "C" int hostsim_encode(void *p, const void *pcm, int bits, int n_frames, 
         }
     }
     AriTabs T = {(const u8 *)rom_ari_lookup, rom_ari_cumfreq, rom_ari_freq};
-    for (int tile = 0; tile < b.n_tiles; tile++)
-        for (int lane = 0; lane < 32; lane++) {
-            if (bits == 16) pitch_body<16>(b, tile, lane); else pitch_body<24>(b, tile, lane);
+    static PitchShared psh;
+    static RateShared rsh;
+    const bool lane_serial = getenv("HOSTSIM_LANE_SERIAL") != 0; // older one-lane-per-stream bodies, kept for debugging
+    b.pcm = pcm;
+    std::vector<int64_t> pcm_off(s->n_streams);
+    for (int i = 0; i < s->n_streams; i++) pcm_off[i] = (int64_t)i * n_frames * N;
+    b.pcm_off = pcm_off.data();
+    if (lane_serial) {
+        for (int tile = 0; tile < b.n_tiles; tile++)
+            for (int lane = 0; lane < 32; lane++) {
+                if (bits == 16) pitch_body<16>(b, tile, lane); else pitch_body<24>(b, tile, lane);
+            }
+    } else {
+        for (int li = 0; li < b.n_lanes; li++) {
+            if (bits == 16) pitch_warp_body<16>(b, li, psh); else pitch_warp_body<24>(b, li, psh);
         }
+    }
     for (int f = 0; f < n_frames; f++)
         for (int tile = 0; tile < b.n_tiles; tile++)
             for (int lane = 0; lane < 32; lane++) {
                 if (bits == 16) run_front<16>(b, f, tile, lane); else run_front<24>(b, f, tile, lane);
             }
-    for (int tile = 0; tile < b.n_tiles; tile++)
-        for (int lane = 0; lane < 32; lane++) rate_body(b, tile, lane, (const u8 *)rom_ari_lookup, rom_ari_bits);
+    if (lane_serial) {
+        for (int tile = 0; tile < b.n_tiles; tile++)
+            for (int lane = 0; lane < 32; lane++) rate_body(b, tile, lane, (const u8 *)rom_ari_lookup, rom_ari_bits);
+    } else {
+        for (int li = 0; li < b.n_lanes; li++) rate_warp_body(b, li, rsh, (const u8 *)rom_ari_lookup, rom_ari_bits);
+    }
     for (int f = 0; f < n_frames; f++)
         for (int tile = 0; tile < b.n_tiles; tile++)
             for (int lane = 0; lane < 32; lane++) back_body(b, f, tile, lane, T, rom_ari_bits);
