@@ -114,6 +114,8 @@ LC3_HD i32 l_shl_p(i32 a, i32 n)
     i32 r = (i32)((u32)a << n);
     return (r >> n) != a ? ((a >> 31) ^ LC3_I32_MAX) : r;
 }
+// L_shl for a count known not to exceed the headroom of a (norm_l(a) >= n): no saturation test
+LC3_HD i32 l_shl_ns(i32 a, i32 n) { return n >= 0 ? (i32)((u32)a << n) : a >> imin(-n, 31); }
 LC3_HD i32 l_shl(i32 a, i32 n) { return n <= 0 ? l_shr_p(a, n < -32 ? 32 : -n) : l_shl_p(a, n); }
 LC3_HD i32 l_shr(i32 a, i32 n) { return n < 0 ? l_shl_p(a, n < -32 ? 32 : -n) : l_shr_p(a, n); }
 LC3_HD i32 l_norm(i32 a) { return a == 0 ? 0 : clz32((u32)(a ^ (a >> 31))) - 1; }

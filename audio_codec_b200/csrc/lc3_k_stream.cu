@@ -1,0 +1,114 @@
+// sm_100a kernels of the batched LC3plus encoder and their launchers (C ABI towards lc3_api.c), part: staging, per-stream time-domain pass, per-stream rate-loop pass, state reset.
+//
+// Thread mapping: frame-parallel passes run one lane per channel-frame (32 lanes of a warp = the same 32
+// channel-streams of a tile at one frame index); per-stream passes run one warp per channel-stream.  Every
+// per-lane array access with a warp-uniform index is one coalesced request into the tile-interleaved
+// buffers (lc3_layout.h).  No tensor cores: the arithmetic is saturating 16/32-bit fixed point.
+#include <cuda_runtime.h>
+#include "lc3_body_frame.cuh"
+#include "lc3_pitch_warp.cuh"
+#include "lc3_rate_warp.cuh"
+
+using namespace lc3k;
+
+// ---- staging: caller's PCM (sample-major per stream) -> tile-interleaved, history frame first.
+// grid = (tiles, segments of STAGE_SEG samples); 32 lanes x 32 samples per step through shared memory.
+#define STAGE_SEG 1024
+template <class T> __global__ void __launch_bounds__(256) k_stage(LC3K_Batch b)
+{
+    __shared__ T sm[32][33];
+    const int tile = blockIdx.x, tx = threadIdx.x & 31, ty = threadIdx.x >> 5; // 32 x 8
+    const int N = b.N, total = b.n_frames * N;
+    const size_t per_tile = (size_t)(b.n_frames + 1) * N;
+    T *dst = (T *)b.pcm_t + (size_t)tile * per_tile * LC3K_LANES;
+    const T *src = (const T *)b.pcm + (size_t)b.frame0 * N;
+
+    if (blockIdx.y == 0) { // history prefix from the state, then the new history = last frame of the chunk (lane = tx)
+        T *hist_pool = sizeof(T) == 2 ? (T *)b.hist16 : (T *)b.hist32;
+        const int li = tile * 32 + tx;
+        if (li < b.n_lanes) {
+            SV<T> h = slot_view(hist_pool, b.slot[li], LC3K_MAX_N);
+            const T *last = src + b.pcm_off[li] + (total - N);
+            for (int i = ty; i < N; i += 8) { dst[(size_t)i * 32 + tx] = h[i]; h[i] = last[i]; }
+        }
+    }
+    const int c_end = min(total, (int)(blockIdx.y + 1) * STAGE_SEG);
+    for (int c0 = blockIdx.y * STAGE_SEG; c0 < c_end; c0 += 32) {
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            const int lane = ty + 8 * r, li = tile * 32 + lane, i = c0 + tx;
+            T v = 0;
+            if (li < b.n_lanes && i < total) v = src[b.pcm_off[li] + i];
+            sm[lane][tx] = v;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            const int k = ty + 8 * r, i = c0 + k;
+            if (i < total) dst[(size_t)(N + i) * 32 + tx] = sm[tx][k];
+        }
+        __syncthreads();
+    }
+}
+
+// per-stream passes: one warp per channel-stream, 4 streams per block
+template <int BITS> __global__ void __launch_bounds__(128, 4) k_pitch(LC3K_Batch b)
+{
+    __shared__ PitchShared sh[4];
+    const int w = threadIdx.x >> 5;
+    pitch_warp_body<BITS>(b, blockIdx.x * 4 + w, sh[w]);
+}
+
+__global__ void __launch_bounds__(128) k_rate(LC3K_Batch b)
+{
+    __shared__ RateShared sh[4];
+    __shared__ u8 lut[4096];
+    __shared__ uint16_t bits[1088];
+    for (int i = threadIdx.x; i < 4096; i += 128) lut[i] = (u8)rom_ari_lookup[i];
+    for (int i = threadIdx.x; i < 1088; i += 128) bits[i] = rom_ari_bits[i];
+    __syncthreads();
+    const int w = threadIdx.x >> 5;
+    rate_warp_body(b, blockIdx.x * 4 + w, sh[w], lut, bits);
+}
+
+__global__ void k_reset(i32 *st32, i16 *st16, i16 *hist16, i32 *hist32, const i32 *slots, int n)
+{
+    const int k = blockIdx.x;
+    if (k >= n) return;
+    const int slot = slots[k];
+    SV<i32> a = slot_view(st32, slot, ST32_N);
+    SV<i16> c = slot_view(st16, slot, ST16_N);
+    SV<i16> h = slot_view(hist16, slot, LC3K_MAX_N);
+    SV<i32> g = slot_view(hist32, slot, LC3K_MAX_N);
+    for (int i = threadIdx.x; i < ST32_N; i += blockDim.x) a[i] = i == ST_X_EXP ? 15 : (i == ST_RESAMP_EXP ? 17 : 0);
+    for (int i = threadIdx.x; i < ST16_N; i += blockDim.x) c[i] = 0;
+    for (int i = threadIdx.x; i < LC3K_MAX_N; i += blockDim.x) { h[i] = 0; g[i] = 0; }
+}
+
+static int done() { return (int)cudaGetLastError(); }
+
+extern "C" int lc3k_launch_reset(int32_t *st32, int16_t *st16, int16_t *hist16, int32_t *hist32, const int32_t *slots, int n, void *stream)
+{
+    if (n <= 0) return 0;
+    k_reset<<<n, 64, 0, (cudaStream_t)stream>>>(st32, st16, hist16, hist32, slots, n);
+    return done();
+}
+extern "C" int lc3k_launch_stage(const LC3K_Batch *b, void *stream)
+{
+    const dim3 grid(b->n_tiles, (b->n_frames * b->N + STAGE_SEG - 1) / STAGE_SEG);
+    if (b->bits == 16) k_stage<int16_t><<<grid, 256, 0, (cudaStream_t)stream>>>(*b);
+    else k_stage<int32_t><<<grid, 256, 0, (cudaStream_t)stream>>>(*b);
+    return done();
+}
+extern "C" int lc3k_launch_pitch(const LC3K_Batch *b, void *stream)
+{
+    const int blocks = (b->n_lanes + 3) / 4;
+    if (b->bits == 16) k_pitch<16><<<blocks, 128, 0, (cudaStream_t)stream>>>(*b);
+    else k_pitch<24><<<blocks, 128, 0, (cudaStream_t)stream>>>(*b);
+    return done();
+}
+extern "C" int lc3k_launch_rate(const LC3K_Batch *b, void *stream)
+{
+    k_rate<<<(b->n_lanes + 3) / 4, 128, 0, (cudaStream_t)stream>>>(*b);
+    return done();
+}

@@ -8,10 +8,12 @@
 namespace lc3k {
 
 // (a + jb)(c + jd), every product halved before the add (cplxMpy32_32_16_2, fx/basop_mpy.h:45-50)
+// The twiddle tables hold no -32768 (tests/test_rom_bounds.py), so each halved product is below 2^30 in
+// magnitude: neither Mpy_32_16's -1 x -1 case nor the L_add/L_sub saturation of the reference can trigger.
 LC3_HD void cmul_half(i32 &re, i32 &im, i32 a, i32 b, i32 c, i32 d)
 {
-    re = l_sub(mpy32x16(a, c) >> 1, mpy32x16(b, d) >> 1);
-    im = l_add(mpy32x16(a, d) >> 1, mpy32x16(b, c) >> 1);
+    re = (mpy32x16k(a, c) >> 1) - (mpy32x16k(b, d) >> 1);
+    im = (mpy32x16k(a, d) >> 1) + (mpy32x16k(b, c) >> 1);
 }
 
 template <int L> struct TwSlot {
@@ -25,18 +27,20 @@ LC3_HD i32 mdct_frame(XS xs, i32 x_exp, const i16 *win, int wLen, int memLen, A 
 {
     constexpr int m = N >> 1;
     const int z = 2 * N - wLen;
+    // |x| <= 2^15 and |w| <= 32767 (no -32768 in the window ROM): a sum of two products stays below 2^31, so the
+    // reference's L_mac0/L_msu0 cannot saturate here
     Range rg; range_init(rg);
     int i;
     for (i = 0; i < m; i++) {
-        i32 v = l_msu0(l_mult0(xs(i - memLen), win[i]), xs(2 * m - 1 - i - memLen), win[2 * m - 1 - i]);
+        i32 v = xs(i - memLen) * win[i] - xs(2 * m - 1 - i - memLen) * win[2 * m - 1 - i];
         y[m + i] = v; range_add(rg, v);
     }
     for (i = 0; i < z; i++) {
-        i32 v = l_mult0(xs(2 * m - memLen + i), win[2 * m + i]);
+        i32 v = xs(2 * m - memLen + i) * win[2 * m + i];
         y[m - 1 - i] = v; range_add(rg, v);
     }
     for (; i < m; i++) {
-        i32 v = l_mac0(l_mult0(xs(2 * m - memLen + i), win[2 * m + i]), xs(4 * m - memLen - 1 - i), win[4 * m - 1 - i]);
+        i32 v = xs(2 * m - memLen + i) * win[2 * m + i] + xs(4 * m - memLen - 1 - i) * win[4 * m - 1 - i];
         y[m - 1 - i] = v; range_add(rg, v);
     }
     const i32 s = imax(0, range_headroom32(rg, 0));
@@ -51,7 +55,8 @@ LC3_HD i32 mdct_frame(XS xs, i32 x_exp, const i16 *win, int wLen, int memLen, A 
     constexpr int step = (N % 3 == 0) ? 960 / N : 640 / N;
     i32 a1, a2, a3, a4;
     for (int k = 0, lo = 0, hi = N - 2; k < M - 1; k += 2, lo += 2, hi -= 2) {
-        i32 p0 = l_shl_p(y[lo], s), p1 = l_shl_p(y[lo + 1], s), q0 = l_shl_p(y[hi], s), q1 = l_shl_p(y[hi + 1], s);
+        // s is the block headroom: the shift cannot overflow
+        i32 p0 = (i32)((u32)y[lo] << s), p1 = (i32)((u32)y[lo + 1] << s), q0 = (i32)((u32)y[hi] << s), q1 = (i32)((u32)y[hi + 1] << s);
         cmul_half(a1, a2, q1, p0, tw[2 * k], tw[2 * k + 1]);
         cmul_half(a3, a4, q0, p1, tw[2 * k + 2], tw[2 * k + 3]);
         y[lo] = a2; y[lo + 1] = a1;

@@ -141,11 +141,10 @@ template <int BITS> LC3_HD void pitch_warp_body(const LC3K_Batch &b, int li, Pit
             for (int n = l; n < len; n += 32) {
                 const int t = n * off_frac, ii = 1 + n * off_int + t / upfac - rl, fr = t % upfac;
                 const i16 *co = &sh.filt[fr * delay2], *in = &sh.xs[64 + ii];
-                i32 acc = l_mult0(in[0], co[0]);
-                for (int m = 1; m < delay2; m++) {
-                    i32 c = co[m];
-                    if (c) acc = l_mac0(acc, in[m], c);
-                }
+                // the reference's saturating L_mac0 chain cannot saturate: sum |taps| <= 56970 < 2^16 for every
+                // phase of every rate (checked against the ROM in tests/test_rom_bounds.py), |x| <= 2^15
+                i32 acc = 0;
+                for (int m = 0; m < delay2; m++) acc += in[m] * co[m];
                 sh.fir[n] = (i16)l_round(acc);
             }
         LC3_LANES_END
@@ -211,8 +210,8 @@ template <int BITS> LC3_HD void pitch_warp_body(const LC3K_Batch &b, int li, Pit
             LC3_LANES(l)
                 i64 kw = LC3_I32_MIN * (i64)4294967296LL, k2 = kw;
                 for (int n = 17 + l; n <= 114; n += 32) {
-                    i32 acc = l_mult0(s[0], s[-n]);
-                    for (int m = 1; m < acflen6; m++) acc = l_mac0(acc, s[m], s[m - n]);
+                    i32 acc = 0; // <= 80 products of |v| <= 2^12 operands: below 2^31, the L_mac0 chain cannot saturate
+                    for (int m = 0; m < acflen6; m++) acc += s[m] * s[m - n];
                     const i64 a = argmax_key(mpy32x16(acc, rom_olpa_weight[n - 17]), n);
                     kw = a > kw ? a : kw;
                     if (n >= lo && n <= hi) { const i64 c = argmax_key(acc, n); k2 = c > k2 ? c : k2; }
@@ -299,8 +298,11 @@ template <int BITS> LC3_HD void pitch_warp_body(const LC3K_Batch &b, int li, Pit
                 LC3_LANES(l) // lane = candidate lag: cross-correlation, sliding lagged energy, normalisation
                     if (l < nlags) {
                         const int n = ac_lo + l;
-                        i32 s0 = l_mac0(0, xp[0], xp[-n]);
-                        for (int m = 1; m < acflen; m++) s0 = l_mac0(s0, xp[m], xp[m - n]);
+                        // <= 128 products of |v| <= 2^12 operands: only the last term can reach +-2^31, so the
+                        // saturating chain equals the clamped exact sum
+                        i64 s64 = 0;
+                        for (int m = 0; m < acflen; m++) s64 += (i64)xp[m] * xp[m - n];
+                        const i32 s0 = clamp64(s64);
                         i32 s2 = sum2_0;
                         for (int q = ac_lo + 1; q <= n; q++) { // slide the window one sample per lag (ltpf_coder_fx.c:116-120)
                             const i32 o = xp[acflen - 1 - (q - 1)], w = xp[-q];

@@ -31,12 +31,14 @@ template <class A, class E> LC3_HD i32 gain_energies(A x, i32 x_e, int lg, E en)
         i32 m = l_max(l_max(l_abs(v0), l_abs(v1)), l_max(l_abs(v2), l_abs(v3)));
         x_max = l_max(x_max, m);
         i32 s = m != 0 ? l_norm(m) : 31;
-        s = s_sub(s, 2);
+        s = s - 2;
+        // the shift leaves 2 bits of headroom, the rounded values are below 2^13 and 1 + 4 * 2 * t^2 < 2^29:
+        // none of the reference's saturating operators (L_shl, round_fx, L_mac) can saturate here
         i32 e = 1, t;
-        t = l_round(l_shl(v0, s)); e = l_mac(e, t, t);
-        t = l_round(l_shl(v1, s)); e = l_mac(e, t, t);
-        t = l_round(l_shl(v2, s)); e = l_mac(e, t, t);
-        t = l_round(l_shl(v3, s)); e = l_mac(e, t, t);
+        t = (l_shl_ns(v0, s) + 0x8000) >> 16; e += 2 * t * t;
+        t = (l_shl_ns(v1, s) + 0x8000) >> 16; e += 2 * t * t;
+        t = (l_shl_ns(v2, s) + 0x8000) >> 16; e += 2 * t * t;
+        t = (l_shl_ns(v3, s) + 0x8000) >> 16; e += 2 * t * t;
         s = s_shl(s_sub(x_e, s), 1);
         if (e == 1 && s < 0) s = 0;
         t = l_add(m_log2(e), l_shl_p(s, 25) );

@@ -95,12 +95,13 @@ LC3_HD int cb_search(const i16 *t, const i16 *cb)
     int best = 0;
     i32 bmse = 0;
     for (int r = 0; r < 32; r++) {
-        i32 mse = 0;
+        i64 acc = 0; // squares are non-negative: the saturating L_mac0 chain equals the clamped exact sum
 #pragma unroll
         for (int c = 0; c < 8; c++) {
             i32 e = s_sub(cb[r * 8 + c], t[c]);
-            mse = l_mac0(mse, e, e);
+            acc += (i64)e * e;
         }
+        const i32 mse = acc > LC3_I32_MAX ? LC3_I32_MAX : (i32)acc;
         if (r == 0 || mse < bmse) { bmse = mse; best = r; }
     }
     return best;
@@ -441,7 +442,8 @@ template <class A> LC3_HD void mdct_shape(A d, const i16 *g, const i16 *g_exp, c
     int j = 0;
     for (int b = 0; b < nbands; b++) {
         const i32 gg = g[b], ge = g_exp[b];
-        for (; j < bo[b + 1]; j++) d[j] = l_shl(mpy32x16(d[j], gg), ge);
+        const int stop = bo[b + 1];
+        for (; j < stop; j++) d[j] = l_shl(mpy32x16k(d[j], gg), ge); // gg > 0 (2^x mantissa)
     }
 }
 

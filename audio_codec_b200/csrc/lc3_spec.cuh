@@ -5,7 +5,8 @@
 
 namespace lc3k {
 
-LC3_HD i32 sq_hi(i32 v, i32 sh) { i32 t = hi16(l_shl(v, sh)); return l_mult0(t, t); }
+// sh never exceeds the headroom of v at the call sites (it is a minimum of norm_l values), so L_shl cannot saturate
+LC3_HD i32 sq_hi(i32 v, i32 sh) { i32 t = hi16(l_shl_ns(v, sh)); return t * t; }
 LC3_HD i32 hr15(i32 v, i32 cur) { return v != 0 ? imin(cur, l_norm(v)) : cur; }
 
 // en[0..nbands) mantissas on the common exponent returned.  bo: bands_offset table of this config.
@@ -41,7 +42,7 @@ template <class A> LC3_HD i32 band_energy(i32 *en, A d, i32 d_exp, const i16 *bo
             i32 v0 = d[i], v1 = d[i + 1];
             i32 s2 = hr15(v1, hr15(v0, 15));
             i32 a = imin(sq_hi(v0, s2), 0x3FFFFFFF);
-            i32 t = hi16(l_shl(v1, s2));
+            i32 t = hi16(l_shl_ns(v1, s2));
             en[band] = l_mac0(a, t, t) >> 1;
             e = s_sub(1, s_shl(s2, 1));
         }
@@ -54,11 +55,12 @@ template <class A> LC3_HD i32 band_energy(i32 *en, A d, i32 d_exp, const i16 *bo
         int w = bo[band + 1] - bo[band];
         w = w < 0 ? 0 : (w > 31 ? 31 : w);
         i32 s2 = s_sub(s1, rom_bands_nrg_scale[w]);
-        i32 a = 0;
+        i64 a64 = 0; // non-negative terms: the saturating L_mac0 chain equals the clamped exact sum
         for (; i < stop; i++) {
-            i32 t = hi16(l_shl(d[i], s2));
-            a = l_mac0(a, t, t);
+            i32 t = hi16(l_shl_ns(d[i], s2));
+            a64 += (i64)t * t;
         }
+        i32 a = a64 > LC3_I32_MAX ? LC3_I32_MAX : (i32)a64;
         i = bo[band + 1];
         a = mpy32x16(a, rom_inv_int[w]);
         i32 s = l_norm(a);

@@ -95,8 +95,8 @@ template <int MAXORD, class A> LC3_HD void tns_coder(TnsOut &o, A x, int bw, int
             i32 sh = headroom, nrg = 0;
             for (int i = 0; i < n; i++) {
                 if (nrg >= 0x40000000) { sh = s_sub(sh, 1); nrg = nrg >> 2; }
-                i32 t = l_round(l_shl(x[lo + i], sh));
-                nrg = l_mac0(nrg, t, t);
+                i32 t = l_round(l_shl_ns(x[lo + i], sh)); // sh <= block headroom
+                nrg += t * t;                             // nrg < 2^30 here and t^2 <= 2^30: L_mac0 cannot saturate
             }
             if (nrg != 0) {
                 i32 s = s_norm(n);
@@ -123,16 +123,34 @@ template <int MAXORD, class A> LC3_HD void tns_coder(TnsOut &o, A x, int bw, int
             const i32 facs = s_div(0x2000, l_round(nrg));
 
             // autocorrelation lags 0..MAXORD of the block-scaled bins, sliding window in registers
+            // |partial sum of v[i] v[i-l]| <= sum v^2, so if the lag-0 energy fits 32 bits no L_mac0 of any lag can
+            // have saturated and plain arithmetic is exact; otherwise redo the block with the saturating operators
             i32 acc[MAXORD + 1], hist[MAXORD + 1];
+            i64 e0 = 0;
 #pragma unroll
             for (int l = 0; l <= MAXORD; l++) { acc[l] = 0; hist[l] = 0; }
             for (int i = 0; i < n; i++) {
-                i32 v = l_round(l_shl(x[lo + i], shifts));
+                i32 v = l_round(l_shl_ns(x[lo + i], shifts)); // shifts <= block headroom
 #pragma unroll
                 for (int l = MAXORD; l > 0; l--) hist[l] = hist[l - 1];
                 hist[0] = v;
+                e0 += (i64)v * v;
 #pragma unroll
-                for (int l = 0; l <= MAXORD; l++) acc[l] = l_mac0(acc[l], hist[l], v);
+                for (int l = 1; l <= MAXORD; l++) acc[l] += hist[l] * v;
+            }
+            if (e0 <= LC3_I32_MAX) {
+                acc[0] = (i32)e0;
+            } else {
+#pragma unroll
+                for (int l = 0; l <= MAXORD; l++) { acc[l] = 0; hist[l] = 0; }
+                for (int i = 0; i < n; i++) {
+                    i32 v = l_round(l_shl_ns(x[lo + i], shifts));
+#pragma unroll
+                    for (int l = MAXORD; l > 0; l--) hist[l] = hist[l - 1];
+                    hist[0] = v;
+#pragma unroll
+                    for (int l = 0; l <= MAXORD; l++) acc[l] = l_mac0(acc[l], hist[l], v);
+                }
             }
 #pragma unroll
             for (int lag = 0; lag <= MAXORD; lag++) {

@@ -42,3 +42,26 @@ def make_streams_fast(n_streams, n_samples, fs, frame_len, bits=16, n_unique=64)
     for i in range(n_streams):
         out[i] = np.roll(base[i % base.shape[0]], (i // base.shape[0]) * 97)
     return out
+
+
+def make_torture(n_samples, fs, bits=16, seed=7):
+    """Adversarial streams for the saturation / headroom paths: [10, n_samples].
+    full-scale noise, full-scale square, Nyquist alternation, negative-rail DC, sparse impulses, silence then
+    a full-scale step, +-1 LSB noise, full-scale chirp, full-scale low sine, clipped sum of tones."""
+    full = 32767 if bits == 16 else 8388607
+    lo = -full - 1
+    rng = np.random.RandomState(seed)
+    t = np.arange(n_samples, dtype=np.float64) / fs
+    x = np.zeros((10, n_samples), dtype=np.float64)
+    x[0] = rng.randint(lo, full + 1, n_samples)
+    x[1] = np.where((np.arange(n_samples) // 37) % 2 == 0, full, lo)
+    x[2] = np.where(np.arange(n_samples) % 2 == 0, full, lo)
+    x[3] = lo
+    x[4, ::211] = full
+    x[4, 100::503] = lo
+    x[5, n_samples // 3:] = full
+    x[6] = rng.randint(-1, 2, n_samples)
+    x[7] = full * np.sin(2 * np.pi * (50 + 0.45 * fs * t / max(t[-1], 1e-9) / 2) * t)
+    x[8] = full * np.sin(2 * np.pi * 60 * t)
+    x[9] = np.clip(3.0 * full * (np.sin(2 * np.pi * 440 * t) + np.sin(2 * np.pi * 3000 * t)), lo, full)
+    return np.clip(np.round(x), lo, full).astype(np.int16 if bits == 16 else np.int32)

@@ -4,7 +4,7 @@ import numpy as np
 import pytest
 
 import lc3ref
-from audio_codec_b200.synth import make_streams, make_streams_fast
+from audio_codec_b200.synth import make_streams, make_streams_fast, make_torture
 
 pytestmark = pytest.mark.gpu
 
@@ -173,3 +173,18 @@ def test_error_codes():
     assert e.set_bitrate(32000) == 0
     assert e.set_frame_dms(50) == 15                  # LC3_BITRATE_SET_ERROR (fx/lc3.c:219)
     assert e.num_bytes == 40 and e.frame_len == 160 and e.delay == 160 - 2 * 60
+
+
+@pytest.mark.parametrize("fs,dms,br,bits", [(48000, 100, 128000, 16), (48000, 100, 320000, 24), (16000, 50, 32000, 16),
+                                            (48000, 25, 256000, 16), (32000, 100, 64000, 16), (8000, 100, 16000, 24),
+                                            (24000, 25, 96000, 24), (44100, 100, 160000, 16)])
+def test_adversarial_signals(fs, dms, br, bits):
+    """Rail-to-rail noise, squares, DC, impulses, steps: the inputs that reach the saturating operators."""
+    import audio_codec_b200 as ac
+    N, nf = _frame_len(fs, dms), 20
+    pcm = make_torture(nf * N, fs, bits)[:, None, :]
+    encs = [ac.Encoder(fs, 1, dms, br) for _ in range(pcm.shape[0])]
+    out = _batch(ac, encs, nf, pcm, bits)
+    for s in range(pcm.shape[0]):
+        want = _oracle(fs, 1, dms, br, bits, pcm[s])
+        assert np.array_equal(out[s, :, :want.shape[1]], want), f"stream {s}"

@@ -10,7 +10,7 @@ import pytest
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.join(HERE, "hostsim"))
 import run as hs  # noqa: E402
-from audio_codec_b200.synth import make_streams  # noqa: E402
+from audio_codec_b200.synth import make_streams, make_torture  # noqa: E402
 
 CASES = [(48000, 100, 128000, 16), (16000, 50, 32000, 16), (48000, 25, 128000, 16), (8000, 100, 16000, 16),
          (24000, 50, 48000, 24), (32000, 100, 80000, 16), (44100, 100, 96000, 16), (8000, 25, 64000, 16),
@@ -71,3 +71,17 @@ def test_host_config_matches_reference_getters(L):
                     if r0 == 0:
                         assert ref.num_bytes == L.lc3cfg_num_bytes(C.byref(c))
                         assert R.lc3_enc_get_real_bitrate(ref.h) == L.lc3cfg_real_bitrate(C.byref(c))
+
+
+@pytest.mark.parametrize("fs,dms,br,bits", [(48000, 100, 128000, 16), (48000, 100, 320000, 24), (16000, 50, 32000, 16),
+                                            (48000, 25, 256000, 16), (32000, 100, 64000, 16), (8000, 100, 16000, 24),
+                                            (24000, 25, 96000, 24), (44100, 100, 160000, 16)])
+def test_bodies_equal_oracle_on_adversarial_signals(L, fs, dms, br, bits):
+    """Rail-to-rail noise, squares, DC, impulses, steps: the inputs that reach the saturating operators."""
+    N = (48000 if fs == 44100 else fs) // 100 * dms // 100
+    nf = 14
+    pcm = make_torture(nf * N, fs, bits)
+    a = hs.sim_encode(L, fs, dms, [(br, nf)], pcm, bits)[0]
+    b = hs.oracle_encode(fs, dms, [(br, nf)], pcm, bits)[0]
+    bad = np.argwhere((a != b).any(2))
+    assert len(bad) == 0, f"first mismatch (stream, frame) = {bad[0]}"

@@ -11,7 +11,7 @@ import numpy as np
 import pytest
 
 import lc3ref
-from audio_codec_b200.synth import make_streams
+from audio_codec_b200.synth import make_streams, make_torture
 
 ETSI = "/root/reference/LC3plus_ETSI_src_v17171_20200723"
 needs_ref = pytest.mark.skipif(not (lc3ref.have_ref() and os.path.isdir(ETSI)), reason="reference tree absent")
@@ -96,3 +96,15 @@ def test_oracle_error_codes():
         assert ref.set_bitrate(br) == ora.set_bitrate(br), br
     assert R.lc3_enc_set_frame_dms(ref.h, 50) == O.lc3o_enc_set_frame_dms(ora.h, 50) == 15
     assert O.lc3o_enc_set_frame_dms(ora.h, 30) == 10
+
+
+@needs_ref
+@pytest.mark.parametrize("fs,dms,br,bits", [(48000, 100, 128000, 16), (48000, 100, 320000, 24), (16000, 50, 32000, 16),
+                                            (48000, 25, 256000, 16), (32000, 100, 64000, 16), (8000, 100, 16000, 24)])
+def test_oracle_equals_reference_on_adversarial_signals(fs, dms, br, bits):
+    N = (48000 if fs == 44100 else fs) // 100 * dms // 100
+    pcm = make_torture(20 * N, fs, bits)
+    for s in range(pcm.shape[0]):
+        a = lc3ref.RefEnc(fs, 1, dms, br).encode(pcm[s:s + 1], bits)
+        b = lc3ref.OracleEnc(fs, 1, dms, br).encode(pcm[s:s + 1], bits)
+        assert np.array_equal(a, b), f"stream {s}: first differing frame {np.nonzero((a != b).any(1))[0][:1]}"

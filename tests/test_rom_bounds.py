@@ -1,0 +1,35 @@
+"""Range facts about the ROM that the kernels rely on where they drop a saturation the reference carries."""
+import os
+import re
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _tab(name):
+    s = open(os.path.join(ROOT, "audio_codec_b200", "csrc", "rom_tables.inc")).read()
+    m = re.search(r"ROM_TAB\(\w+, " + name + r", (\d+)\) = \{(.*?)\};", s, re.S)
+    v = [int(x, 0) for x in re.findall(r"-?(?:0x[0-9a-fA-F]+|\d+)", m.group(2))]
+    assert len(v) == int(m.group(1))
+    return v
+
+
+def test_resampler_taps_cannot_overflow_32_bits():
+    """lc3_pitch_warp.cuh phase B: sum |taps| of every polyphase branch < 2^16, so |sum x*c| < 2^31 for |x| <= 2^15."""
+    f, p = _tab("rom_resamp_filt"), _tab("rom_resamp_params")
+    for fs in range(5):
+        up, delay = p[fs * 4], p[fs * 4 + 1]
+        for fr in range(up):
+            co = f[fs * 240 + fr * delay * 2: fs * 240 + (fr + 1) * delay * 2]
+            assert sum(abs(c) for c in co) * 32768 < 2 ** 31
+
+
+def test_product_and_oracle_rom_identical():
+    a = open(os.path.join(ROOT, "audio_codec_b200", "csrc", "rom_tables.inc")).read()
+    b = open(os.path.join(ROOT, "oracle", "rom_tables.inc")).read()
+    assert a == b
+
+
+def test_constants_used_with_unchecked_multiply_are_not_minus_one():
+    """mpy32x16k / mpy32x32k skip the (-1 x -1) saturation test: their constant operands must differ from the minimum."""
+    for name in ("rom_hp50_num", "rom_hp50_den", "rom_ltpf_inter_filt", "rom_tns_quant_pts"):
+        assert -32768 not in _tab(name), name
