@@ -37,7 +37,7 @@ typedef struct {
     int32_t *h_slot, *d_slot, *h_ostride, *d_ostride;
     int64_t *h_poff, *d_poff, *h_ooff, *d_ooff;
     /* work buffers */
-    size_t work_cap[6]; void *work[6];
+    size_t work_cap[7]; void *work[7];
     /* staging for host-pointer calls */
     size_t in_cap, out_cap, bfi_cap; void *d_in, *d_out, *d_bfi; uint8_t *h_bfi;
     int chunk_frames;
@@ -251,12 +251,12 @@ static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_
     if (fc < 1) fc = 1;
     if (fc > n_frames) fc = n_frames;
     const size_t ftl = (size_t)fc * b.n_tiles * 32;
-    const size_t need[6] = {(size_t)b.n_tiles * 32 * (size_t)(fc + 1) * N * sb, ftl * PO_N * 4, ftl * N * 4, ftl * FO_N * 4,
-                            ftl * (N / 4) * 4, ftl * RO_N * 4};
-    for (int i = 0; i < 6; i++)
+    const size_t need[7] = {(size_t)b.n_tiles * 32 * (size_t)(fc + 1) * N * sb, ftl * PO_N * 4, ftl * N * 4, ftl * FO_N * 4,
+                            ftl * (N / 4) * 4, ftl * RO_N * 4, ftl * 128 * 2};
+    for (int i = 0; i < 7; i++)
         if (ensure(&g.work[i], &g.work_cap[i], need[i], 0)) return 1;
     b.pcm_t = g.work[0]; b.pout = (int32_t *)g.work[1]; b.spec = (int32_t *)g.work[2]; b.fout = (int32_t *)g.work[3];
-    b.en4 = (int32_t *)g.work[4]; b.rout = (int32_t *)g.work[5];
+    b.en4 = (int32_t *)g.work[4]; b.rout = (int32_t *)g.work[5]; b.r12 = (int16_t *)g.work[6];
 
     const int n_chunks = (n_frames + fc - 1) / fc;
     if (g.prof_on && g.n_ev < n_chunks * 6) {
@@ -275,7 +275,7 @@ static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_
             CU((cudaError_t)launch[k](&b, g.stream));
         }
         if (g.prof_on) CU(cudaEventRecord(g.ev[c * 6 + 5], g.stream));
-        g.launches += 5;
+        g.launches += bits == 16 ? 7 : 5;
     }
     CU(cudaStreamSynchronize(g.stream)); /* lane tables are reused by the next bucket */
     if (g.prof_on) {

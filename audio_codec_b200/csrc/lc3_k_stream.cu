@@ -52,12 +52,28 @@ template <class T> __global__ void __launch_bounds__(256) k_stage(LC3K_Batch b)
 }
 
 // per-stream passes: one warp per channel-stream, 4 streams per block
-template <int BITS> __global__ void __launch_bounds__(128, 4) k_pitch(LC3K_Batch b)
+template <int BITS, bool PRE> __global__ void __launch_bounds__(128, 4) k_pitch(LC3K_Batch b)
 {
     __shared__ PitchShared sh[4];
     const int w = threadIdx.x >> 5;
-    pitch_warp_body<BITS>(b, blockIdx.x * 4 + w, sh[w]);
+    pitch_warp_body<BITS, PRE>(b, blockIdx.x * 4 + w, sh[w]);
 }
+
+// resampler FIR, frame-parallel: one warp per (channel-stream, frame)
+__global__ void __launch_bounds__(128) k_fir(LC3K_Batch b)
+{
+    __shared__ FirShared sh[4];
+    __shared__ i16 filt[240];
+    for (int i = threadIdx.x; i < 240; i += 128) filt[i] = rom_resamp_filt[b.fs_idx * 240 + i];
+    __syncthreads();
+    const int w = threadIdx.x >> 5;
+    const long long item = (long long)blockIdx.x * 4 + w;
+    if (item >= (long long)b.n_frames * b.n_lanes) return;
+    fir_warp_body(b, (int)(item % b.n_lanes), (int)(item / b.n_lanes), sh[w], filt);
+}
+
+// scalar recursions (high-pass, attack detector): one lane per channel-stream
+__global__ void __launch_bounds__(32) k_scalar(LC3K_Batch b) { scalar_body(b, blockIdx.x, threadIdx.x); }
 
 __global__ void __launch_bounds__(128) k_rate(LC3K_Batch b)
 {
@@ -102,9 +118,16 @@ extern "C" int lc3k_launch_stage(const LC3K_Batch *b, void *stream)
 }
 extern "C" int lc3k_launch_pitch(const LC3K_Batch *b, void *stream)
 {
+    cudaStream_t s = (cudaStream_t)stream;
     const int blocks = (b->n_lanes + 3) / 4;
-    if (b->bits == 16) k_pitch<16><<<blocks, 128, 0, (cudaStream_t)stream>>>(*b);
-    else k_pitch<24><<<blocks, 128, 0, (cudaStream_t)stream>>>(*b);
+    if (b->bits == 16) {
+        const long long items = (long long)b->n_frames * b->n_lanes;
+        k_fir<<<(unsigned)((items + 3) / 4), 128, 0, s>>>(*b);
+        k_scalar<<<b->n_tiles, 32, 0, s>>>(*b);
+        k_pitch<16, true><<<blocks, 128, 0, s>>>(*b);
+    } else {
+        k_pitch<24, false><<<blocks, 128, 0, s>>>(*b);
+    }
     return done();
 }
 extern "C" int lc3k_launch_rate(const LC3K_Batch *b, void *stream)

@@ -79,6 +79,7 @@ typedef struct {
     int32_t *fout;            /* [n_frames][n_tiles][FO_N][32] */
     int32_t *en4;             /* [n_frames][n_tiles][N/4][32] */
     int32_t *rout;            /* [n_frames][n_tiles][RO_N][32] */
+    int16_t *r12;             /* [n_frames][n_tiles][128][32] 12.8 kHz signal: FIR output, then high-passed in place */
 } LC3K_Batch;
 
 #ifdef __cplusplus
@@ -86,7 +87,7 @@ extern "C" {
 #endif
 /* kernel launchers (lc3_kernels.cu); stream is a cudaStream_t.  Return 0 or a cudaError_t value. */
 int lc3k_launch_stage(const LC3K_Batch *b, void *stream);
-int lc3k_launch_pitch(const LC3K_Batch *b, void *stream);
+int lc3k_launch_pitch(const LC3K_Batch *b, void *stream);   /* 16-bit: FIR, scalar recursions, pitch analysis (3 kernels); 24-bit: 1 fused kernel */
 int lc3k_launch_front(const LC3K_Batch *b, void *stream);
 int lc3k_launch_rate(const LC3K_Batch *b, void *stream);
 int lc3k_launch_back(const LC3K_Batch *b, void *stream);

@@ -274,6 +274,7 @@ template <class XS> LC3_HD void attack_detector(AttackState &st, XS xs, int N, i
 {
     const int n16 = 160;
     Range rg; range_init(rg);
+#pragma unroll 16
     for (int i = 0; i < N; i++) range_add(rg, xs(i));
     i32 s0 = s_add(range_headroom16(rg, 0), in_scaling);
     Range r1; range_init(r1); range_add(r1, st.filter_mem[0]); range_add(r1, st.filter_mem[1]);
@@ -294,6 +295,7 @@ template <class XS> LC3_HD void attack_detector(AttackState &st, XS xs, int N, i
     // decimate, 3-tap high-pass (on the unfiltered neighbours), block energies, in one sweep
     i32 dm2 = st.filter_mem[0], dm1 = st.filter_mem[1];
     i32 acc = st.acc_energy, detected = st.position >= 2, pos = -1, be = 0;
+#pragma unroll 8
     for (int i = 0; i < n16; i++) {
         i32 d;
         if (dec == 2) d = s_add(s_shr(xs(2 * i), ds), s_shr(xs(2 * i + 1), ds));

@@ -40,7 +40,11 @@ template <class T> struct RawPcm {
     LC3_HDM i32 operator()(int i) const { return (i < 0 && first) ? (i32)hist[N + i] : (i32)cur[i]; }
 };
 
-template <int BITS> LC3_HD void pitch_warp_body(const LC3K_Batch &b, int li, PitchShared &sh)
+// PRE = true (16-bit input only): the resampler FIR, the high-pass recursion and the attack detector have already
+// run in their own passes (fir_warp_body, scalar_body below) and b.r12 holds the high-passed 12.8 kHz samples;
+// this body then does the pitch analysis only.  PRE = false: everything in one pass (24-bit input, whose block
+// exponent depends on the filter state and therefore cannot be split).
+template <int BITS, bool PRE> LC3_HD void pitch_warp_body(const LC3K_Batch &b, int li, PitchShared &sh)
 {
     typedef typename std::conditional<BITS == 16, i16, i32>::type T;
     if (li >= b.n_lanes) return;
@@ -129,40 +133,48 @@ template <int BITS> LC3_HD void pitch_warp_body(const LC3K_Batch &b, int li, Pit
                 LC3_LANES_END
             }
         }
-        {
-            const i32 shx = s_sub(23, x_exp);
+        if (PRE) {
+            SV<const i16> r = tile_view((const i16 *)b.r12, frame_tile(b, f, tile), 128, tl);
             LC3_LANES(l)
-                for (int i = l - rl; i < N; i += 32) sh.xs[64 + i] = (i16)(BITS == 16 ? raw(i) : l_round(l_shl(raw(i), shx)));
+                for (int n = l; n < len; n += 32) sh.s12[24 + n] = r[n];
+                if (attack_handling) for (int i = l; i < N; i += 32) sh.xs[64 + i] = (i16)raw(i); // for the attack detector
             LC3_LANES_END
-        }
-
-        // ---- B. polyphase FIR to 12.8 kHz (resamp12k8_fx.c:62-86): lane = output sample
-        LC3_LANES(l)
-            for (int n = l; n < len; n += 32) {
-                const int t = n * off_frac, ii = 1 + n * off_int + t / upfac - rl, fr = t % upfac;
-                const i16 *co = &sh.filt[fr * delay2], *in = &sh.xs[64 + ii];
-                // the reference's saturating L_mac0 chain cannot saturate: sum |taps| <= 56970 < 2^16 for every
-                // phase of every rate (checked against the ROM in tests/test_rom_bounds.py), |x| <= 2^15
-                i32 acc = 0;
-                for (int m = 0; m < delay2; m++) acc += in[m] * co[m];
-                sh.fir[n] = (i16)l_round(acc);
+        } else {
+            {
+                const i32 shx = s_sub(23, x_exp);
+                LC3_LANES(l)
+                    for (int i = l - rl; i < N; i += 32) sh.xs[64 + i] = (i16)(BITS == 16 ? raw(i) : l_round(l_shl(raw(i), shx)));
+                LC3_LANES_END
             }
-        LC3_LANES_END
 
-        // ---- C. 50 Hz high-pass, a true recursion (resamp12k8_fx.c:88-104): every lane runs it redundantly so
-        //         the filter state stays warp-uniform; all lanes store the same value to s12[24 + n]
-        {
-            const i32 n0 = rom_hp50_num[0], n1 = rom_hp50_num[1], n2 = rom_hp50_num[2], d0 = rom_hp50_den[0], d1 = rom_hp50_den[1];
-            for (int n = 0; n < len; n++) {
-                const i32 v = sh.fir[n];
-                const i32 o = l_mac0(m0, n0, v);
-                const i32 t = l_mac0(mpy32x16k(o, d0), n1, v);
-                m0 = l_add(m1, l_shl_p(t, 1));
-                m1 = l_mac0(mpy32x16k(o, d1), n2, v);
-                sh.s12[24 + n] = (i16)l_round(o);
+            // ---- B. polyphase FIR to 12.8 kHz (resamp12k8_fx.c:62-86): lane = output sample
+            LC3_LANES(l)
+                for (int n = l; n < len; n += 32) {
+                    const int t = n * off_frac, ii = 1 + n * off_int + t / upfac - rl, fr = t % upfac;
+                    const i16 *co = &sh.filt[fr * delay2], *in = &sh.xs[64 + ii];
+                    // the reference's saturating L_mac0 chain cannot saturate: sum |taps| <= 56970 < 2^16 for every
+                    // phase of every rate (checked against the ROM in tests/test_rom_bounds.py), |x| <= 2^15
+                    i32 acc = 0;
+                    for (int m = 0; m < delay2; m++) acc += in[m] * co[m];
+                    sh.fir[n] = (i16)l_round(acc);
+                }
+            LC3_LANES_END
+
+            // ---- C. 50 Hz high-pass, a true recursion (resamp12k8_fx.c:88-104): every lane runs it redundantly so
+            //         the filter state stays warp-uniform; all lanes store the same value to s12[24 + n]
+            {
+                const i32 n0 = rom_hp50_num[0], n1 = rom_hp50_num[1], n2 = rom_hp50_num[2], d0 = rom_hp50_den[0], d1 = rom_hp50_den[1];
+                for (int n = 0; n < len; n++) {
+                    const i32 v = sh.fir[n];
+                    const i32 o = l_mac0(m0, n0, v);
+                    const i32 t = l_mac0(mpy32x16k(o, d0), n1, v);
+                    m0 = l_add(m1, l_shl_p(t, 1));
+                    m1 = l_mac0(mpy32x16k(o, d1), n2, v);
+                    sh.s12[24 + n] = (i16)l_round(o);
+                }
             }
+            LC3_SYNC; // s12[0 .. len] is the delayed 12.8 kHz signal of this frame
         }
-        LC3_SYNC; // s12[0 .. len] is the delayed 12.8 kHz signal of this frame
 
         // ---- D. OLPA: 2:1 decimation with a 5-tap low-pass (olpa_fx.c:36-58): lane = 6.4 kHz sample.
         //         v[j] = m12[3 + j] for j < 0, s12[j] otherwise; output k uses v[2k-3 .. 2k+1].
@@ -470,16 +482,78 @@ template <int BITS> LC3_HD void pitch_warp_body(const LC3K_Batch &b, int li, Pit
         if (l < 3) s16[S16_OLPA_S12 + l] = sh.m12[l];
         for (int k = l; k < olpa_len; k += 32) s16[S16_OLPA_BUF + k] = sh.olpa[ob][k];
         for (int k = l; k < lt_len; k += 32) s16[S16_LTPF_BUF + k] = sh.ltpf[lb][k];
+        if (l == 0 && !PRE) { st[ST_MEM50_0] = m0; st[ST_MEM50_1] = m1; }
         if (l == 0) {
-            st[ST_MEM50_0] = m0; st[ST_MEM50_1] = m1;
-            st[ST_OLPA_EXP] = olpa_exp; st[ST_OLPA_PITCH] = olpa_pitch;
-            st[ST_LTPF_EXP] = ltpf_exp; st[ST_LTPF_NC] = ltpf_nc; st[ST_LTPF_MNC] = ltpf_mnc;
-            st[ST_LTPF_ON] = ltpf_on; st[ST_LTPF_PITCH] = ltpf_pitch_mem;
             st[ST_ATT_F0] = as.filter_mem[0]; st[ST_ATT_F1] = as.filter_mem[1]; st[ST_ATT_DET] = as.detected;
             st[ST_ATT_POS] = as.position; st[ST_ATT_SCAL] = as.scaling; st[ST_ATT_ACC] = as.acc_energy;
             st[ST_X_EXP] = x_exp; st[ST_RESAMP_EXP] = resamp_exp;
+            st[ST_OLPA_EXP] = olpa_exp; st[ST_OLPA_PITCH] = olpa_pitch;
+            st[ST_LTPF_EXP] = ltpf_exp; st[ST_LTPF_NC] = ltpf_nc; st[ST_LTPF_MNC] = ltpf_mnc;
+            st[ST_LTPF_ON] = ltpf_on; st[ST_LTPF_PITCH] = ltpf_pitch_mem;
         }
     LC3_LANES_END
+}
+
+// ---- resampler FIR as its own frame-parallel pass (16-bit input): one warp per (channel-stream, frame)
+struct FirShared { i16 xs[64 + LC3K_MAX_N]; };
+
+LC3_HD void fir_warp_body(const LC3K_Batch &b, int li, int f, FirShared &sh, const i16 *filt /* this rate's 240 taps */)
+{
+    if (li >= b.n_lanes) return;
+    const int tile = li >> 5, tl = li & 31, N = b.N, rl = b.r12k8_mem_in_len, len = 32 * (b.dms / 25);
+    const int upfac = rom_resamp_params[b.fs_idx * 4 + 0], delay2 = 2 * rom_resamp_params[b.fs_idx * 4 + 1];
+    const int off_int = rom_resamp_params[b.fs_idx * 4 + 2], off_frac = rom_resamp_params[b.fs_idx * 4 + 3];
+    RawPcm<i16> raw;
+    raw.N = N;
+    raw.hist = tile_view((const i16 *)b.pcm_t, (size_t)tile, (size_t)(b.n_frames + 1) * N, tl);
+    raw.cur = (const i16 *)b.pcm + b.pcm_off[li] + (size_t)(b.frame0 + f) * N;
+    raw.first = f == 0;
+    LC3_LANES(l)
+        for (int i = l - rl; i < N; i += 32) sh.xs[64 + i] = (i16)raw(i);
+    LC3_LANES_END
+    SV<i16> r = tile_view(b.r12, frame_tile(b, f, tile), 128, tl);
+    LC3_LANES(l)
+        for (int n = l; n < len; n += 32) { // see pitch_warp_body phase B for why plain arithmetic is exact
+            const int t = n * off_frac, ii = 1 + n * off_int + t / upfac - rl, fr = t % upfac;
+            const i16 *co = &filt[fr * delay2], *in = &sh.xs[64 + ii];
+            i32 acc = 0;
+            for (int m = 0; m < delay2; m++) acc += in[m] * co[m];
+            r[n] = (i16)l_round(acc);
+        }
+    LC3_LANES_END
+}
+
+// ---- the 50 Hz high-pass as its own pass (16-bit input): ONE LANE PER CHANNEL-STREAM walks the frames in order
+// through the recursion (resamp12k8_fx.c:88-104), in place on b.r12.  It is the one part of the time-domain chain
+// with no parallelism inside a stream; with a lane per stream it costs one warp instruction per 32 streams.
+LC3_HD void scalar_body(const LC3K_Batch &b, int tile, int lane)
+{
+    const int li = tile * LC3K_LANES + lane;
+    if (li >= b.n_lanes) return;
+    SV<i32> st = slot_view(b.st32, b.slot[li], ST32_N);
+    const int len = 32 * (b.dms / 25);
+    i32 m0 = st[ST_MEM50_0], m1 = st[ST_MEM50_1];
+    const i32 n0 = rom_hp50_num[0], n1 = rom_hp50_num[1], n2 = rom_hp50_num[2], d0 = rom_hp50_den[0], d1 = rom_hp50_den[1];
+    for (int f = 0; f < b.n_frames; f++) {
+        SV<i16> r = tile_view(b.r12, frame_tile(b, f, tile), 128, lane);
+        // fetch the frame first (independent loads), then run the recursion from registers/local memory: with one
+        // warp per 32 streams this pass is latency-bound and a load inside the recursion would serialise with it
+        i16 buf[128];
+#pragma unroll 16
+        for (int n = 0; n < len; n++) buf[n] = r[n];
+#pragma unroll 4
+        for (int n = 0; n < len; n++) {
+            const i32 v = buf[n];
+            const i32 o = l_mac0(m0, n0, v);
+            const i32 t = l_mac0(mpy32x16k(o, d0), n1, v);
+            m0 = l_add(m1, l_shl_p(t, 1));
+            m1 = l_mac0(mpy32x16k(o, d1), n2, v);
+            buf[n] = (i16)l_round(o);
+        }
+#pragma unroll 16
+        for (int n = 0; n < len; n++) r[n] = buf[n];
+    }
+    st[ST_MEM50_0] = m0; st[ST_MEM50_1] = m1;
 }
 
 } // namespace lc3k

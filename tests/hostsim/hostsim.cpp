@@ -131,8 +131,17 @@ extern "C" int hostsim_encode(void *p, const void *pcm, int bits, int n_frames, 
                 if (bits == 16) pitch_body<16>(b, tile, lane); else pitch_body<24>(b, tile, lane);
             }
     } else {
-        for (int li = 0; li < b.n_lanes; li++) {
-            if (bits == 16) pitch_warp_body<16>(b, li, psh); else pitch_warp_body<24>(b, li, psh);
+        std::vector<int16_t> r12(ftl * 128);
+        b.r12 = r12.data();
+        if (bits == 16) { // three passes as the kernels run them
+            static FirShared fsh;
+            for (int f = 0; f < n_frames; f++)
+                for (int li = 0; li < b.n_lanes; li++) fir_warp_body(b, li, f, fsh, &rom_resamp_filt[b.fs_idx * 240]);
+            for (int tile = 0; tile < b.n_tiles; tile++)
+                for (int lane = 0; lane < 32; lane++) scalar_body(b, tile, lane);
+            for (int li = 0; li < b.n_lanes; li++) pitch_warp_body<16, true>(b, li, psh);
+        } else {
+            for (int li = 0; li < b.n_lanes; li++) pitch_warp_body<24, false>(b, li, psh);
         }
     }
     for (int f = 0; f < n_frames; f++)
