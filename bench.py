@@ -256,7 +256,10 @@ def main():
     achieved = ALGO_BYTES_PER_FRAME * frames_per_launch / (avg_ms * 1e-3) / 1e9
     traffic = None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(top)
+        # DRAM bytes of the dominant kernel from the committed `ncu --set full` capture (tools/ncu_summary.py), per launch,
+        # rescaled linearly if this run's launch covers a different number of channel-frames than the captured one
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        traffic = tj[f"k_{top}"][0]["dram_bytes"] * frames_per_launch / tj["_frames_per_launch"]
     except Exception:
         pass
     sm_clock = summarize_clocks(rows)
