@@ -263,13 +263,19 @@ def main():
     except Exception:
         pass
     sm_clock = summarize_clocks(rows)
-    int_peak = 148 * 4 * 32 * (sm_clock["sm_mhz"] or 1965) * 1e6   # one warp instruction per SMSP per clock
+    int_peak, int_src = 148 * 4 * 32 * (sm_clock["sm_mhz"] or 1965) * 1e6, "148 SMs x 4 schedulers x 32 lanes x median SM clock"
+    try:   # measured on this pool's B200 by tools/int_peak.cu (mixed IMAD+LOP3 stream, 97 % of the issue limit)
+        ip = json.load(open(os.path.join(ROOT, "profiles", "int_peak.json")))
+        int_peak = ip["mixed_thread_instr_per_s"] * (sm_clock["sm_mhz"] or 1965) * 1e3 / ip["sm_clock_khz_max"]
+        int_src = "measured: profiles/int_peak.json (tools/int_peak.cu), scaled to the median SM clock of this run"
+    except Exception:
+        pass
     roofline = {"bound": "hbm", "kernel": f"k_{top}", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                 "frac": achieved / hbm_peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_frame": ALGO_BYTES_PER_FRAME, "avg_launch_ms": avg_ms,
                 "kernel_ms_share": {k: v / sum(kern.values()) for k, v in kern.items()},
                 "int_alu": {"note": "the path is integer-issue bound, not HBM bound (SURVEY.md 8d): reference weighted ops/frame x frames/s "
-                                    "over 148 SMs x 4 schedulers x 32 lanes x median SM clock",
+                                    "over the integer issue peak", "peak_source": int_src,
                             "weighted_ops_per_frame": WOPS_PER_FRAME, "achieved_wops_per_s": value / world * WOPS_PER_FRAME,
                             "peak_thread_instr_per_s": int_peak, "frac": value / world * WOPS_PER_FRAME / int_peak}}
     line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
