@@ -11,6 +11,10 @@
 #include "lc3_config.h"
 
 #define LC3B_MAGIC 0x4c433362u
+#define N_PIPES 3
+enum { K_STAGE = 0, K_FIR, K_SCALAR, K_PITCH, K_FRONT, K_RATE, K_BACK, N_KERNELS };
+/* kernels that read and write per-stream state: chunk c+1's launch must wait for chunk c's */
+static const int k_stateful[N_KERNELS] = {1 /* input history */, 0, 1 /* high-pass memory */, 1, 0, 1 /* rate-loop feedback */, 0};
 
 struct LC3_Enc { /* lives in the caller's block; device state is referenced by slot */
     uint32_t magic;
@@ -36,14 +40,19 @@ typedef struct {
     size_t lanes_cap;
     int32_t *h_slot, *d_slot, *h_ostride, *d_ostride;
     int64_t *h_poff, *d_poff, *h_ooff, *d_ooff;
-    /* work buffers */
-    size_t work_cap[7]; void *work[7];
+    /* chunk pipeline: N_PIPES chunks of frames in flight, each on its own stream with its own work buffers */
+    struct {
+        cudaStream_t par, ser;  /* frame-parallel kernels + copies | per-stream (stateful) kernels, higher priority */
+        size_t work_cap[7]; void *work[7];
+        cudaEvent_t state_ev[N_KERNELS], hop_ev[N_KERNELS + 2], done_ev;
+    } pipe[N_PIPES];
+    cudaEvent_t start_ev, end_ev;
     /* staging for host-pointer calls */
     size_t in_cap, out_cap, bfi_cap; void *d_in, *d_out, *d_bfi; uint8_t *h_bfi;
     int chunk_frames;
     long long launches;
     /* optional per-kernel timing with CUDA events on the launching stream */
-    int prof_on; cudaEvent_t *ev; int n_ev; double prof_ms[8];
+    int prof_on; cudaEvent_t *ev; int n_ev; double prof_ms[N_KERNELS + 3];
     char err[256];
 } Ctx;
 
@@ -102,8 +111,22 @@ static int ctx_init(void)
     }
     CU(cudaGetDevice(&g.device));
     CU(cudaStreamCreateWithFlags(&g.stream, cudaStreamNonBlocking));
+    int prio_lo = 0, prio_hi = 0;
+    CU(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    for (int p = 0; p < N_PIPES; p++) {
+        /* the per-stream kernels are short on parallelism (one warp or lane per stream) and sit on the critical path of
+         * the next chunk: at higher priority their blocks are placed as soon as SM resources free up, so they run
+         * underneath the previous chunk's frame-parallel kernels instead of queueing behind their grids */
+        CU(cudaStreamCreateWithPriority(&g.pipe[p].par, cudaStreamNonBlocking, prio_lo));
+        CU(cudaStreamCreateWithPriority(&g.pipe[p].ser, cudaStreamNonBlocking, prio_hi));
+        for (int k = 0; k < N_KERNELS; k++) CU(cudaEventCreateWithFlags(&g.pipe[p].state_ev[k], cudaEventDisableTiming));
+        for (int k = 0; k < N_KERNELS + 2; k++) CU(cudaEventCreateWithFlags(&g.pipe[p].hop_ev[k], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&g.pipe[p].done_ev, cudaEventDisableTiming));
+    }
+    CU(cudaEventCreate(&g.start_ev));
+    CU(cudaEventCreate(&g.end_ev));
     g.dirty_lo = 1 << 30; g.dirty_hi = -1;
-    g.chunk_frames = 1 << 19;
+    g.chunk_frames = 1 << 17;
     if (pool_grow(4096)) return 1;
     g.failed = 0;
     g.ready = 1;
@@ -193,10 +216,11 @@ static int lanes_reserve(size_t n)
 }
 
 /* one bucket: encoders that share (fs_idx, dms).  idx[] lists their positions in encs[]. */
+typedef struct { const void *h_pcm; void *h_out; } ChunkCopy; /* host buffers to copy chunk by chunk (NULL: not needed) */
+
 static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_frames, const void *d_pcm, size_t stride,
-                      int bits, uint8_t *d_out, size_t ostride, const int *num_bytes_in, int n_streams_total)
+                      int bits, uint8_t *d_out, size_t ostride, const int *num_bytes_in, const ChunkCopy *cp)
 {
-    (void)n_streams_total;
     const LC3Cfg *c0 = &encs[idx[0]]->cfg;
     const int N = c0->N, sb = bits == 16 ? 2 : 4;
     size_t n_lanes = 0;
@@ -247,48 +271,89 @@ static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_
         b.bfi = (const uint8_t *)g.d_bfi;
     }
 
+    /* frames per chunk: about g.chunk_frames channel-frames each, balanced over the chunks */
     int fc = g.chunk_frames / (b.n_tiles * 32);
     if (fc < 1) fc = 1;
     if (fc > n_frames) fc = n_frames;
+    const int n_chunks = (n_frames + fc - 1) / fc;
+    fc = (n_frames + n_chunks - 1) / n_chunks;
+    const int n_pipes = n_chunks < N_PIPES ? n_chunks : N_PIPES;
     const size_t ftl = (size_t)fc * b.n_tiles * 32;
     const size_t need[7] = {(size_t)b.n_tiles * 32 * (size_t)(fc + 1) * N * sb, ftl * PO_N * 4, ftl * N * 4, ftl * FO_N * 4,
                             ftl * (N / 4) * 4, ftl * RO_N * 4, ftl * 128 * 2};
-    for (int i = 0; i < 7; i++)
-        if (ensure(&g.work[i], &g.work_cap[i], need[i], 0)) return 1;
-    b.pcm_t = g.work[0]; b.pout = (int32_t *)g.work[1]; b.spec = (int32_t *)g.work[2]; b.fout = (int32_t *)g.work[3];
-    b.en4 = (int32_t *)g.work[4]; b.rout = (int32_t *)g.work[5]; b.r12 = (int16_t *)g.work[6];
+    for (int p = 0; p < n_pipes; p++)
+        for (int i = 0; i < 7; i++)
+            if (ensure(&g.pipe[p].work[i], &g.pipe[p].work_cap[i], need[i], 0)) return 1;
 
-    const int n_chunks = (n_frames + fc - 1) / fc;
-    if (g.prof_on && g.n_ev < n_chunks * 6) {
-        cudaEvent_t *ne = (cudaEvent_t *)realloc(g.ev, (size_t)n_chunks * 6 * sizeof(cudaEvent_t));
+    const int EPC = 2 * N_KERNELS; /* profiling events per chunk: one before and one after every kernel */
+    if (g.prof_on && g.n_ev < n_chunks * EPC) {
+        cudaEvent_t *ne = (cudaEvent_t *)realloc(g.ev, (size_t)n_chunks * EPC * sizeof(cudaEvent_t));
         if (!ne) return 1;
         g.ev = ne;
-        for (; g.n_ev < n_chunks * 6; g.n_ev++) CU(cudaEventCreate(&g.ev[g.n_ev]));
+        for (; g.n_ev < n_chunks * EPC; g.n_ev++) CU(cudaEventCreate(&g.ev[g.n_ev]));
     }
-    int (*const launch[5])(const LC3K_Batch *, void *) = {lc3k_launch_stage, lc3k_launch_pitch, lc3k_launch_front,
-                                                          lc3k_launch_rate, lc3k_launch_back};
+    int (*const launch[N_KERNELS])(const LC3K_Batch *, void *) = {lc3k_launch_stage, lc3k_launch_fir, lc3k_launch_scalar, lc3k_launch_pitch,
+                                                                  lc3k_launch_front, lc3k_launch_rate, lc3k_launch_back};
+    /* everything queued on the main stream so far (state reset, configuration, lane tables, whole-buffer input copy)
+     * is ordered before the first chunk of every pipe */
+    CU(cudaEventRecord(g.start_ev, g.stream));
     for (int f0 = 0, c = 0; f0 < n_frames; f0 += fc, c++) {
+        const int p = c % N_PIPES;
+        const cudaStream_t par = g.pipe[p].par, ser = g.pipe[p].ser;
+        void *const *w = g.pipe[p].work;
+        if (c < N_PIPES) { CU(cudaStreamWaitEvent(par, g.start_ev, 0)); CU(cudaStreamWaitEvent(ser, g.start_ev, 0)); }
+        else CU(cudaStreamWaitEvent(ser, g.pipe[p].done_ev, 0)); /* chunk c - N_PIPES is done with these work buffers */
         b.frame0 = f0;
         b.n_frames = n_frames - f0 < fc ? n_frames - f0 : fc;
-        for (int k = 0; k < 5; k++) {
-            if (g.prof_on) CU(cudaEventRecord(g.ev[c * 6 + k], g.stream));
-            CU((cudaError_t)launch[k](&b, g.stream));
+        b.pcm_t = w[0]; b.pout = (int32_t *)w[1]; b.spec = (int32_t *)w[2]; b.fout = (int32_t *)w[3];
+        b.en4 = (int32_t *)w[4]; b.rout = (int32_t *)w[5]; b.r12 = (int16_t *)w[6];
+        cudaStream_t cur = par;
+        if (cp && cp->h_pcm) /* this chunk's columns of every stream's PCM rows, one rectangle per channel */
+            for (int ch = 0; ch < c0->channels; ch++) {
+                const size_t off = ((size_t)ch * n_frames + f0) * N * sb;
+                CU(cudaMemcpy2DAsync((char *)d_pcm + off, stride, (const char *)cp->h_pcm + off, stride, (size_t)b.n_frames * N * sb,
+                                     (size_t)n, cudaMemcpyHostToDevice, par));
+            }
+        for (int k = 0; k < N_KERNELS; k++) {
+            if (bits != 16 && (k == K_FIR || k == K_SCALAR)) continue; /* fused into K_PITCH for 24-bit input */
+            const cudaStream_t st = k_stateful[k] ? ser : par;
+            if (st != cur) { /* the chunk's kernels form a chain: hand over between the two streams */
+                CU(cudaEventRecord(g.pipe[p].hop_ev[k], cur));
+                CU(cudaStreamWaitEvent(st, g.pipe[p].hop_ev[k], 0));
+                cur = st;
+            }
+            if (k_stateful[k] && c > 0) CU(cudaStreamWaitEvent(st, g.pipe[(c - 1) % N_PIPES].state_ev[k], 0));
+            if (g.prof_on) CU(cudaEventRecord(g.ev[c * EPC + 2 * k], st));
+            CU((cudaError_t)launch[k](&b, st));
+            if (g.prof_on) CU(cudaEventRecord(g.ev[c * EPC + 2 * k + 1], st));
+            if (k_stateful[k] && c + 1 < n_chunks) CU(cudaEventRecord(g.pipe[p].state_ev[k], st));
         }
-        if (g.prof_on) CU(cudaEventRecord(g.ev[c * 6 + 5], g.stream));
+        /* K_BACK ran on `par` */
+        if (cp && cp->h_out) {
+            const size_t nb = (size_t)lc3cfg_num_bytes(c0), off = (size_t)f0 * nb;
+            CU(cudaMemcpy2DAsync((char *)cp->h_out + off, ostride, d_out + off, ostride, (size_t)b.n_frames * nb, (size_t)n,
+                                 cudaMemcpyDeviceToHost, par));
+        }
+        CU(cudaEventRecord(g.pipe[p].done_ev, par));
         g.launches += bits == 16 ? 7 : 5;
     }
+    for (int p = 0; p < n_pipes; p++) CU(cudaStreamWaitEvent(g.stream, g.pipe[p].done_ev, 0));
+    CU(cudaEventRecord(g.end_ev, g.stream));
     CU(cudaStreamSynchronize(g.stream)); /* lane tables are reused by the next bucket */
     if (g.prof_on) {
+        /* per-kernel time = elapsed on the kernel's own stream; with several chunks in flight the kernels of different
+         * chunks share the SMs, so these sum to more than the span */
         float ms;
         for (int c = 0; c < n_chunks; c++)
-            for (int k = 0; k < 5; k++) {
-                CU(cudaEventElapsedTime(&ms, g.ev[c * 6 + k], g.ev[c * 6 + k + 1]));
+            for (int k = 0; k < N_KERNELS; k++) {
+                if (bits != 16 && (k == K_FIR || k == K_SCALAR)) continue;
+                CU(cudaEventElapsedTime(&ms, g.ev[c * EPC + 2 * k], g.ev[c * EPC + 2 * k + 1]));
                 g.prof_ms[k] += ms;
             }
-        CU(cudaEventElapsedTime(&ms, g.ev[0], g.ev[(n_chunks - 1) * 6 + 5]));
-        g.prof_ms[5] += ms;
-        g.prof_ms[6] += 1;
-        g.prof_ms[7] += n_chunks;
+        CU(cudaEventElapsedTime(&ms, g.start_ev, g.end_ev));
+        g.prof_ms[N_KERNELS] += ms;
+        g.prof_ms[N_KERNELS + 1] += 1;
+        g.prof_ms[N_KERNELS + 2] += n_chunks;
     }
     return 0;
 }
@@ -313,9 +378,11 @@ static LC3_Error run_batch(struct LC3_Enc *const *encs, int n_streams, int n_fra
     cudaSetDevice(g.device);
     unsigned id = ++g_call_id;
     size_t max_in = 0, max_out = 0;
-    int uniform = 1;
+    int uniform = 1, one_bucket = 1;
     for (int i = 0; i < n_streams; i++) {
         struct LC3_Enc *e = encs[i];
+        if (e->cfg.dms_idx != encs[0]->cfg.dms_idx || e->cfg.fs_idx != encs[0]->cfg.fs_idx || e->cfg.channels != encs[0]->cfg.channels)
+            one_bucket = 0;
         if ((unsigned)e->batch_mark == id) { snprintf(g.err, sizeof(g.err), "encoder listed twice in one batch"); goto done; }
         e->batch_mark = (int)id;
         if (e->dirty) cfg_to_shadow(e);
@@ -330,9 +397,14 @@ static LC3_Error run_batch(struct LC3_Enc *const *encs, int n_streams, int n_fra
     const int pcm_dev = is_device_ptr(pcm), out_dev = is_device_ptr(out);
     const void *d_pcm = pcm;
     uint8_t *d_out = (uint8_t *)out;
+    /* equal-sized streams of one (sample rate, frame size): host buffers are copied chunk by chunk on the chunk's own
+     * stream, so the copies of one chunk overlap the kernels of its neighbours; otherwise whole-buffer copies up front */
+    const int chunked = uniform && one_bucket;
+    ChunkCopy cp = {chunked && !pcm_dev ? pcm : NULL, chunked && !out_dev ? out : NULL};
     if (!pcm_dev) {
         if (ensure(&g.d_in, &g.in_cap, (size_t)n_streams * stride + max_in, 0)) goto done;
-        if (uniform) {
+        if (chunked) { /* copied per chunk in run_bucket */
+        } else if (uniform) {
             if (cu_fail(cudaMemcpy2DAsync(g.d_in, stride, pcm, stride, max_in, n_streams, cudaMemcpyHostToDevice, g.stream), "H2D pcm")) goto done;
         } else {
             for (int i = 0; i < n_streams; i++) {
@@ -354,9 +426,9 @@ static LC3_Error run_batch(struct LC3_Enc *const *encs, int n_streams, int n_fra
         int n = 0;
         for (int i = 0; i < n_streams; i++)
             if (encs[i]->cfg.dms_idx * 5 + encs[i]->cfg.fs_idx == key) order[n++] = i;
-        if (n && run_bucket(encs, order, n, n_frames, d_pcm, stride, bits, d_out, ostride, num_bytes, n_streams)) goto done;
+        if (n && run_bucket(encs, order, n, n_frames, d_pcm, stride, bits, d_out, ostride, num_bytes, &cp)) goto done;
     }
-    if (!out_dev) {
+    if (!out_dev && !chunked) {
         if (uniform) {
             if (cu_fail(cudaMemcpy2DAsync(out, ostride, d_out, ostride, max_out, n_streams, cudaMemcpyDeviceToHost, g.stream), "D2H out")) goto done;
         } else {

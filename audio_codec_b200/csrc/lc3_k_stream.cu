@@ -116,18 +116,26 @@ extern "C" int lc3k_launch_stage(const LC3K_Batch *b, void *stream)
     else k_stage<int32_t><<<grid, 256, 0, (cudaStream_t)stream>>>(*b);
     return done();
 }
+// 16-bit input: FIR (frame-parallel), high-pass recursion (lane per stream), then pitch analysis (warp per stream);
+// 24-bit input: the fused kernel does all three (lc3k_launch_fir / _scalar are then no-ops)
+extern "C" int lc3k_launch_fir(const LC3K_Batch *b, void *stream)
+{
+    if (b->bits != 16) return 0;
+    const long long items = (long long)b->n_frames * b->n_lanes;
+    k_fir<<<(unsigned)((items + 3) / 4), 128, 0, (cudaStream_t)stream>>>(*b);
+    return done();
+}
+extern "C" int lc3k_launch_scalar(const LC3K_Batch *b, void *stream)
+{
+    if (b->bits != 16) return 0;
+    k_scalar<<<b->n_tiles, 32, 0, (cudaStream_t)stream>>>(*b);
+    return done();
+}
 extern "C" int lc3k_launch_pitch(const LC3K_Batch *b, void *stream)
 {
-    cudaStream_t s = (cudaStream_t)stream;
     const int blocks = (b->n_lanes + 3) / 4;
-    if (b->bits == 16) {
-        const long long items = (long long)b->n_frames * b->n_lanes;
-        k_fir<<<(unsigned)((items + 3) / 4), 128, 0, s>>>(*b);
-        k_scalar<<<b->n_tiles, 32, 0, s>>>(*b);
-        k_pitch<16, true><<<blocks, 128, 0, s>>>(*b);
-    } else {
-        k_pitch<24, false><<<blocks, 128, 0, s>>>(*b);
-    }
+    if (b->bits == 16) k_pitch<16, true><<<blocks, 128, 0, (cudaStream_t)stream>>>(*b);
+    else k_pitch<24, false><<<blocks, 128, 0, (cudaStream_t)stream>>>(*b);
     return done();
 }
 extern "C" int lc3k_launch_rate(const LC3K_Batch *b, void *stream)

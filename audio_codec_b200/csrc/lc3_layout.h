@@ -87,7 +87,9 @@ extern "C" {
 #endif
 /* kernel launchers (lc3_kernels.cu); stream is a cudaStream_t.  Return 0 or a cudaError_t value. */
 int lc3k_launch_stage(const LC3K_Batch *b, void *stream);
-int lc3k_launch_pitch(const LC3K_Batch *b, void *stream);   /* 16-bit: FIR, scalar recursions, pitch analysis (3 kernels); 24-bit: 1 fused kernel */
+int lc3k_launch_fir(const LC3K_Batch *b, void *stream);     /* 16-bit input only (no-op otherwise): resampler FIR, frame-parallel */
+int lc3k_launch_scalar(const LC3K_Batch *b, void *stream);  /* 16-bit input only (no-op otherwise): 50 Hz high-pass recursion, lane per stream */
+int lc3k_launch_pitch(const LC3K_Batch *b, void *stream);   /* pitch analysis + attack detector, warp per stream (24-bit: also the two above) */
 int lc3k_launch_front(const LC3K_Batch *b, void *stream);
 int lc3k_launch_rate(const LC3K_Batch *b, void *stream);
 int lc3k_launch_back(const LC3K_Batch *b, void *stream);

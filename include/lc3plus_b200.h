@@ -103,13 +103,15 @@ void lc3plus_enc_release(LC3_Enc *encoder);
 /* NEW: number of kernels launched by this process so far (for benchmarks' gpu_launches). */
 long long lc3plus_kernel_launches(void);
 /* NEW: per-kernel device timing with CUDA events on the library's launching stream.  After enable(1), every
- * batch call accumulates into ms[8] = {stage, pitch, front, rate, back kernel ms, first-launch-to-last-kernel
- * span ms, calls, chunks}; enable() also clears the accumulators. */
+ * batch call accumulates into ms[10] = {stage, fir, scalar, pitch, front, rate, back kernel ms (each bracketed by events
+ * on the stream it was launched on; chunks overlap, so these can sum to more than the span), start-of-first-chunk to
+ * end-of-last-chunk span ms, calls, chunks}; enable() also clears the accumulators. */
 void lc3plus_profile_enable(int on);
 void lc3plus_profile_read(double *ms);
 /* NEW: last CUDA error string seen by the library ("" if none). */
 const char *lc3plus_last_error(void);
-/* NEW: upper bound on channel-frames processed per internal chunk (default 524288); tuning knob. */
+/* NEW: upper bound on channel-frames processed per internal chunk (default 131072); up to three chunks are in
+ * flight at once, each on its own CUDA stream with its own work buffers. */
 void lc3plus_set_chunk_frames(int channel_frames);
 
 #ifdef __cplusplus
