@@ -335,7 +335,7 @@ static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_
                                  cudaMemcpyDeviceToHost, par));
         }
         CU(cudaEventRecord(g.pipe[p].done_ev, par));
-        g.launches += bits == 16 ? 7 : 5;
+        g.launches += (bits == 16 ? 7 : 5) + (N >= 160); /* frame lengths >= 160: tile MDCT kernel + lane-per-frame front end */
     }
     for (int p = 0; p < n_pipes; p++) CU(cudaStreamWaitEvent(g.stream, g.pipe[p].done_ev, 0));
     CU(cudaEventRecord(g.end_ev, g.stream));

@@ -1,11 +1,14 @@
 // Frame-parallel passes: one lane encodes the spectral half of one channel-frame.
 #pragma once
 #include "lc3_stages.cuh"
+#include "lc3_mdct_tile.cuh"
 
 namespace lc3k {
 
 // ---- spectral front end: fx/enc_lc3.c:83-84, :119-175 (+ the state-free half of :181-185)
-template <int N, int BITS> LC3_HD void front_body(const LC3K_Batch &b, int f, int tile, int lane)
+// TILE_MDCT: the MDCT has already been done by the tile kernel (lc3_mdct_tile.cuh), b.spec holds the spectrum and
+// fout[FO_D_EXP] its exponent.
+template <int N, int BITS, bool TILE_MDCT = false> LC3_HD void front_body(const LC3K_Batch &b, int f, int tile, int lane)
 {
     const int li = tile * LC3K_LANES + lane;
     if (li >= b.n_lanes) return;
@@ -18,8 +21,13 @@ template <int N, int BITS> LC3_HD void front_body(const LC3K_Batch &b, int f, in
     SV<i32> d = tile_view(b.spec, ft, N, lane);
     const i16 *bands = &rom_bands_offset[b.bands_off];
 
-    i32 w[N];
-    const i32 d_exp = mdct_frame<N>(xs, x_exp, &rom_win[b.W_off], b.W_len, b.mdct_mem_len, d, w);
+    SV<i32> fo = tile_view(b.fout, ft, FO_N, lane);
+    i32 d_exp;
+    if (TILE_MDCT) d_exp = fo[FO_D_EXP];
+    else {
+        i32 w[N];
+        d_exp = mdct_frame<N>(xs, x_exp, &rom_win[b.W_off], b.W_len, b.mdct_mem_len, d, w);
+    }
 
     i32 en[64];
     const i32 en_exp = band_energy(en, d, d_exp, bands, b.fs_idx, b.nbands, b.dms_idx);
@@ -48,7 +56,6 @@ template <int N, int BITS> LC3_HD void front_body(const LC3K_Batch &b, int f, in
     SV<i32> en4 = tile_view(b.en4, ft, N / 4, lane);
     const i32 x_max = gain_energies(d, d_exp, b.yLen, en4);
 
-    SV<i32> fo = tile_view(b.fout, ft, FO_N, lane);
     fo[FO_D_EXP] = d_exp; fo[FO_BW] = bw; fo[FO_TNS_BITS] = tns.bits; fo[FO_TNS_NFILT] = tns.nfilt;
     fo[FO_TNS_ORDER0] = tns.order[0]; fo[FO_TNS_ORDER1] = tns.order[1]; fo[FO_X_MAX] = x_max;
     for (int i = 0; i < 16; i++) fo[FO_TNS_IDX + i] = tns.idx[i];

@@ -1,21 +1,81 @@
-// spectral front-end kernel, instantiated per frame length in lc3_k_front_*.cu (split for parallel builds)
+// spectral front-end kernels, instantiated per frame length in lc3_k_front_*.cu (split for parallel builds)
 #pragma once
 #include <cuda_runtime.h>
 #include "lc3_body_frame.cuh"
 
 using namespace lc3k;
 
-template <int N, int BITS> __global__ void __launch_bounds__(128) k_front(LC3K_Batch b)
+template <int N, int BITS, bool TILE_MDCT> __global__ void __launch_bounds__(128, TILE_MDCT ? 6 : 4) k_front(LC3K_Batch b)
 {
     const int warp = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (warp >= b.n_frames * b.n_tiles) return;
-    front_body<N, BITS>(b, warp / b.n_tiles, warp % b.n_tiles, lane);
+    front_body<N, BITS, TILE_MDCT>(b, warp / b.n_tiles, warp % b.n_tiles, lane);
+}
+
+// MDCT of one tile (32 channel-frames) per block, spectrum in shared memory (lc3_mdct_tile.cuh).  In the twiddle,
+// leaf, column and post phases a warp only touches its own four frames (w, w+8, w+16, w+24), so warp-level
+// synchronisation is enough between them.
+template <int N, int BITS> __global__ void __launch_bounds__(256, 2) k_mdct(LC3K_Batch b)
+{
+    typedef MdctTile<N> G;
+    extern __shared__ __align__(16) i32 mt_smem[];
+    i32 *X = mt_smem, *mx = X + 32 * G::S, *mn = mx + G::PARTS * 32;
+    i16 *s_tw = (i16 *)(mn + G::PARTS * 32), *s_sn = s_tw + G::TW_LEN, *s_W = s_sn + G::SN_LEN;
+    const int f = blockIdx.x / b.n_tiles, tile = blockIdx.x % b.n_tiles, t = threadIdx.x, w = t >> 5, l = t & 31;
+    {
+        const MtTabs R = mt_rom_tabs<N>();
+        for (int i = t; i < G::TW_LEN; i += G::THREADS) s_tw[i] = R.tw[i];
+        for (int i = t; i < G::SN_LEN; i += G::THREADS) s_sn[i] = R.sn[i];
+        for (int i = t; i < G::W_LEN; i += G::THREADS) s_W[i] = R.W[i];
+    }
+    const MtTabs T = {s_tw, s_sn, s_W};
+    mt_fold<N, BITS>(b, f, tile, t, X, mx, mn);
+    __syncthreads();
+#pragma unroll 1
+    for (int j = 0; j < 4; j++) mt_pre<N>(X, mx, mn, w + 8 * j, l, T);
+    __syncwarp();
+    mt_leaf<N>(X, w + 8 * (l >> 3), l & 7);
+    __syncwarp();
+#pragma unroll 1
+    for (int j = 0; j < 4; j++) {
+        cpx o[8];
+        if (l < G::LEAF) mt_col_compute<N>(X, w + 8 * j, l, o, T);
+        __syncwarp();
+        if (l < G::LEAF) mt_col_store<N>(X, w + 8 * j, l, o);
+    }
+    __syncwarp();
+#pragma unroll 1
+    for (int j = 0; j < 4; j++) mt_post<N>(X, w + 8 * j, l, T);
+    __syncthreads();
+    mt_store<N>(b, f, tile, t, X, mx, mn);
 }
 
 template <int N> static int front_launch(const LC3K_Batch *b, cudaStream_t s)
 {
     const int warps = b->n_frames * b->n_tiles, blocks = (warps + 3) / 4;
-    if (b->bits == 16) k_front<N, 16><<<blocks, 128, 0, s>>>(*b);
-    else k_front<N, 24><<<blocks, 128, 0, s>>>(*b);
+    if (b->bits == 16) k_front<N, 16, false><<<blocks, 128, 0, s>>>(*b);
+    else k_front<N, 24, false><<<blocks, 128, 0, s>>>(*b);
+    return (int)cudaGetLastError();
+}
+
+// frame lengths with an 8-column FFT: tile MDCT kernel, then the rest of the front end one lane per channel-frame
+template <int N> static int front_launch_tiled(const LC3K_Batch *b, cudaStream_t s)
+{
+    static bool attr_set = false;
+    const size_t smem = MdctTile<N>::smem_bytes;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(k_mdct<N, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_mdct<N, 24>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return (int)e;
+        attr_set = true;
+    }
+    const int tiles = b->n_frames * b->n_tiles, blocks = (tiles + 3) / 4;
+    if (b->bits == 16) {
+        k_mdct<N, 16><<<tiles, 256, smem, s>>>(*b);
+        k_front<N, 16, true><<<blocks, 128, 0, s>>>(*b);
+    } else {
+        k_mdct<N, 24><<<tiles, 256, smem, s>>>(*b);
+        k_front<N, 24, true><<<blocks, 128, 0, s>>>(*b);
+    }
     return (int)cudaGetLastError();
 }

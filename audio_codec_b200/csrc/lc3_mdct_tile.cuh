@@ -1,0 +1,212 @@
+// Low-delay MDCT of one TILE (32 channel-frames) per thread block, spectrum resident in shared memory.
+//
+// Same arithmetic, operation for operation, as the lane-per-frame mdct_frame() (lc3_mdct.cuh; fx/mdct_fx.c:17-96,
+// fx/dct4_fx.c:16-138, fftN2 fx/fft.c:3364-3651) -- only the work-to-thread mapping differs.  The lane-per-frame
+// form makes ~9 passes over a 2 x N-word per-lane working set that lives in global/local memory; with ~75 000
+// lanes resident that set is far larger than L2 and every pass goes to DRAM (ncu: 9.5 GB per launch at C1).
+// Here a block of 256 threads owns the 32 frames of one tile, keeps them in shared memory and walks the phases
+//   fold      thread = (tile lane, 1/8 of the samples): window + aliasing fold, coalesced reads of the staged PCM
+//   twiddle   warp = frame, lane = pair of complex points: block shift + pre-twiddle
+//   leaf      thread = (frame, leaf): 8 leaf FFTs of length N/16 per frame, in registers, written back in place
+//   column    warp = frame, lane = column: radix-8 butterflies with twiddles (load all, sync, store all)
+//   post      warp = frame, lane = pair: post-twiddle
+//   store     thread = (tile lane, 1/8 of the bins): coalesced write into the tile-interleaved spectrum
+// Frame lengths with an 8-column FFT only (N = 160, 240, 320, 480); shorter frames keep the lane-per-frame path.
+//
+// Shared-memory row of a frame: complex point j at word 2j + 2(j >> 3) (one complex of padding per 8, so that the
+// 8 contiguous points a column task loads and the stride-8 points a leaf task loads are both conflict-free as
+// 64-bit accesses); row stride S = 2 mod 4 words so that the four frames of a warp's leaf tasks fall in disjoint
+// bank halves, and tile-lane-major access (fold, store) is at worst 2-way conflicted.
+#pragma once
+#include "lc3_mdct.cuh"
+#include "lc3_stages.cuh"
+
+namespace lc3k {
+
+template <int N> struct MdctTile {
+    static constexpr int M = N / 2, LEAF = M / 8;
+    static constexpr int ROW = N + 2 * LEAF;
+    static constexpr int S = ROW + ((6 - ROW % 4) % 4);
+    static constexpr int THREADS = 256, PARTS = THREADS / 32;
+    static constexpr int SC = (N % 3 == 0) ? (N == 480 ? 2 : 4) : (N == 320 ? 2 : 4); // twiddle stride of cfft<M> (lc3_fft.cuh)
+    static constexpr int WOFF = (N % 3 == 0) ? 60 : 40;
+    static constexpr int FFT_SCALE = (M == 240) ? 9 : 8;
+    // twiddle tables, copied to shared memory by the kernel: in this mapping their indices differ from lane to lane,
+    // which the constant cache serialises (one address per cycle); entries used: pre-twiddle N, post-twiddle
+    // 2 * (M/2) * step + 2, column twiddles up to SC * (M - 1) + 2 - WOFF
+    static constexpr int TW_LEN = N, SN_LEN = (N % 3 == 0) ? 482 : 322, W_LEN = 480;
+    static constexpr size_t smem_bytes = (size_t)(32 * S + 2 * PARTS * 32) * sizeof(i32) + (size_t)(TW_LEN + SN_LEN + W_LEN) * sizeof(i16);
+    static_assert(N == 160 || N == 240 || N == 320 || N == 480, "8-column FFT lengths only");
+};
+
+struct MtTabs { const i16 *tw, *sn, *W; };
+template <int N> LC3_HD MtTabs mt_rom_tabs()
+{
+    MtTabs T = {&rom_dct4_twiddle[rom_dct4_twiddle_off[TwSlot<N>::v]], (N % 3 == 0) ? rom_sin480 : rom_sin320,
+                (N % 3 == 0) ? rom_rot480 : rom_rot320};
+    return T;
+}
+
+LC3_HD int mt_ridx(int r) { return r + 2 * (r >> 4); }  // real index -> word in the padded row
+LC3_HD int mt_cidx(int j) { return 2 * j + 2 * (j >> 3); } // complex index -> word of its real part
+
+LC3_HD cpx mt_ld2(const i32 *p)
+{
+#if defined(__CUDA_ARCH__)
+    const int2 v = *reinterpret_cast<const int2 *>(p);
+    cpx c = {v.x, v.y};
+#else
+    cpx c = {p[0], p[1]};
+#endif
+    return c;
+}
+LC3_HD void mt_st2(i32 *p, cpx c)
+{
+#if defined(__CUDA_ARCH__)
+    *reinterpret_cast<int2 *>(p) = make_int2(c.re, c.im);
+#else
+    p[0] = c.re; p[1] = c.im;
+#endif
+}
+
+// block shift of frame fr from the per-part partial ranges
+template <int N> LC3_HD i32 mt_shift(const i32 *mx, const i32 *mn, int fr)
+{
+    Range r; range_init(r);
+    for (int p = 0; p < MdctTile<N>::PARTS; p++) { r.mx = imax(r.mx, mx[p * 32 + fr]); r.mn = imin(r.mn, mn[p * 32 + fr]); }
+    return imax(0, range_headroom32(r, 0));
+}
+
+// ---- fold: thread t = (lane of the tile, part)
+template <int N, int BITS> LC3_HD void mt_fold(const LC3K_Batch &b, int f, int tile, int t, i32 *X, i32 *mx, i32 *mn)
+{
+    typedef MdctTile<N> G;
+    constexpr int m = N / 2;
+    const int lane = t & 31, part = t >> 5, li = tile * LC3K_LANES + lane;
+    i32 *y = X + lane * G::S;
+    Range rg; range_init(rg);
+    if (li < b.n_lanes) {
+        SV<const i32> po = tile_view((const i32 *)b.pout, frame_tile(b, f, tile), PO_N, lane);
+        PcmView<BITS> xs = pcm_view<BITS>(b, tile, lane, f, po[PO_X_EXP]);
+        const i16 *win = &rom_win[b.W_off];
+        const int memLen = b.mdct_mem_len, z = 2 * N - b.W_len;
+        for (int i = part; i < m; i += G::PARTS) { // same three expressions as mdct_frame()
+            i32 v = xs(i - memLen) * win[i] - xs(2 * m - 1 - i - memLen) * win[2 * m - 1 - i];
+            y[mt_ridx(m + i)] = v; range_add(rg, v);
+            if (i < z) v = xs(2 * m - memLen + i) * win[2 * m + i];
+            else v = xs(2 * m - memLen + i) * win[2 * m + i] + xs(4 * m - memLen - 1 - i) * win[4 * m - 1 - i];
+            y[mt_ridx(m - 1 - i)] = v; range_add(rg, v);
+        }
+    } else {
+        for (int i = part; i < N; i += G::PARTS) y[mt_ridx(i)] = 0;
+    }
+    mx[part * 32 + lane] = rg.mx; mn[part * 32 + lane] = rg.mn;
+}
+
+// ---- block shift + pre-twiddle of frame fr: lane l takes pairs l, l+32, ...
+template <int N> LC3_HD void mt_pre(i32 *X, const i32 *mx, const i32 *mn, int fr, int l, const MtTabs &T)
+{
+    typedef MdctTile<N> G;
+    i32 *y = X + fr * G::S;
+    const i32 s = mt_shift<N>(mx, mn, fr);
+    const i16 *tw = T.tw;
+    for (int kk = l; kk < G::M / 2; kk += 32) {
+        const int lo = mt_ridx(2 * kk), hi = mt_ridx(N - 2 - 2 * kk);
+        const cpx p = mt_ld2(y + lo), q = mt_ld2(y + hi);
+        const i32 p0 = (i32)((u32)p.re << s), p1 = (i32)((u32)p.im << s), q0 = (i32)((u32)q.re << s), q1 = (i32)((u32)q.im << s);
+        i32 a1, a2, a3, a4;
+        cmul_half(a1, a2, q1, p0, tw[4 * kk], tw[4 * kk + 1]);
+        cmul_half(a3, a4, q0, p1, tw[4 * kk + 2], tw[4 * kk + 3]);
+        cpx o0 = {a2, a1}, o1 = {a4, l_neg(a3)};
+        mt_st2(y + lo, o0); mt_st2(y + hi, o1);
+    }
+}
+
+// ---- leaf FFT i (0..7) of frame fr, in place: point m of the leaf is complex point i + 8m of the frame
+template <int N> LC3_HD void mt_leaf(i32 *X, int fr, int i)
+{
+    typedef MdctTile<N> G;
+    i32 *y = X + fr * G::S + 2 * i;
+    fft_leaf<G::LEAF>(
+        [&](int m) { cpx c = mt_ld2(y + 18 * m); c.re >>= 5; c.im >>= 5; return c; },
+        [&](int m, cpx c) { mt_st2(y + 18 * m, c); });
+}
+
+// ---- column i (0..LEAF-1) of frame fr: output i of the 8 leaves = complex points 8i..8i+7
+template <int N> LC3_HD void mt_col_compute(const i32 *X, int fr, int i, cpx *o, const MtTabs &T)
+{
+    typedef MdctTile<N> G;
+    const i32 *y = X + fr * G::S + 18 * i;
+    const i16 *W = T.W;
+    cpx v[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        const cpx a = mt_ld2(y + 2 * k);
+        if (k == 0 || i == 0) {
+            v[k].re = a.re >> 1;
+            v[k].im = a.im >> 1;
+        } else {
+            const i32 c = W[G::SC * i + G::SC * k * G::LEAF - G::WOFF], d = W[G::SC * i + G::SC * k * G::LEAF + 1 - G::WOFF];
+            v[k].re = l_sub(mpy32x16(a.re, c), mpy32x16(a.im, d)) >> 1;
+            v[k].im = l_add(mpy32x16(a.re, d), mpy32x16(a.im, c)) >> 1;
+        }
+    }
+    dft8<false>(v, o);
+}
+template <int N> LC3_HD void mt_col_store(i32 *X, int fr, int i, const cpx *o)
+{
+    typedef MdctTile<N> G;
+    i32 *y = X + fr * G::S;
+#pragma unroll
+    for (int m = 0; m < 8; m++) mt_st2(y + mt_cidx(i + m * G::LEAF), o[m]);
+}
+
+// ---- post-twiddle of frame fr: lane l takes pairs l, l+32, ... (each pair touches only its own four words)
+template <int N> LC3_HD void mt_post(i32 *X, int fr, int l, const MtTabs &T)
+{
+    typedef MdctTile<N> G;
+    i32 *y = X + fr * G::S;
+    const i16 *sn = T.sn;
+    constexpr int step = (N % 3 == 0) ? 960 / N : 640 / N;
+    constexpr int M2 = G::M / 2 - 1;
+    for (int p = l; p <= M2; p += 32) {
+        const int lo = mt_ridx(2 * p), hi = mt_ridx(N - 2 - 2 * p);
+        const cpx L = mt_ld2(y + lo), H = mt_ld2(y + hi);
+        i32 a1, a2, a3, a4;
+        cpx oL, oH;
+        if (p == M2) {
+            cmul_half(a3, a4, L.im, L.re, sn[2 * p * step], sn[2 * p * step + 1]);
+            a1 = mpy32x16k(H.re, 23170) >> 1;
+            a2 = mpy32x16k(H.im, 23170) >> 1;
+            oH.re = l_add(a1, a2); oL.im = l_sub(a1, a2); oH.im = l_neg(a3); oL.re = a4;
+        } else {
+            cmul_half(a3, a4, H.re, H.im, sn[2 * (p + 1) * step], sn[2 * (p + 1) * step + 1]);
+            if (p == 0) { oH.im = l_neg(L.im >> 1); oL.re = L.re >> 1; }
+            else {
+                cmul_half(a1, a2, L.im, L.re, sn[2 * p * step], sn[2 * p * step + 1]);
+                oH.im = l_neg(a1); oL.re = a2;
+            }
+            oL.im = a3; oH.re = a4;
+        }
+        mt_st2(y + lo, oL); mt_st2(y + hi, oH);
+    }
+}
+
+// ---- store: thread t = (lane of the tile, part); also the block exponent of the frame
+template <int N> LC3_HD void mt_store(const LC3K_Batch &b, int f, int tile, int t, const i32 *X, const i32 *mx, const i32 *mn)
+{
+    typedef MdctTile<N> G;
+    const int lane = t & 31, part = t >> 5, li = tile * LC3K_LANES + lane;
+    if (li >= b.n_lanes) return;
+    const size_t ft = frame_tile(b, f, tile);
+    const i32 *y = X + lane * G::S;
+    SV<i32> d = tile_view(b.spec, ft, N, lane);
+    for (int e = part; e < N; e += G::PARTS) d[e] = y[mt_ridx(e)];
+    if (part == 0) {
+        const i32 x_exp = tile_view((const i32 *)b.pout, ft, PO_N, lane)[PO_X_EXP];
+        const i32 y_e = s_sub(s_sub(x_exp, 2), mt_shift<N>(mx, mn, lane));
+        tile_view(b.fout, ft, FO_N, lane)[FO_D_EXP] = s_add(s_add(y_e, G::FFT_SCALE), 2);
+    }
+}
+
+} // namespace lc3k

@@ -153,6 +153,7 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--streams", type=int, default=4096, help="streams per GPU")
     ap.add_argument("--frames", type=int, default=100, help="frames per stream per step")
+    ap.add_argument("--chunk", type=int, default=0, help="channel-frames per internal chunk (0: library default); profiling aid")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
@@ -190,6 +191,8 @@ def main():
     if rank:
         pcm = np.roll(pcm, 131 * rank, axis=1)
     encs = [ac.Encoder(FS, 1, DMS, BITRATE) for _ in range(S)]
+    if args.chunk:
+        ac.set_chunk_frames(args.chunk)
     d_pcm = torch.from_numpy(pcm).cuda()
     d_out = torch.zeros((S, F, NBYTES), dtype=torch.uint8, device="cuda")
 

@@ -29,6 +29,36 @@ template <int BITS> static void run_front(const LC3K_Batch &b, int f, int tile, 
     }
 }
 
+// the tile MDCT kernel (k_mdct in lc3_k_front.cuh), phase by phase, each phase a plain loop over the block's threads
+template <int N, int BITS> static void run_mdct_tile(const LC3K_Batch &b, int f, int tile)
+{
+    typedef MdctTile<N> G;
+    static std::vector<i32> sm(G::smem_bytes / sizeof(i32));
+    i32 *X = sm.data(), *mx = X + 32 * G::S, *mn = mx + G::PARTS * 32;
+    const MtTabs T = mt_rom_tabs<N>();
+    for (int t = 0; t < G::THREADS; t++) mt_fold<N, BITS>(b, f, tile, t, X, mx, mn);
+    for (int t = 0; t < G::THREADS; t++) { const int w = t >> 5, l = t & 31; for (int j = 0; j < 4; j++) mt_pre<N>(X, mx, mn, w + 8 * j, l, T); }
+    for (int t = 0; t < G::THREADS; t++) { const int w = t >> 5, l = t & 31; mt_leaf<N>(X, w + 8 * (l >> 3), l & 7); }
+    for (int w = 0; w < 8; w++)
+        for (int j = 0; j < 4; j++) {
+            cpx o[32][8];
+            for (int l = 0; l < G::LEAF; l++) mt_col_compute<N>(X, w + 8 * j, l, o[l], T);
+            for (int l = 0; l < G::LEAF; l++) mt_col_store<N>(X, w + 8 * j, l, o[l]);
+        }
+    for (int t = 0; t < G::THREADS; t++) { const int w = t >> 5, l = t & 31; for (int j = 0; j < 4; j++) mt_post<N>(X, w + 8 * j, l, T); }
+    for (int t = 0; t < G::THREADS; t++) mt_store<N>(b, f, tile, t, X, mx, mn);
+}
+template <int BITS> static void run_front_tile(const LC3K_Batch &b, int f, int tile)
+{ // same split as front_launch_tiled / front_launch
+    switch (b.N) {
+    case 160: run_mdct_tile<160, BITS>(b, f, tile); for (int l = 0; l < 32; l++) front_body<160, BITS, true>(b, f, tile, l); break;
+    case 240: run_mdct_tile<240, BITS>(b, f, tile); for (int l = 0; l < 32; l++) front_body<240, BITS, true>(b, f, tile, l); break;
+    case 320: run_mdct_tile<320, BITS>(b, f, tile); for (int l = 0; l < 32; l++) front_body<320, BITS, true>(b, f, tile, l); break;
+    case 480: run_mdct_tile<480, BITS>(b, f, tile); for (int l = 0; l < 32; l++) front_body<480, BITS, true>(b, f, tile, l); break;
+    default: for (int l = 0; l < 32; l++) run_front<BITS>(b, f, tile, l);
+    }
+}
+
 struct Sim {
     LC3Cfg cfg;
     int n_streams, n_slots;
@@ -145,10 +175,14 @@ extern "C" int hostsim_encode(void *p, const void *pcm, int bits, int n_frames, 
         }
     }
     for (int f = 0; f < n_frames; f++)
-        for (int tile = 0; tile < b.n_tiles; tile++)
-            for (int lane = 0; lane < 32; lane++) {
-                if (bits == 16) run_front<16>(b, f, tile, lane); else run_front<24>(b, f, tile, lane);
-            }
+        for (int tile = 0; tile < b.n_tiles; tile++) {
+            if (lane_serial) { // the original lane-per-frame MDCT for every frame length
+                for (int lane = 0; lane < 32; lane++) {
+                    if (bits == 16) run_front<16>(b, f, tile, lane); else run_front<24>(b, f, tile, lane);
+                }
+            } else if (bits == 16) run_front_tile<16>(b, f, tile);
+            else run_front_tile<24>(b, f, tile);
+        }
     if (lane_serial) {
         for (int tile = 0; tile < b.n_tiles; tile++)
             for (int lane = 0; lane < 32; lane++) rate_body(b, tile, lane, (const u8 *)rom_ari_lookup, rom_ari_bits);
