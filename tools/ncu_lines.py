@@ -1,11 +1,14 @@
 #!/usr/bin/env python3
-"""Aggregate an ncu report's per-SASS-instruction counters by CUDA source line.
+"""Aggregate an ncu report's per-SASS-instruction counters by CUDA source line and by pipeline stage.
 
     tools/ncu_lines.py <report.ncu-rep> <kernel regex> <mangled name substring> [top N]
 
 `ncu --page source --csv` lists SASS instructions in address order with "Instructions Executed" and stall
-samples; `nvdisasm -g -c` on the cubin extracted from liblc3plus_b200.so lists the same instructions with
-`//## File "...", line N` markers (nvcc -lineinfo).  The two listings are joined by position."""
+samples; `nvdisasm -gi -c` on the cubin extracted from liblc3plus_b200.so lists the same instructions with
+`//## File "...", line N inlined at "...", line M` chains (nvcc -lineinfo).  The two listings are joined by
+position.  Three views: by innermost line (where the instruction was written), by "stage frame" = the outermost
+frame of the inline chain that is not the kernel body/wrapper (which stage function called it), and the static
+SASS size of each stage (instruction-cache footprint)."""
 import csv
 import glob
 import os
@@ -16,6 +19,17 @@ import tempfile
 from collections import defaultdict
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+# frames that only dispatch: the stage is the first frame below them
+WRAPPERS = ("lc3_k_front.cuh", "lc3_k_back.cu", "lc3_k_stream.cu", "lc3_body_frame.cuh", "lc3_k_front_a.cu")
+BODIES = ("lc3_pitch_warp.cuh", "lc3_rate_warp.cuh")  # warp bodies: their own lines are the stages
+
+
+def src_line(cache, f, ln):
+    path = os.path.join(ROOT, "audio_codec_b200", "csrc", f)
+    if path not in cache:
+        cache[path] = open(path).read().splitlines() if os.path.exists(path) else []
+    L = cache[path]
+    return L[ln - 1].strip()[:84] if 0 < ln <= len(L) else ""
 
 
 def main():
@@ -38,67 +52,61 @@ def main():
     dis = []
     for cub in glob.glob(os.path.join(tmp, "*.cubin")):
         if mangled.encode() in open(cub, "rb").read():
-            dis = subprocess.run(["nvdisasm", "-g", "-c", cub], capture_output=True, text=True).stdout.splitlines()
+            dis = subprocess.run(["nvdisasm", "-gi", "-c", cub], capture_output=True, text=True).stdout.splitlines()
             if any(l.startswith(".text.") and mangled in l for l in dis):
                 break
     start = next(i for i, l in enumerate(dis) if l.startswith(".text.") and mangled in l)
-    lines = []
-    cur = ("?", 0)
-    stack = ""
+    chains = []          # per instruction: tuple of (file, line) frames, innermost first
+    cur, fresh = [], True
     for l in dis[start + 1:]:
         if l.startswith("\t.section") or l.startswith(".text."):
             break
-        m = re.search(r'//## File "([^"]+)", line (\d+)(.*)', l)
+        m = re.search(r'//## File "([^"]+)", line (\d+)', l)
         if m:
-            cur = (os.path.basename(m.group(1)), int(m.group(2)))
-            stack = m.group(3)
+            if fresh:
+                cur, fresh = [], False
+            cur.append((os.path.basename(m.group(1)), int(m.group(2))))
             continue
-        m = re.match(r"\s+/\*[0-9a-f]{4,}\*/\s+(.*?);", l)
-        if m:
-            lines.append(cur)
-    n = min(len(lines), len(sass))
-    if len(lines) != len(sass):
-        print(f"warning: {len(sass)} profiled vs {len(lines)} disassembled instructions", file=sys.stderr)
-    agg = defaultdict(lambda: [0, 0, 0])
-    tot_i = tot_s = 0
-    for k in range(n):
-        a = agg[lines[k]]
-        a[0] += sass[k][1]; a[1] += sass[k][2]; a[2] += 1
-        tot_i += sass[k][1]; tot_s += sass[k][2]
+        if re.match(r"\s+/\*[0-9a-f]{4,}\*/\s+(.*?);", l):
+            chains.append(tuple(cur) if cur else (("?", 0),))
+            fresh = True
+    n = min(len(chains), len(sass))
+    if len(chains) != len(sass):
+        print(f"warning: {len(sass)} profiled vs {len(chains)} disassembled instructions", file=sys.stderr)
+
+    def stage_of(ch):
+        # the call site in the kernel body: innermost frame that lies in a body/wrapper file
+        for fr in ch:
+            if fr[0] in WRAPPERS or fr[0] in BODIES:
+                return fr
+        return ch[-1]
+
+    def below_stage(ch):
+        # the line of the stage function itself: the frame just inside the call site
+        for i, fr in enumerate(ch):
+            if fr[0] in WRAPPERS or fr[0] in BODIES:
+                return ch[i - 1] if i > 0 else fr
+        return ch[0]
+
+    tot_i = sum(s[1] for s in sass[:n])
+    tot_s = sum(s[2] for s in sass[:n])
     print(f"total warp instructions {tot_i}, stall samples {tot_s}, SASS instructions {n}")
-    byfile = defaultdict(lambda: [0, 0])
-    for (f, ln), a in agg.items():
-        byfile[f][0] += a[0]; byfile[f][1] += a[1]
-    for f, a in sorted(byfile.items(), key=lambda x: -x[1][0]):
-        print(f"  {f:28s} inst {100 * a[0] / max(tot_i, 1):5.1f}%  samples {100 * a[1] / max(tot_s, 1):5.1f}%")
-    # primitives (lc3_basop/lc3_math/intrinsics) carry no inline stack in the line table: attribute them to the
-    # nearest preceding line of stage code
-    prim = ("lc3_basop.cuh", "lc3_math.cuh", "lc3_warp.cuh", "sm_30_intrinsics.hpp", "sm_80_rt.hpp")
-    owner, bycaller, bycl = ("?", 0), defaultdict(lambda: [0, 0]), defaultdict(lambda: [0, 0])
+    inner, stage, stagefile = defaultdict(lambda: [0, 0, 0]), defaultdict(lambda: [0, 0, 0]), defaultdict(lambda: [0, 0, 0])
     for k in range(n):
-        if lines[k][0] not in prim:
-            owner = lines[k]
-        bycaller[owner[0]][0] += sass[k][1]; bycaller[owner[0]][1] += sass[k][2]
-        bycl[owner][0] += sass[k][1]; bycl[owner][1] += sass[k][2]
-    print("by stage file (primitives attributed to the nearest preceding stage line):")
-    for f, a in sorted(bycaller.items(), key=lambda x: -x[1][0]):
-        print(f"  {f:28s} inst {100 * a[0] / max(tot_i, 1):5.1f}%  samples {100 * a[1] / max(tot_s, 1):5.1f}%")
-    print("top stage lines incl. their primitives:")
-    for (f, ln), a in sorted(bycl.items(), key=lambda x: -x[1][0])[:top // 2]:
-        path = os.path.join(ROOT, "audio_codec_b200", "csrc", f)
-        txt = ""
-        if os.path.exists(path):
-            L = open(path).read().splitlines()
-            txt = L[ln - 1].strip()[:80] if 0 < ln <= len(L) else ""
-        print(f"  {f}:{ln:<4d} inst {100 * a[0] / max(tot_i, 1):5.1f}%  samp {100 * a[1] / max(tot_s, 1):5.1f}% | {txt}")
-    print("top lines by executed instructions:")
-    src_cache = {}
-    for (f, ln), a in sorted(agg.items(), key=lambda x: -x[1][0])[:top]:
-        path = os.path.join(ROOT, "audio_codec_b200", "csrc", f)
-        if path not in src_cache:
-            src_cache[path] = open(path).read().splitlines() if os.path.exists(path) else []
-        text = src_cache[path][ln - 1].strip()[:90] if 0 < ln <= len(src_cache[path]) else ""
-        print(f"  {f}:{ln:<4d} inst {100 * a[0] / max(tot_i, 1):5.1f}%  samp {100 * a[1] / max(tot_s, 1):5.1f}%  sass {a[2]:4d} | {text}")
+        for d, key in ((inner, chains[k][0]), (stage, stage_of(chains[k])), (stagefile, below_stage(chains[k]))):
+            a = d[key]
+            a[0] += sass[k][1]; a[1] += sass[k][2]; a[2] += 1
+    cache = {}
+    pct = lambda a: f"inst {100 * a[0] / max(tot_i, 1):5.1f}%  samp {100 * a[1] / max(tot_s, 1):5.1f}%  sass {a[2]:5d}"
+    print("by call site in the kernel body (everything inlined below it included; exact, from the inline chain):")
+    for (f, ln), a in sorted(stage.items(), key=lambda x: -x[1][0])[:top]:
+        print(f"  {f}:{ln:<4d} {pct(a)} | {src_line(cache, f, ln)}")
+    print("by line of the stage function called from the body (its callees included):")
+    for (f, ln), a in sorted(stagefile.items(), key=lambda x: -x[1][0])[:top]:
+        print(f"  {f}:{ln:<4d} {pct(a)} | {src_line(cache, f, ln)}")
+    print("top innermost lines:")
+    for (f, ln), a in sorted(inner.items(), key=lambda x: -x[1][0])[:top]:
+        print(f"  {f}:{ln:<4d} {pct(a)} | {src_line(cache, f, ln)}")
 
 
 if __name__ == "__main__":
