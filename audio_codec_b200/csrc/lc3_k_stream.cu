@@ -52,7 +52,7 @@ template <class T> __global__ void __launch_bounds__(256) k_stage(LC3K_Batch b)
 }
 
 // per-stream passes: one warp per channel-stream, 4 streams per block
-template <int BITS, bool PRE> __global__ void __launch_bounds__(128, 6) k_pitch(LC3K_Batch b)
+template <int BITS, bool PRE> __global__ void __launch_bounds__(128, 7) k_pitch(LC3K_Batch b)
 {
     __shared__ PitchShared sh[4];
     const int w = threadIdx.x >> 5;
