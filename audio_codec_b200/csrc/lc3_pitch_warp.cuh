@@ -25,9 +25,10 @@ struct PitchShared {
     i16 s12[24 + 128 + 8];        // [24-sample delay line | new 12.8 kHz samples]
     i16 fir[128];                 // resampler output before the high-pass
     i16 m12[4];                   // olpa_mem_s12k8
-    i16 olpa[2][130 + 64 + 2];    // 6.4 kHz history + new samples, ping-pong
-    i16 ltpf[2][264 + 128 + 4];   // 12.8 kHz history + new samples, ping-pong
+    i16 olpa[2][4 + 130 + 64 + 2]; // 6.4 kHz history + new samples, ping-pong; 4 samples of pad in front (phase E reads 2 of them)
+    i16 ltpf[2][4 + 264 + 128 + 4]; // 12.8 kHz history + new samples, ping-pong; 4 samples of pad in front (lag windows read 3)
     i16 ac[32];                   // LTPF normalised correlations
+    i32 xc[128];                  // LTPF cross-correlation partial sums [lane][4 lags]
     i16 dd[2 + 160 + 2];          // attack detector: decimated signal, two samples of history first
 };
 
@@ -66,8 +67,8 @@ template <int BITS, bool PRE> LC3_HD void pitch_warp_body(const LC3K_Batch &b, i
         for (int k = l; k < 240; k += 32) sh.filt[k] = rom_resamp_filt[b.fs_idx * 240 + k];
         if (l < 24) sh.s12[l] = s16[S16_MEM_OUT + l];
         if (l < 3) sh.m12[l] = s16[S16_OLPA_S12 + l];
-        for (int k = l; k < olpa_len; k += 32) sh.olpa[0][k] = s16[S16_OLPA_BUF + k];
-        for (int k = l; k < lt_len; k += 32) sh.ltpf[0][k] = s16[S16_LTPF_BUF + k];
+        for (int k = l; k < olpa_len; k += 32) sh.olpa[0][4 + k] = s16[S16_OLPA_BUF + k];
+        for (int k = l; k < lt_len; k += 32) sh.ltpf[0][4 + k] = s16[S16_LTPF_BUF + k];
     LC3_LANES_END
     i32 m0 = st[ST_MEM50_0], m1 = st[ST_MEM50_1];
     i32 olpa_exp = st[ST_OLPA_EXP], olpa_pitch = st[ST_OLPA_PITCH];
@@ -178,7 +179,7 @@ template <int BITS, bool PRE> LC3_HD void pitch_warp_body(const LC3K_Batch &b, i
 
         // ---- D. OLPA: 2:1 decimation with a 5-tap low-pass (olpa_fx.c:36-58): lane = 6.4 kHz sample.
         //         v[j] = m12[3 + j] for j < 0, s12[j] otherwise; output k uses v[2k-3 .. 2k+1].
-        i16 *omem = sh.olpa[ob], *s6 = omem + olpa_len;
+        i16 *omem = sh.olpa[ob] + 4, *s6 = omem + olpa_len;
         LC3_LANES(l)
             for (int k = l; k < len2; k += 32) {
                 i32 v[5];
@@ -219,14 +220,33 @@ template <int BITS, bool PRE> LC3_HD void pitch_warp_body(const LC3K_Batch &b, i
             // ---- E. autocorrelation, lags 17..114: lane = lag (olpa_fx.c:101-122, :157-172)
             const i16 *s = dms == 25 ? s6 - 16 : s6;
             const i32 lo = s_max(17, s_sub(olpa_pitch, 4)), hi = s_min(114, s_add(olpa_pitch, 4));
+            // Each lane takes four consecutive lags and slides a four-sample window of the lagged signal through
+            // registers: two shared-memory loads per four products.  (Lanes 0..24 cover lags 17..116; the two lags
+            // past 114 read the pad in front of the history and are dropped.)
             LC3_LANES(l)
                 i64 kw = LC3_I32_MIN * (i64)4294967296LL, k2 = kw;
-                for (int n = 17 + l; n <= 114; n += 32) {
-                    i32 acc = 0; // <= 80 products of |v| <= 2^12 operands: below 2^31, the L_mac0 chain cannot saturate
-                    for (int m = 0; m < acflen6; m++) acc += s[m] * s[m - n];
-                    const i64 a = argmax_key(mpy32x16(acc, rom_olpa_weight[n - 17]), n);
-                    kw = a > kw ? a : kw;
-                    if (n >= lo && n <= hi) { const i64 c = argmax_key(acc, n); k2 = c > k2 ? c : k2; }
+                const int n0 = 17 + 4 * l;
+                if (n0 <= 114) {
+                    // <= 80 products of |v| <= 2^12 operands: below 2^31, the L_mac0 chain cannot saturate
+                    i32 a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+                    const i16 *q = s - n0; // q[m - j] = s[m - (n0 + j)]
+                    i32 w1 = q[-1], w2 = q[-2], w3 = q[-3];
+#pragma unroll 4
+                    for (int m = 0; m < acflen6; m++) {
+                        const i32 x = s[m], w0 = q[m];
+                        a0 += x * w0; a1 += x * w1; a2 += x * w2; a3 += x * w3;
+                        w3 = w2; w2 = w1; w1 = w0;
+                    }
+                    const i32 accs[4] = {a0, a1, a2, a3};
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        const int n = n0 + j;
+                        if (n > 114) break;
+                        const i32 acc = accs[j];
+                        const i64 a = argmax_key(mpy32x16(acc, rom_olpa_weight[n - 17]), n);
+                        kw = a > kw ? a : kw;
+                        if (n >= lo && n <= hi) { const i64 c = argmax_key(acc, n); k2 = c > k2 ? c : k2; }
+                    }
                 }
                 sh.red.q[l] = kw;
                 sh.red.q2[l] = k2;
@@ -252,7 +272,7 @@ template <int BITS, bool PRE> LC3_HD void pitch_warp_body(const LC3K_Batch &b, i
             olpa_pitch = p;
             pitch = s_shl(p, 1);
             // history for the next frame goes to the other buffer
-            i16 *onext = sh.olpa[ob ^ 1];
+            i16 *onext = sh.olpa[ob ^ 1] + 4;
             LC3_LANES(l)
                 for (int k = l; k < olpa_len; k += 32) onext[k] = omem[k + len2];
             LC3_LANES_END
@@ -262,7 +282,7 @@ template <int BITS, bool PRE> LC3_HD void pitch_warp_body(const LC3K_Batch &b, i
         // ---- G. LTPF (ltpf_coder_fx.c:17-307)
         i32 ltpf_bits, lt0 = 0, lt1 = 0, lt2 = 0, nc_ltpf, pitch_ltpf = 0, active = 0;
         {
-            i16 *lmem = sh.ltpf[lb], *x = lmem + lt_len;
+            i16 *lmem = sh.ltpf[lb] + 4, *x = lmem + lt_len;
             LC3_LANES(l)
                 for (int k = l; k <= len; k += 32) x[k] = sh.s12[k];
             LC3_LANES_END
@@ -307,19 +327,51 @@ template <int BITS, bool PRE> LC3_HD void pitch_warp_body(const LC3K_Batch &b, i
                 const i32 n1 = l_norm(sum1);
                 sum1 = l_shl(sum1, n1);
 
-                LC3_LANES(l) // lane = candidate lag: cross-correlation, sliding lagged energy, normalisation
+                // cross-correlations of the <= 17 candidate lags: lane = (four consecutive lags, one sixth of the samples),
+                // a four-sample window of the lagged signal slides through registers.  A segment has <= 22 products of
+                // |v| <= 2^12 operands, so its partial sums fit 32 bits; the six partials are added exactly below.
+                const int seg_len = (acflen + 5) / 6;
+                LC3_LANES(l)
+                    const int qd = l / 6, sg = l - 6 * qd;
+                    i32 a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+                    i64 e_all = 0;
+                    if (qd < 5) {
+                        const int m_lo = sg * seg_len, m_hi = imin(acflen, m_lo + seg_len);
+                        const i16 *q = xp - (ac_lo + 4 * qd); // q[m - j] = xp[m - (ac_lo + 4 qd + j)]
+                        i32 w1 = q[m_lo - 1], w2 = q[m_lo - 2], w3 = q[m_lo - 3];
+                        for (int m = m_lo; m < m_hi; m++) {
+                            const i32 x = xp[m], w0 = q[m];
+                            a0 += x * w0; a1 += x * w1; a2 += x * w2; a3 += x * w3;
+                            w3 = w2; w2 = w1; w1 = w0;
+                        }
+                    }
+                    sh.xc[4 * l] = a0; sh.xc[4 * l + 1] = a1; sh.xc[4 * l + 2] = a2; sh.xc[4 * l + 3] = a3;
+                    // energy of every sample any lagged window touches (bounds all window energies from above)
+                    for (int m = -ac_hi + l; m < acflen - ac_lo; m += 32) { const i32 v = xp[m]; e_all += v * v; }
+                    sh.red.q[l] = e_all;
+                    // change of the lagged window's energy from lag n-1 to lag n = ac_lo + l (ltpf_coder_fx.c:116-120)
+                    i32 dlt = 0;
+                    if (l >= 1 && l < nlags) { const i32 o = xp[acflen - (ac_lo + l)], w = xp[-(ac_lo + l)]; dlt = w * w - o * o; }
+                    sh.red.a[l] = dlt;
+                LC3_LANES_END
+                // If even the union of the windows has an energy below 2^31, no window energy and no intermediate of the
+                // reference's L_msu0/L_mac0 chain can saturate, and the chain is a plain prefix sum.
+                const bool plain = 1 + warp_sum64(sh.red.q) <= (i64)LC3_I32_MAX;
+                LC3_LANES(l) // lane = candidate lag
                     if (l < nlags) {
-                        const int n = ac_lo + l;
-                        // <= 128 products of |v| <= 2^12 operands: only the last term can reach +-2^31, so the
-                        // saturating chain equals the clamped exact sum
+                        const int n = ac_lo + l, qd = l >> 2, j = l & 3;
                         i64 s64 = 0;
-                        for (int m = 0; m < acflen; m++) s64 += (i64)xp[m] * xp[m - n];
+                        for (int sg = 0; sg < 6; sg++) s64 += sh.xc[4 * (6 * qd + sg) + j];
                         const i32 s0 = clamp64(s64);
                         i32 s2 = sum2_0;
-                        for (int q = ac_lo + 1; q <= n; q++) { // slide the window one sample per lag (ltpf_coder_fx.c:116-120)
-                            const i32 o = xp[acflen - 1 - (q - 1)], w = xp[-q];
-                            s2 = l_msu0(s2, o, o);
-                            s2 = l_mac0(s2, w, w);
+                        if (plain) {
+                            for (int k = 1; k <= l; k++) s2 += sh.red.a[k];
+                        } else {
+                            for (int q = ac_lo + 1; q <= n; q++) {
+                                const i32 o = xp[acflen - 1 - (q - 1)], w = xp[-q];
+                                s2 = l_msu0(s2, o, o);
+                                s2 = l_mac0(s2, w, w);
+                            }
                         }
                         sh.ac[l] = (i16)normcorr_q15(s0, sum1, s2, 1, n1);
                     }
@@ -385,7 +437,7 @@ template <int BITS, bool PRE> LC3_HD void pitch_warp_body(const LC3K_Batch &b, i
                 nc_ltpf = normcorr;
                 ltpf_bits = 1;
             }
-            i16 *lnext = sh.ltpf[lb ^ 1];
+            i16 *lnext = sh.ltpf[lb ^ 1] + 4;
             LC3_LANES(l)
                 for (int k = l; k < lt_len; k += 32) lnext[k] = lmem[k + len];
             LC3_LANES_END
@@ -480,8 +532,8 @@ template <int BITS, bool PRE> LC3_HD void pitch_warp_body(const LC3K_Batch &b, i
     LC3_LANES(l)
         if (l < 24) s16[S16_MEM_OUT + l] = sh.s12[l];
         if (l < 3) s16[S16_OLPA_S12 + l] = sh.m12[l];
-        for (int k = l; k < olpa_len; k += 32) s16[S16_OLPA_BUF + k] = sh.olpa[ob][k];
-        for (int k = l; k < lt_len; k += 32) s16[S16_LTPF_BUF + k] = sh.ltpf[lb][k];
+        for (int k = l; k < olpa_len; k += 32) s16[S16_OLPA_BUF + k] = sh.olpa[ob][4 + k];
+        for (int k = l; k < lt_len; k += 32) s16[S16_LTPF_BUF + k] = sh.ltpf[lb][4 + k];
         if (l == 0 && !PRE) { st[ST_MEM50_0] = m0; st[ST_MEM50_1] = m1; }
         if (l == 0) {
             st[ST_ATT_F0] = as.filter_mem[0]; st[ST_ATT_F1] = as.filter_mem[1]; st[ST_ATT_DET] = as.detected;

@@ -77,23 +77,28 @@ LC3_HD void rate_warp_body(const LC3K_Batch &b, int li, RateShared &sh, const u8
             for (int it = 0; it < 8; it++) {
                 fac = fac >> 1;
                 offset = l_sub(offset, fac);
+                // One pass: every quadruple at or above the threshold adds its own cost; the ones below it cost
+                // 0x3C7AE each, but only underneath the highest one above it -- and there are
+                // top + 1 - (number above) of those, so they need no second pass.
                 LC3_LANES(l)
-                    i32 top = -1;
-                    for (int i = l; i < lg4; i += 32)
-                        if (l_sub(sh.en[i], offset) >= 0x9CCCD) top = i;
-                    sh.red.a[l] = top;
-                LC3_LANES_END
-                const i32 top = warp_max(sh.red.a);
-                LC3_LANES(l)
+                    i32 top = -1, cnt = 0;
                     i64 est = 0;
                     for (int i = l; i < lg4; i += 32) {
                         const i32 t = l_sub(sh.en[i], offset);
-                        if (t < 0x9CCCD) { if (i < top) est += 0x3C7AE; }
-                        else { est += t; const i32 d2 = l_sub(t, 0x460000); if (d2 >= 0) est += d2; }
+                        if (t >= 0x9CCCD) {
+                            top = i; cnt++;
+                            est += t;
+                            const i32 d2 = l_sub(t, 0x460000);
+                            if (d2 >= 0) est += d2;
+                        }
                     }
-                    sh.red.q[l] = est;
+                    // a lane holds at most 4 quadruples, each term < 2^33: the total splits into two 32-bit sums
+                    sh.red.a[l] = (i32)(est & 0xFFFFF); sh.red.b[l] = (i32)(est >> 20); sh.red.c[l] = cnt; sh.red.d[l] = top;
                 LC3_LANES_END
-                const i32 est = clamp64(warp_sum64(sh.red.q));
+                const i32 top = warp_max(sh.red.d);
+                i64 est64 = ((i64)warp_sum(sh.red.b) << 20) + warp_sum(sh.red.a);
+                if (top >= 0) est64 += (i64)0x3C7AE * (top + 1 - warp_sum(sh.red.c));
+                const i32 est = clamp64(est64);
                 if (est > target && top >= 0) offset = l_add(offset, fac);
             }
             const i32 g = hi16(offset);
