@@ -12,9 +12,10 @@
 
 #define LC3B_MAGIC 0x4c433362u
 #define N_PIPES 3
-enum { K_STAGE = 0, K_FIR, K_SCALAR, K_PITCH, K_FRONT, K_RATE, K_BACK, N_KERNELS };
+#define N_WORK 8
+enum { K_STAGE = 0, K_FIR, K_SCALAR, K_PITCH, K_FRONT, K_RATE, K_QUANT, K_BACK, N_KERNELS };
 /* kernels that read and write per-stream state: chunk c+1's launch must wait for chunk c's */
-static const int k_stateful[N_KERNELS] = {1 /* input history */, 0, 1 /* high-pass memory */, 1, 0, 1 /* rate-loop feedback */, 0};
+static const int k_stateful[N_KERNELS] = {1 /* input history */, 0, 1 /* high-pass memory */, 1, 0, 1 /* rate-loop feedback */, 0, 0};
 
 struct LC3_Enc { /* lives in the caller's block; device state is referenced by slot */
     uint32_t magic;
@@ -43,7 +44,7 @@ typedef struct {
     /* chunk pipeline: N_PIPES chunks of frames in flight, each on its own stream with its own work buffers */
     struct {
         cudaStream_t par, ser;  /* frame-parallel kernels + copies | per-stream (stateful) kernels, higher priority */
-        size_t work_cap[7]; void *work[7];
+        size_t work_cap[N_WORK]; void *work[N_WORK];
         cudaEvent_t state_ev[N_KERNELS], hop_ev[N_KERNELS + 2], done_ev;
     } pipe[N_PIPES];
     cudaEvent_t start_ev, end_ev;
@@ -279,10 +280,10 @@ static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_
     fc = (n_frames + n_chunks - 1) / n_chunks;
     const int n_pipes = n_chunks < N_PIPES ? n_chunks : N_PIPES;
     const size_t ftl = (size_t)fc * b.n_tiles * 32;
-    const size_t need[7] = {(size_t)b.n_tiles * 32 * (size_t)(fc + 1) * N * sb, ftl * PO_N * 4, ftl * N * 4, ftl * FO_N * 4,
-                            ftl * (N / 4) * 4, ftl * RO_N * 4, ftl * 128 * 2};
+    const size_t need[N_WORK] = {(size_t)b.n_tiles * 32 * (size_t)(fc + 1) * N * sb, ftl * PO_N * 4, ftl * N * 4, ftl * FO_N * 4,
+                                 ftl * (N / 4) * 4, ftl * RO_N * 4, ftl * 128 * 2, ftl * N * 2};
     for (int p = 0; p < n_pipes; p++)
-        for (int i = 0; i < 7; i++)
+        for (int i = 0; i < N_WORK; i++)
             if (ensure(&g.pipe[p].work[i], &g.pipe[p].work_cap[i], need[i], 0)) return 1;
 
     const int EPC = 2 * N_KERNELS; /* profiling events per chunk: one before and one after every kernel */
@@ -293,7 +294,7 @@ static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_
         for (; g.n_ev < n_chunks * EPC; g.n_ev++) CU(cudaEventCreate(&g.ev[g.n_ev]));
     }
     int (*const launch[N_KERNELS])(const LC3K_Batch *, void *) = {lc3k_launch_stage, lc3k_launch_fir, lc3k_launch_scalar, lc3k_launch_pitch,
-                                                                  lc3k_launch_front, lc3k_launch_rate, lc3k_launch_back};
+                                                                  lc3k_launch_front, lc3k_launch_rate, lc3k_launch_quant, lc3k_launch_back};
     /* everything queued on the main stream so far (state reset, configuration, lane tables, whole-buffer input copy)
      * is ordered before the first chunk of every pipe */
     CU(cudaEventRecord(g.start_ev, g.stream));
@@ -306,7 +307,7 @@ static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_
         b.frame0 = f0;
         b.n_frames = n_frames - f0 < fc ? n_frames - f0 : fc;
         b.pcm_t = w[0]; b.pout = (int32_t *)w[1]; b.spec = (int32_t *)w[2]; b.fout = (int32_t *)w[3];
-        b.en4 = (int32_t *)w[4]; b.rout = (int32_t *)w[5]; b.r12 = (int16_t *)w[6];
+        b.en4 = (int32_t *)w[4]; b.rout = (int32_t *)w[5]; b.r12 = (int16_t *)w[6]; b.xq = (int16_t *)w[7];
         cudaStream_t cur = par;
         if (cp && cp->h_pcm) /* this chunk's columns of every stream's PCM rows, one rectangle per channel */
             for (int ch = 0; ch < c0->channels; ch++) {
@@ -335,7 +336,7 @@ static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_
                                  cudaMemcpyDeviceToHost, par));
         }
         CU(cudaEventRecord(g.pipe[p].done_ev, par));
-        g.launches += (bits == 16 ? 7 : 5) + (N >= 160); /* frame lengths >= 160: tile MDCT kernel + lane-per-frame front end */
+        g.launches += (bits == 16 ? 8 : 6) + (N >= 160); /* frame lengths >= 160: tile MDCT kernel + lane-per-frame front end */
     }
     for (int p = 0; p < n_pipes; p++) CU(cudaStreamWaitEvent(g.stream, g.pipe[p].done_ev, 0));
     CU(cudaEventRecord(g.end_ev, g.stream));

@@ -151,8 +151,10 @@ LC3_HD void enc_sym(RangeCoder &s, const AriTabs &T, int ctx, int sym)
 LC3_HD i32 res_bit(const u32 *res, int i) { return (i32)((res[i >> 5] >> (i & 31)) & 1u); }
 
 // fx/ari_codec.c:94-406.  lsbs: scratch for the diverted LSB plane (2*L bits, packed).
-template <class XQ, class CD>
-LC3_HD void ari_encode(u8 *bytes, BackWriter &w, i32 nbbits, XQ xq, const TnsOut &tns, i32 lastnz, CD cd,
+// The context / escape level / MSB symbol of each tuple (the reference's codingdata[], written by its quantiser,
+// fx/quantize_spec_fx.c:100-190) are recomputed here from the quantised bins as the loop goes.
+template <class XQ>
+LC3_HD void ari_encode(u8 *bytes, BackWriter &w, i32 nbbits, XQ xq, int nt, i32 rateFlag, const TnsOut &tns, i32 lastnz,
                        const u32 *res, i32 nres, i32 lsbMode, int lpc_weighting, const AriTabs &T, u32 *lsbs)
 {
     int nlsbs = 0;
@@ -174,17 +176,31 @@ LC3_HD void ari_encode(u8 *bytes, BackWriter &w, i32 nbbits, XQ xq, const TnsOut
         }
     }
 
-    for (int k = 0, ci = 0; k < lastnz; k += 2, ci += 3) {
-        const i32 a = xq[k], b = xq[k + 1], lev = cd[ci + 1], msb = cd[ci + 2];
-        const int ctx = cd[ci];
-        if (lev < 0) { enc_sym(s, T, ctx, 0); continue; }
+    const int nt_half = nt >> 1;
+    i32 c = 0;
+    for (int k = 0; k < lastnz; k += 2) {
+        const i32 a = xq[k], b = xq[k + 1];
+        const i32 a1 = s_abs(a), b1 = s_abs(b), mx = imax(a1, b1);
+        int ctx = c + rateFlag;
+        if (k > nt_half) ctx += 1 << 8;
+        if (mx == 0) { enc_sym(s, T, ctx, 0); c = ((c & 0xf) << 4) + 1; continue; }
+        i32 lev, msb;
+        if (mx < 4) {
+            lev = 0; msb = a1 + (b1 << 2);
+            c = ((c & 0xf) << 4) + a1 + b1 + 1;
+        } else if (mx < 8) {
+            lev = 1; msb = (a1 >> 1) + ((b1 >> 1) << 2);
+            c = ((c & 0xf) << 4) + 2 * ((a1 >> 1) + (b1 >> 1)) + 1;
+        } else {
+            lev = 13 - s_norm(mx); msb = (a1 >> lev) + ((b1 >> lev) << 2);
+            c = ((c & 0xf) << 4) + 12 + imin(lev, 3);
+        }
         if (lev == 0) {
             enc_sym(s, T, ctx, msb);
             if (a != 0) put_bit(w, (a >> 15) & 1);
             if (b != 0) put_bit(w, (b >> 15) & 1);
             continue;
         }
-        const i32 a1 = s_abs(a), b1 = s_abs(b);
         if (lsbMode == 0) {
             for (int l = 0; l < lev; l++) { // escape symbol + one LSB plane per level
                 enc_sym(s, T, ctx + rom_ari_esc_nb[l < 3 ? l : 3], 16);

@@ -63,7 +63,7 @@ template <int N, int BITS, bool TILE_MDCT = false> LC3_HD void front_body(const 
 }
 
 // ---- back end: fx/enc_lc3.c:196-242 (adjust gain, final quantisation, residual, noise factor, entropy coding)
-LC3_HD void back_body(const LC3K_Batch &b, int f, int tile, int lane, const AriTabs &T, const uint16_t *ari_bitstab)
+LC3_HD void back_body(const LC3K_Batch &b, int f, int tile, int lane, const AriTabs &T)
 {
     const int li = tile * LC3K_LANES + lane;
     if (li >= b.n_lanes) return;
@@ -78,14 +78,13 @@ LC3_HD void back_body(const LC3K_Batch &b, int f, int tile, int lane, const AriT
     const i32 lpc_weighting = cfg[CFG_LPC_WEIGHTING];
     const i32 d_exp = fo[FO_D_EXP], bw = fo[FO_BW], tbits_quant = ro[RO_TBITS_QUANT];
 
-    i32 qgain = ro[RO_QGAIN], gain, gain_e;
+    // gain index after adjustment, quantised bins and their summary come from the tile quantiser (lc3_quant_tile.cuh)
+    const i32 qgain = ro[RO_QGAIN];
+    i32 gain, gain_e;
     gain_from_index(s_add(qgain, qgain_off), gain, gain_e);
-    const int change = adjust_gain(qgain, ro[RO_QGAIN_MIN], qgain_off, gain, gain_e, tbits_quant, ro[RO_NBITS1], b.fs_idx);
-
-    i16 xq[LC3K_MAX_N], cd[3 * LC3K_MAX_N / 2];
+    SV<const i16> xq = tile_view((const i16 *)b.xq, ft, b.N, lane);
     QuantOut q;
-    quantize<true>(q, d, d_exp, gain, gain_e, xq, b.yLen, tbits_quant, total_bits, b.fs_idx, cd, change ? 0 : -1,
-                   T.lut, ari_bitstab);
+    q.lastnz = ro[RO_LASTNZ]; q.lsbMode = ro[RO_LSBMODE]; q.nBits2 = ro[RO_NBITS2]; q.nBits = 0;
 
     u32 res[LC3K_MAX_N / 32 + 1], lsbs[2 * LC3K_MAX_N / 32 + 1];
     i32 nres = 0;
@@ -109,7 +108,8 @@ LC3_HD void back_body(const LC3K_Batch &b, int f, int tile, int lane, const AriT
     for (int i = 0; i < target_bytes; i++) bytes[i] = 0;
     BackWriter w;
     side_info(w, bytes, total_bits, b.yLen, si, b.fs_idx);
-    ari_encode(bytes, w, total_bits, xq, tns, q.lastnz, cd, res, nres, q.lsbMode, lpc_weighting, T, lsbs);
+    const i32 rateFlag = s_sub(total_bits, s_add(160, s_imult(b.fs_idx, 160))) > 0 ? 2 << 8 : 0;
+    ari_encode(bytes, w, total_bits, xq, b.yLen, rateFlag, tns, q.lastnz, res, nres, q.lsbMode, lpc_weighting, T, lsbs);
 
     u8 *dst = b.out + b.out_off[li] + (size_t)(b.frame0 + f) * b.out_stride[li];
     for (int i = 0; i < target_bytes; i++) dst[i] = bytes[i];

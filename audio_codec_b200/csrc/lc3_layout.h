@@ -50,7 +50,8 @@ enum {
 };
 
 /* per channel-frame outputs of the rate-loop pass */
-enum { RO_QGAIN = 0, RO_QGAIN_MIN, RO_NBITS1, RO_TBITS_QUANT, RO_N = 4 };
+/* (RO_QGAIN: gain index of the first pass, replaced by the adjusted one by the final quantisation, which adds the last four) */
+enum { RO_QGAIN = 0, RO_QGAIN_MIN, RO_NBITS1, RO_TBITS_QUANT, RO_LASTNZ, RO_LSBMODE, RO_NBITS2, RO_N = 8 };
 
 typedef struct {
     /* bucket geometry (fx/setup_enc_lc3.c:69-127) */
@@ -80,6 +81,7 @@ typedef struct {
     int32_t *en4;             /* [n_frames][n_tiles][N/4][32] */
     int32_t *rout;            /* [n_frames][n_tiles][RO_N][32] */
     int16_t *r12;             /* [n_frames][n_tiles][128][32] 12.8 kHz signal: FIR output, then high-passed in place */
+    int16_t *xq;              /* [n_frames][n_tiles][N][32] quantised spectrum of the final pass */
 } LC3K_Batch;
 
 #ifdef __cplusplus
@@ -92,6 +94,7 @@ int lc3k_launch_scalar(const LC3K_Batch *b, void *stream);  /* 16-bit input only
 int lc3k_launch_pitch(const LC3K_Batch *b, void *stream);   /* pitch analysis + attack detector, warp per stream (24-bit: also the two above) */
 int lc3k_launch_front(const LC3K_Batch *b, void *stream);
 int lc3k_launch_rate(const LC3K_Batch *b, void *stream);
+int lc3k_launch_quant(const LC3K_Batch *b, void *stream);   /* gain adjustment + final quantisation, block per tile */
 int lc3k_launch_back(const LC3K_Batch *b, void *stream);
 /* set the listed state slots to their power-on values (fx/setup_enc_lc3.c:38-66) */
 int lc3k_launch_reset(int32_t *st32, int16_t *st16, int16_t *hist16, int32_t *hist32, const int32_t *slots, int n, void *stream);

@@ -11,6 +11,7 @@ extern "C" {
 #include "lc3_body_frame.cuh"
 #include "lc3_pitch_warp.cuh"
 #include "lc3_rate_warp.cuh"
+#include "lc3_quant_tile.cuh"
 
 using namespace lc3k;
 
@@ -126,6 +127,8 @@ extern "C" int hostsim_encode(void *p, const void *pcm, int bits, int n_frames, 
     std::vector<int32_t> pout(ftl * PO_N), spec(ftl * N), fout(ftl * FO_N), en4(ftl * (N / 4)), rout(ftl * RO_N);
     b.pcm_t = pcm_t.data(); b.pout = pout.data(); b.spec = spec.data(); b.fout = fout.data(); b.en4 = en4.data();
     b.rout = rout.data();
+    std::vector<int16_t> xqbuf(ftl * N);
+    b.xq = xqbuf.data();
 
     // staging (what the stage kernel does): history prefix from the state, frames from the caller, new history
     for (int li = 0; li < s->n_streams; li++) {
@@ -190,7 +193,16 @@ extern "C" int hostsim_encode(void *p, const void *pcm, int bits, int n_frames, 
         for (int li = 0; li < b.n_lanes; li++) rate_warp_body(b, li, rsh, (const u8 *)rom_ari_lookup, rom_ari_bits);
     }
     for (int f = 0; f < n_frames; f++)
-        for (int tile = 0; tile < b.n_tiles; tile++)
-            for (int lane = 0; lane < 32; lane++) back_body(b, f, tile, lane, T, rom_ari_bits);
+        for (int tile = 0; tile < b.n_tiles; tile++) {
+            // the tile quantiser (k_quant in lc3_k_back.cu), phase by phase
+            static QuantShared qs;
+            for (int t = 0; t < 32; t++) qt_setup(b, f, tile, t, qs.fr[t]);
+            for (int t = 0; t < QT_THREADS; t++) qt_quantise(b, f, tile, t, qs);
+            for (int w = 0; w < QT_PARTS; w++)
+                for (int j = 0; j < 4; j++)
+                    qt_analyse(qs.fr[w + 8 * j], qs.xq + (w + 8 * j) * QT_ROW, b.yLen, qs.w[w], (const u8 *)rom_ari_lookup, rom_ari_bits);
+            for (int t = 0; t < QT_THREADS; t++) qt_store(b, f, tile, t, qs);
+            for (int lane = 0; lane < 32; lane++) back_body(b, f, tile, lane, T);
+        }
     return 0;
 }
