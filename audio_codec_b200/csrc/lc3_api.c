@@ -12,7 +12,7 @@
 
 #define LC3B_MAGIC 0x4c433362u
 #define N_PIPES 3
-#define N_WORK 8
+#define N_WORK 9
 enum { K_STAGE = 0, K_FIR, K_SCALAR, K_PITCH, K_FRONT, K_RATE, K_QUANT, K_BACK, N_KERNELS };
 /* kernels that read and write per-stream state: chunk c+1's launch must wait for chunk c's */
 static const int k_stateful[N_KERNELS] = {1 /* input history */, 0, 1 /* high-pass memory */, 1, 0, 1 /* rate-loop feedback */, 0, 0};
@@ -281,7 +281,7 @@ static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_
     const int n_pipes = n_chunks < N_PIPES ? n_chunks : N_PIPES;
     const size_t ftl = (size_t)fc * b.n_tiles * 32;
     const size_t need[N_WORK] = {(size_t)b.n_tiles * 32 * (size_t)(fc + 1) * N * sb, ftl * PO_N * 4, ftl * N * 4, ftl * FO_N * 4,
-                                 ftl * (N / 4) * 4, ftl * RO_N * 4, ftl * 128 * 2, ftl * N * 2};
+                                 ftl * (N / 4) * 4, ftl * RO_N * 4, ftl * 128 * 2, ftl * N * 2, ftl * BEN_N * 4};
     for (int p = 0; p < n_pipes; p++)
         for (int i = 0; i < N_WORK; i++)
             if (ensure(&g.pipe[p].work[i], &g.pipe[p].work_cap[i], need[i], 0)) return 1;
@@ -307,7 +307,7 @@ static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_
         b.frame0 = f0;
         b.n_frames = n_frames - f0 < fc ? n_frames - f0 : fc;
         b.pcm_t = w[0]; b.pout = (int32_t *)w[1]; b.spec = (int32_t *)w[2]; b.fout = (int32_t *)w[3];
-        b.en4 = (int32_t *)w[4]; b.rout = (int32_t *)w[5]; b.r12 = (int16_t *)w[6]; b.xq = (int16_t *)w[7];
+        b.en4 = (int32_t *)w[4]; b.rout = (int32_t *)w[5]; b.r12 = (int16_t *)w[6]; b.xq = (int16_t *)w[7]; b.ben = (int32_t *)w[8];
         cudaStream_t cur = par;
         if (cp && cp->h_pcm) /* this chunk's columns of every stream's PCM rows, one rectangle per channel */
             for (int ch = 0; ch < c0->channels; ch++) {
@@ -336,7 +336,7 @@ static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_
                                  cudaMemcpyDeviceToHost, par));
         }
         CU(cudaEventRecord(g.pipe[p].done_ev, par));
-        g.launches += (bits == 16 ? 8 : 6) + (N >= 160); /* frame lengths >= 160: tile MDCT kernel + lane-per-frame front end */
+        g.launches += (bits == 16 ? 8 : 6) + (N >= 160 ? 2 : 0); /* frame lengths >= 160: the front end is three kernels (tile MDCT, SNS, TNS) */
     }
     for (int p = 0; p < n_pipes; p++) CU(cudaStreamWaitEvent(g.stream, g.pipe[p].done_ev, 0));
     CU(cudaEventRecord(g.end_ev, g.stream));

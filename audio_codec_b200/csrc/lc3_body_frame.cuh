@@ -5,10 +5,10 @@
 
 namespace lc3k {
 
-// ---- spectral front end: fx/enc_lc3.c:83-84, :119-175 (+ the state-free half of :181-185)
-// TILE_MDCT: the MDCT has already been done by the tile kernel (lc3_mdct_tile.cuh), b.spec holds the spectrum and
-// fout[FO_D_EXP] its exponent.
-template <int N, int BITS, bool TILE_MDCT = false> LC3_HD void front_body(const LC3K_Batch &b, int f, int tile, int lane)
+// ---- spectral front end: fx/enc_lc3.c:83-84, :119-175 (+ the state-free half of :181-185), everything in one
+// lane-per-frame pass.  Used for the short frame lengths (N < 160); the longer ones run the tile MDCT kernel
+// (lc3_mdct_tile.cuh: MDCT + band energies), then sns_body, then tns_body below.
+template <int N, int BITS> LC3_HD void front_body(const LC3K_Batch &b, int f, int tile, int lane)
 {
     const int li = tile * LC3K_LANES + lane;
     if (li >= b.n_lanes) return;
@@ -22,12 +22,8 @@ template <int N, int BITS, bool TILE_MDCT = false> LC3_HD void front_body(const 
     const i16 *bands = &rom_bands_offset[b.bands_off];
 
     SV<i32> fo = tile_view(b.fout, ft, FO_N, lane);
-    i32 d_exp;
-    if (TILE_MDCT) d_exp = fo[FO_D_EXP];
-    else {
-        i32 w[N];
-        d_exp = mdct_frame<N>(xs, x_exp, &rom_win[b.W_off], b.W_len, b.mdct_mem_len, d, w);
-    }
+    i32 w[N];
+    const i32 d_exp = mdct_frame<N>(xs, x_exp, &rom_win[b.W_off], b.W_len, b.mdct_mem_len, d, w);
 
     i32 en[64];
     const i32 en_exp = band_energy(en, d, d_exp, bands, b.fs_idx, b.nbands, b.dms_idx);
@@ -60,6 +56,69 @@ template <int N, int BITS, bool TILE_MDCT = false> LC3_HD void front_body(const 
     fo[FO_TNS_ORDER0] = tns.order[0]; fo[FO_TNS_ORDER1] = tns.order[1]; fo[FO_X_MAX] = x_max;
     for (int i = 0; i < 16; i++) fo[FO_TNS_IDX + i] = tns.idx[i];
     for (int i = 0; i < 7; i++) fo[FO_SCF + i] = scf_idx[i];
+}
+
+// ---- tile path, step 2: bandwidth detector and SNS from the band energies the tile MDCT kernel left in b.ben
+// (fx/enc_lc3.c:127-160).  No spectrum access at all: the gains go back into b.ben, packed mantissa | exponent << 16.
+LC3_HD void sns_body(const LC3K_Batch &b, int f, int tile, int lane)
+{
+    const int li = tile * LC3K_LANES + lane;
+    if (li >= b.n_lanes) return;
+    const size_t ft = frame_tile(b, f, tile);
+    SV<i32> eo = tile_view(b.ben, ft, BEN_N, lane);
+    SV<i32> fo = tile_view(b.fout, ft, FO_N, lane);
+    const i32 attack = tile_view((const i32 *)b.pout, ft, PO_N, lane)[PO_ATTACK];
+    i32 en[64];
+    for (int i = 0; i < b.nbands; i++) en[i] = eo[i];
+    const i32 en_exp = eo[BEN_EXP];
+    const i32 bw = b.fs_idx > 0 ? bw_detect(en, en_exp, b.fs_idx, b.dms_idx) : 0;
+    i16 scf[16], scf_q[16], g[64], g_exp[64];
+    i32 scf_idx[7];
+    sns_compute(en, en_exp, b.fs_idx, b.nbands, scf, attack, 16384);
+    sns_quantize(scf, scf_idx, scf_q);
+    sns_interp(scf_q, g, g_exp, b.nbands);
+    for (int i = 0; i < b.nbands; i++) eo[i] = (i32)((u32)g[i] & 0xffffu) | (i32)((u32)(i32)g_exp[i] << 16);
+    fo[FO_BW] = bw;
+    for (int i = 0; i < 7; i++) fo[FO_SCF + i] = scf_idx[i];
+}
+
+// ---- tile path, step 3: spectral shaping, bandwidth cut-off, TNS, per-quadruple log-energies
+// (fx/enc_lc3.c:162-175, first half of :181-185)
+template <int N> LC3_HD void tns_body(const LC3K_Batch &b, int f, int tile, int lane)
+{
+    const int li = tile * LC3K_LANES + lane;
+    if (li >= b.n_lanes) return;
+    SV<const i32> cfg = slot_view(b.cfg, b.slot[li], CFG_N);
+    const size_t ft = frame_tile(b, f, tile);
+    SV<const i32> eo = tile_view((const i32 *)b.ben, ft, BEN_N, lane);
+    SV<i32> fo = tile_view(b.fout, ft, FO_N, lane);
+    SV<i32> d = tile_view(b.spec, ft, N, lane);
+    const i16 *bands = &rom_bands_offset[b.bands_off];
+    const i32 d_exp = fo[FO_D_EXP];
+    i32 bw = fo[FO_BW];
+    i16 g[64], g_exp[64];
+    for (int i = 0; i < b.nbands; i++) { const i32 v = eo[i]; g[i] = (i16)(v & 0xffff); g_exp[i] = (i16)(v >> 16); }
+    mdct_shape(d, g, g_exp, bands, b.nbands);
+
+    const int cut = cfg[CFG_BW_CUTOFF_BIN];
+    if (cut) { // lc3_enc_set_bandwidth was used (fx/cutoff_bandwidth.c:14-28, fx/enc_lc3.c:164-168)
+        if (b.yLen > cut) {
+            for (int i = -1; i < 3; i++) d[cut + i] = d[cut + i] >> (i + 2);
+            for (int i = cut + 3; i < b.yLen; i++) d[i] = 0;
+        }
+        bw = imin(bw, cfg[CFG_BW_INDEX]);
+    }
+
+    TnsOut tns;
+    if (b.dms_idx == 0) tns_coder<8>(tns, d, bw, cfg[CFG_LPC_WEIGHTING], b.nsub, b.dms_idx);
+    else tns_coder<4>(tns, d, bw, cfg[CFG_LPC_WEIGHTING], b.nsub, b.dms_idx);
+
+    SV<i32> en4 = tile_view(b.en4, ft, N / 4, lane);
+    const i32 x_max = gain_energies(d, d_exp, b.yLen, en4);
+
+    fo[FO_BW] = bw; fo[FO_TNS_BITS] = tns.bits; fo[FO_TNS_NFILT] = tns.nfilt;
+    fo[FO_TNS_ORDER0] = tns.order[0]; fo[FO_TNS_ORDER1] = tns.order[1]; fo[FO_X_MAX] = x_max;
+    for (int i = 0; i < 16; i++) fo[FO_TNS_IDX + i] = tns.idx[i];
 }
 
 // ---- back end: fx/enc_lc3.c:196-242 (adjust gain, final quantisation, residual, noise factor, entropy coding)

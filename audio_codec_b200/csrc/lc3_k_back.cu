@@ -33,14 +33,18 @@ __global__ void __launch_bounds__(QT_THREADS) k_quant(LC3K_Batch b)
     qt_store(b, f, tile, t, sh);
 }
 
-__global__ void __launch_bounds__(128) k_back(LC3K_Batch b)
+// small blocks here, unlike k_front / k_sns / k_tns: the warps of this kernel run for very different times (the entropy
+// coder loops are data dependent), and a large block holds its SM slot until its slowest warp is done (measured: 2.44 ms
+// at 4 warps per block, 2.76 at 12, 3.52 at 24)
+#define BACK_WARPS 4
+__global__ void __launch_bounds__(32 * BACK_WARPS) k_back(LC3K_Batch b)
 {
     __shared__ u8 lut[4096];
     __shared__ uint16_t cum[1088], freq[1088];
-    for (int i = threadIdx.x; i < 4096; i += 128) lut[i] = (u8)rom_ari_lookup[i];
-    for (int i = threadIdx.x; i < 1088; i += 128) { cum[i] = rom_ari_cumfreq[i]; freq[i] = rom_ari_freq[i]; }
+    for (int i = threadIdx.x; i < 4096; i += 32 * BACK_WARPS) lut[i] = (u8)rom_ari_lookup[i];
+    for (int i = threadIdx.x; i < 1088; i += 32 * BACK_WARPS) { cum[i] = rom_ari_cumfreq[i]; freq[i] = rom_ari_freq[i]; }
     __syncthreads();
-    const int warp = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    const int warp = blockIdx.x * BACK_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (warp >= b.n_frames * b.n_tiles) return;
     AriTabs T = {lut, cum, freq};
     back_body(b, warp / b.n_tiles, warp % b.n_tiles, lane, T);
@@ -61,7 +65,7 @@ extern "C" int lc3k_launch_quant(const LC3K_Batch *b, void *stream)
 }
 extern "C" int lc3k_launch_back(const LC3K_Batch *b, void *stream)
 {
-    const int warps = b->n_frames * b->n_tiles, blocks = (warps + 3) / 4;
-    k_back<<<blocks, 128, 0, (cudaStream_t)stream>>>(*b);
+    const int warps = b->n_frames * b->n_tiles, blocks = (warps + BACK_WARPS - 1) / BACK_WARPS;
+    k_back<<<blocks, 32 * BACK_WARPS, 0, (cudaStream_t)stream>>>(*b);
     return done();
 }

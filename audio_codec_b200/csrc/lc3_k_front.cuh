@@ -5,11 +5,25 @@
 
 using namespace lc3k;
 
-template <int N, int BITS, bool TILE_MDCT> __global__ void __launch_bounds__(128, TILE_MDCT ? 6 : 4) k_front(LC3K_Batch b)
+// Large blocks on purpose (here and in k_tns, k_sns, k_back): these bodies are tens of thousands of instructions of
+// mostly straight-line code that every warp runs once, so the kernels are bound by instruction fetch unless the warps
+// of an SM walk through the code together and share the fetches (k_sns: "no instruction" stalls 9.7 -> 0, 1.24 -> 0.89 ms).
+#define FRONT_WARPS 16
+#define TNS_WARPS 24
+template <int N, int BITS> __global__ void __launch_bounds__(32 * FRONT_WARPS, 1) k_front(LC3K_Batch b)
 {
-    const int warp = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    const int warp = blockIdx.x * FRONT_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (warp >= b.n_frames * b.n_tiles) return;
-    front_body<N, BITS, TILE_MDCT>(b, warp / b.n_tiles, warp % b.n_tiles, lane);
+    front_body<N, BITS>(b, warp / b.n_tiles, warp % b.n_tiles, lane);
+}
+
+// tile path, steps 2 and 3 (lc3_body_frame.cuh): one lane per channel-frame
+extern "C" int lc3k_sns_launch(const LC3K_Batch *b, void *stream); // k_sns lives in lc3_k_sns.cu (one copy for all frame lengths)
+template <int N> __global__ void __launch_bounds__(32 * TNS_WARPS, 1) k_tns(LC3K_Batch b)
+{
+    const int warp = blockIdx.x * TNS_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (warp >= b.n_frames * b.n_tiles) return;
+    tns_body<N>(b, warp / b.n_tiles, warp % b.n_tiles, lane);
 }
 
 // MDCT of one tile (32 channel-frames) per block, spectrum in shared memory (lc3_mdct_tile.cuh).  In the twiddle,
@@ -19,8 +33,9 @@ template <int N, int BITS> __global__ void __launch_bounds__(256, 2) k_mdct(LC3K
 {
     typedef MdctTile<N> G;
     extern __shared__ __align__(16) i32 mt_smem[];
-    i32 *X = mt_smem, *mx = X + 32 * G::S, *mn = mx + G::PARTS * 32;
-    i16 *s_tw = (i16 *)(mn + G::PARTS * 32), *s_sn = s_tw + G::TW_LEN, *s_W = s_sn + G::SN_LEN;
+    i32 *X = mt_smem, *mx = X + 32 * G::S, *mn = mx + G::PARTS * 32, *smx = mn + G::PARTS * 32;
+    i32 *ben = smx + G::PARTS * 32, *bexp = ben + 32 * G::BROW;
+    i16 *s_tw = (i16 *)(bexp + 32 * G::BROW), *s_sn = s_tw + G::TW_LEN, *s_W = s_sn + G::SN_LEN;
     const int f = blockIdx.x / b.n_tiles, tile = blockIdx.x % b.n_tiles, t = threadIdx.x, w = t >> 5, l = t & 31;
     {
         const MtTabs R = mt_rom_tabs<N>();
@@ -47,18 +62,21 @@ template <int N, int BITS> __global__ void __launch_bounds__(256, 2) k_mdct(LC3K
 #pragma unroll 1
     for (int j = 0; j < 4; j++) mt_post<N>(X, w + 8 * j, l, T);
     __syncthreads();
-    mt_store<N>(b, f, tile, t, X, mx, mn);
+    mt_bands<N>(b, t, X, ben, bexp, smx);
+    __syncthreads();
+    mt_store<N>(b, f, tile, t, X, mx, mn, ben, bexp, smx);
 }
 
 template <int N> static int front_launch(const LC3K_Batch *b, cudaStream_t s)
 {
-    const int warps = b->n_frames * b->n_tiles, blocks = (warps + 3) / 4;
-    if (b->bits == 16) k_front<N, 16, false><<<blocks, 128, 0, s>>>(*b);
-    else k_front<N, 24, false><<<blocks, 128, 0, s>>>(*b);
+    const int warps = b->n_frames * b->n_tiles, blocks = (warps + FRONT_WARPS - 1) / FRONT_WARPS;
+    if (b->bits == 16) k_front<N, 16><<<blocks, 32 * FRONT_WARPS, 0, s>>>(*b);
+    else k_front<N, 24><<<blocks, 32 * FRONT_WARPS, 0, s>>>(*b);
     return (int)cudaGetLastError();
 }
 
-// frame lengths with an 8-column FFT: tile MDCT kernel, then the rest of the front end one lane per channel-frame
+// frame lengths with an 8-column FFT: tile kernel (MDCT + band energies), then SNS and shaping/TNS/energies, each one
+// lane per channel-frame
 template <int N> static int front_launch_tiled(const LC3K_Batch *b, cudaStream_t s)
 {
     static bool attr_set = false;
@@ -69,13 +87,10 @@ template <int N> static int front_launch_tiled(const LC3K_Batch *b, cudaStream_t
         if (e != cudaSuccess) return (int)e;
         attr_set = true;
     }
-    const int tiles = b->n_frames * b->n_tiles, blocks = (tiles + 3) / 4;
-    if (b->bits == 16) {
-        k_mdct<N, 16><<<tiles, 256, smem, s>>>(*b);
-        k_front<N, 16, true><<<blocks, 128, 0, s>>>(*b);
-    } else {
-        k_mdct<N, 24><<<tiles, 256, smem, s>>>(*b);
-        k_front<N, 24, true><<<blocks, 128, 0, s>>>(*b);
-    }
+    const int tiles = b->n_frames * b->n_tiles, blocks = (tiles + TNS_WARPS - 1) / TNS_WARPS;
+    if (b->bits == 16) k_mdct<N, 16><<<tiles, 256, smem, s>>>(*b);
+    else k_mdct<N, 24><<<tiles, 256, smem, s>>>(*b);
+    { const int e = lc3k_sns_launch(b, s); if (e) return e; }
+    k_tns<N><<<blocks, 32 * TNS_WARPS, 0, s>>>(*b);
     return (int)cudaGetLastError();
 }

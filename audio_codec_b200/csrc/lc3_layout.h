@@ -49,6 +49,10 @@ enum {
     FO_N = 32
 };
 
+/* per channel-frame band data (tile MDCT path): 64 band energies + their exponent, later overwritten with the SNS gains
+ * (mantissa in the low, exponent in the high half-word) */
+enum { BEN_EXP = 64, BEN_N = 66 };
+
 /* per channel-frame outputs of the rate-loop pass */
 /* (RO_QGAIN: gain index of the first pass, replaced by the adjusted one by the final quantisation, which adds the last four) */
 enum { RO_QGAIN = 0, RO_QGAIN_MIN, RO_NBITS1, RO_TBITS_QUANT, RO_LASTNZ, RO_LSBMODE, RO_NBITS2, RO_N = 8 };
@@ -81,6 +85,7 @@ typedef struct {
     int32_t *en4;             /* [n_frames][n_tiles][N/4][32] */
     int32_t *rout;            /* [n_frames][n_tiles][RO_N][32] */
     int16_t *r12;             /* [n_frames][n_tiles][128][32] 12.8 kHz signal: FIR output, then high-passed in place */
+    int32_t *ben;             /* [n_frames][n_tiles][BEN_N][32] band energies / SNS gains (tile MDCT path) */
     int16_t *xq;              /* [n_frames][n_tiles][N][32] quantised spectrum of the final pass */
 } LC3K_Batch;
 

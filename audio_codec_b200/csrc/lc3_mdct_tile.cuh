@@ -20,6 +20,7 @@
 #pragma once
 #include "lc3_mdct.cuh"
 #include "lc3_stages.cuh"
+#include "lc3_spec.cuh"
 
 namespace lc3k {
 
@@ -35,7 +36,10 @@ template <int N> struct MdctTile {
     // which the constant cache serialises (one address per cycle); entries used: pre-twiddle N, post-twiddle
     // 2 * (M/2) * step + 2, column twiddles up to SC * (M - 1) + 2 - WOFF
     static constexpr int TW_LEN = N, SN_LEN = (N % 3 == 0) ? 482 : 322, W_LEN = 480;
-    static constexpr size_t smem_bytes = (size_t)(32 * S + 2 * PARTS * 32) * sizeof(i32) + (size_t)(TW_LEN + SN_LEN + W_LEN) * sizeof(i16);
+    // per-band energies of the tile before alignment: mantissa and exponent [32 frames][BROW], row stride odd
+    static constexpr int BROW = 65;
+    static constexpr size_t smem_words = 32 * S + 3 * PARTS * 32 + 2 * 32 * BROW;
+    static constexpr size_t smem_bytes = smem_words * sizeof(i32) + (size_t)(TW_LEN + SN_LEN + W_LEN) * sizeof(i16);
     static_assert(N == 160 || N == 240 || N == 320 || N == 480, "8-column FFT lengths only");
 };
 
@@ -192,8 +196,30 @@ template <int N> LC3_HD void mt_post(i32 *X, int fr, int l, const MtTabs &T)
     }
 }
 
-// ---- store: thread t = (lane of the tile, part); also the block exponent of the frame
-template <int N> LC3_HD void mt_store(const LC3K_Batch &b, int f, int tile, int t, const i32 *X, const i32 *mx, const i32 *mn)
+// ---- band energies (fx/per_band_energy_fx.c) while the spectrum is still in shared memory: thread t = (frame of
+// the tile, part), bands part, part+8, ...; mantissas and exponents stay in shared memory until the store phase
+// aligns them to the frame's largest exponent
+struct MtRow { const i32 *y; LC3_HDM i32 operator[](int e) const { return y[mt_ridx(e)]; } };
+template <int N> LC3_HD void mt_bands(const LC3K_Batch &b, int t, const i32 *X, i32 *ben, i32 *bexp, i32 *smx)
+{
+    typedef MdctTile<N> G;
+    const int lane = t & 31, part = t >> 5;
+    const MtRow row = {X + lane * G::S};
+    const BandGeom g = band_geom(b.fs_idx, b.dms_idx);
+    const i16 *bo = &rom_bands_offset[b.bands_off];
+    i32 smax = -31;
+    for (int band = part; band < b.nbands; band += G::PARTS) {
+        i32 en;
+        const i32 e = band_one(en, row, band, bo, g);
+        ben[lane * G::BROW + band] = en; bexp[lane * G::BROW + band] = e;
+        smax = imax(smax, e);
+    }
+    smx[part * 32 + lane] = smax;
+}
+
+// ---- store: thread t = (tile lane, part): spectrum, block exponent, aligned band energies and their exponent
+template <int N> LC3_HD void mt_store(const LC3K_Batch &b, int f, int tile, int t, const i32 *X, const i32 *mx, const i32 *mn,
+                                      const i32 *ben, const i32 *bexp, const i32 *smx)
 {
     typedef MdctTile<N> G;
     const int lane = t & 31, part = t >> 5, li = tile * LC3K_LANES + lane;
@@ -202,10 +228,16 @@ template <int N> LC3_HD void mt_store(const LC3K_Batch &b, int f, int tile, int 
     const i32 *y = X + lane * G::S;
     SV<i32> d = tile_view(b.spec, ft, N, lane);
     for (int e = part; e < N; e += G::PARTS) d[e] = y[mt_ridx(e)];
+    const i32 x_exp = tile_view((const i32 *)b.pout, ft, PO_N, lane)[PO_X_EXP];
+    const i32 d_exp = s_add(s_add(s_sub(s_sub(x_exp, 2), mt_shift<N>(mx, mn, lane)), G::FFT_SCALE), 2);
+    i32 smax = -31;
+    for (int p = 0; p < G::PARTS; p++) smax = imax(smax, smx[p * 32 + lane]);
+    SV<i32> eo = tile_view(b.ben, ft, BEN_N, lane);
+    for (int band = part; band < b.nbands; band += G::PARTS)
+        eo[band] = ben[lane * G::BROW + band] >> imin(s_sub(smax, bexp[lane * G::BROW + band]), 31);
     if (part == 0) {
-        const i32 x_exp = tile_view((const i32 *)b.pout, ft, PO_N, lane)[PO_X_EXP];
-        const i32 y_e = s_sub(s_sub(x_exp, 2), mt_shift<N>(mx, mn, lane));
-        tile_view(b.fout, ft, FO_N, lane)[FO_D_EXP] = s_add(s_add(y_e, G::FFT_SCALE), 2);
+        tile_view(b.fout, ft, FO_N, lane)[FO_D_EXP] = d_exp;
+        eo[BEN_EXP] = s_add(s_shl(d_exp, 1), smax);
     }
 }
 

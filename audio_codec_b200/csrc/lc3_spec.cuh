@@ -9,66 +9,69 @@ namespace lc3k {
 LC3_HD i32 sq_hi(i32 v, i32 sh) { i32 t = hi16(l_shl_ns(v, sh)); return t * t; }
 LC3_HD i32 hr15(i32 v, i32 cur) { return v != 0 ? imin(cur, l_norm(v)) : cur; }
 
+// Energy of ONE band before the bands are aligned: mantissa en, exponent returned (bands are independent of
+// each other up to that alignment, which is what lets the tile kernel spread them over threads).
+struct BandGeom { int maxbin, one, two; };
+LC3_HD BandGeom band_geom(int fs_idx, int dms_idx)
+{
+    BandGeom g = {400 >> dms_idx, rom_bands_one_max[dms_idx * 5 + fs_idx], rom_bands_two_max[dms_idx * 5 + fs_idx]};
+    return g;
+}
+template <class A> LC3_HD i32 band_one(i32 &en, A d, int band, const i16 *bo, const BandGeom &g)
+{
+    if (band < g.one) { // width-1 bands
+        const i32 v = d[band];
+        const i32 s2 = hr15(v, 15);
+        en = sq_hi(v, s2);
+        return s_sub(1, s_shl(s2, 1));
+    }
+    if (band < g.two) { // width-2 bands
+        const int i = g.one + 2 * (band - g.one);
+        if (i + 1 >= g.maxbin) {
+            if (i >= g.maxbin) { en = 0; return 1 - 30; }
+            // the reference reads d[band] here, not d[i] (per_band_energy_fx.c:117-128)
+            const i32 v = d[band];
+            const i32 s2 = hr15(v, 15);
+            en = sq_hi(v, s2);
+            return s_sub(1, s_shl(s2, 1));
+        }
+        const i32 v0 = d[i], v1 = d[i + 1];
+        const i32 s2 = hr15(v1, hr15(v0, 15));
+        const i32 a = imin(sq_hi(v0, s2), 0x3FFFFFFF);
+        const i32 t = hi16(l_shl_ns(v1, s2));
+        en = l_mac0(a, t, t) >> 1;
+        return s_sub(1, s_shl(s2, 1));
+    }
+    // wider bands
+    const int start = bo[band], stop = imin(bo[band + 1], g.maxbin);
+    i32 s1 = 15;
+    for (int k = start; k < stop; k++) s1 = hr15(d[k], s1);
+    int w = bo[band + 1] - bo[band];
+    w = w < 0 ? 0 : (w > 31 ? 31 : w);
+    const i32 s2 = s_sub(s1, rom_bands_nrg_scale[w]);
+    i64 a64 = 0; // non-negative terms: the saturating L_mac0 chain equals the clamped exact sum
+    for (int i = start; i < stop; i++) {
+        const i32 t = hi16(l_shl_ns(d[i], s2));
+        a64 += (i64)t * t;
+    }
+    i32 a = a64 > LC3_I32_MAX ? LC3_I32_MAX : (i32)a64;
+    a = mpy32x16(a, rom_inv_int[w]);
+    const i32 s = l_norm(a);
+    en = l_shl(a, s);
+    return s_sub(1, s_add(s_shl(s2, 1), s));
+}
+
 // en[0..nbands) mantissas on the common exponent returned.  bo: bands_offset table of this config.
 template <class A> LC3_HD i32 band_energy(i32 *en, A d, i32 d_exp, const i16 *bo, int fs_idx, int nbands, int dms_idx)
 {
     i16 be[64];
-    const int maxbin = 400 >> dms_idx;
-    const int one = rom_bands_one_max[dms_idx * 5 + fs_idx], two = rom_bands_two_max[dms_idx * 5 + fs_idx];
-    int band = 0, i;
+    const BandGeom g = band_geom(fs_idx, dms_idx);
     i32 smax = -31;
-
-    for (; band < one; band++) { // width-1 bands
-        i32 v = d[band];
-        i32 s2 = hr15(v, 15);
-        en[band] = sq_hi(v, s2);
-        i32 e = s_sub(1, s_shl(s2, 1));
+    for (int band = 0; band < nbands; band++) {
+        const i32 e = band_one(en[band], d, band, bo, g);
         be[band] = (i16)e; smax = imax(smax, e);
     }
-    i = one;
-    for (; band < two; band++, i += 2) { // width-2 bands
-        i32 e;
-        if (i + 1 >= maxbin) {
-            if (i >= maxbin) {
-                en[band] = 0;
-                e = 1 - 30;
-            } else { // the reference reads d[band] here, not d[i] (per_band_energy_fx.c:117-128)
-                i32 v = d[band];
-                i32 s2 = hr15(v, 15);
-                en[band] = sq_hi(v, s2);
-                e = s_sub(1, s_shl(s2, 1));
-            }
-        } else {
-            i32 v0 = d[i], v1 = d[i + 1];
-            i32 s2 = hr15(v1, hr15(v0, 15));
-            i32 a = imin(sq_hi(v0, s2), 0x3FFFFFFF);
-            i32 t = hi16(l_shl_ns(v1, s2));
-            en[band] = l_mac0(a, t, t) >> 1;
-            e = s_sub(1, s_shl(s2, 1));
-        }
-        be[band] = (i16)e; smax = imax(smax, e);
-    }
-    for (; band < nbands; band++) { // wider bands
-        const int stop = imin(bo[band + 1], maxbin);
-        i32 s1 = 15;
-        for (int k = i; k < stop; k++) s1 = hr15(d[k], s1);
-        int w = bo[band + 1] - bo[band];
-        w = w < 0 ? 0 : (w > 31 ? 31 : w);
-        i32 s2 = s_sub(s1, rom_bands_nrg_scale[w]);
-        i64 a64 = 0; // non-negative terms: the saturating L_mac0 chain equals the clamped exact sum
-        for (; i < stop; i++) {
-            i32 t = hi16(l_shl_ns(d[i], s2));
-            a64 += (i64)t * t;
-        }
-        i32 a = a64 > LC3_I32_MAX ? LC3_I32_MAX : (i32)a64;
-        i = bo[band + 1];
-        a = mpy32x16(a, rom_inv_int[w]);
-        i32 s = l_norm(a);
-        en[band] = l_shl(a, s);
-        i32 e = s_sub(1, s_add(s_shl(s2, 1), s));
-        be[band] = (i16)e; smax = imax(smax, e);
-    }
-    for (band = 0; band < nbands; band++) en[band] = en[band] >> imin(s_sub(smax, be[band]), 31);
+    for (int band = 0; band < nbands; band++) en[band] = en[band] >> imin(s_sub(smax, be[band]), 31);
     return s_add(s_shl(d_exp, 1), smax);
 }
 

@@ -47,16 +47,27 @@ template <int N, int BITS> static void run_mdct_tile(const LC3K_Batch &b, int f,
             for (int l = 0; l < G::LEAF; l++) mt_col_store<N>(X, w + 8 * j, l, o[l]);
         }
     for (int t = 0; t < G::THREADS; t++) { const int w = t >> 5, l = t & 31; for (int j = 0; j < 4; j++) mt_post<N>(X, w + 8 * j, l, T); }
-    for (int t = 0; t < G::THREADS; t++) mt_store<N>(b, f, tile, t, X, mx, mn);
+    i32 *smx = mn + G::PARTS * 32, *ben = smx + G::PARTS * 32, *bexp = ben + 32 * G::BROW;
+    for (int t = 0; t < G::THREADS; t++) mt_bands<N>(b, t, X, ben, bexp, smx);
+    for (int t = 0; t < G::THREADS; t++) mt_store<N>(b, f, tile, t, X, mx, mn, ben, bexp, smx);
 }
 template <int BITS> static void run_front_tile(const LC3K_Batch &b, int f, int tile)
 { // same split as front_launch_tiled / front_launch
     switch (b.N) {
-    case 160: run_mdct_tile<160, BITS>(b, f, tile); for (int l = 0; l < 32; l++) front_body<160, BITS, true>(b, f, tile, l); break;
-    case 240: run_mdct_tile<240, BITS>(b, f, tile); for (int l = 0; l < 32; l++) front_body<240, BITS, true>(b, f, tile, l); break;
-    case 320: run_mdct_tile<320, BITS>(b, f, tile); for (int l = 0; l < 32; l++) front_body<320, BITS, true>(b, f, tile, l); break;
-    case 480: run_mdct_tile<480, BITS>(b, f, tile); for (int l = 0; l < 32; l++) front_body<480, BITS, true>(b, f, tile, l); break;
-    default: for (int l = 0; l < 32; l++) run_front<BITS>(b, f, tile, l);
+    case 160: run_mdct_tile<160, BITS>(b, f, tile); break;
+    case 240: run_mdct_tile<240, BITS>(b, f, tile); break;
+    case 320: run_mdct_tile<320, BITS>(b, f, tile); break;
+    case 480: run_mdct_tile<480, BITS>(b, f, tile); break;
+    default: for (int l = 0; l < 32; l++) run_front<BITS>(b, f, tile, l); return;
+    }
+    for (int l = 0; l < 32; l++) sns_body(b, f, tile, l);
+    for (int l = 0; l < 32; l++) {
+        switch (b.N) {
+        case 160: tns_body<160>(b, f, tile, l); break;
+        case 240: tns_body<240>(b, f, tile, l); break;
+        case 320: tns_body<320>(b, f, tile, l); break;
+        case 480: tns_body<480>(b, f, tile, l); break;
+        }
     }
 }
 
@@ -129,6 +140,8 @@ extern "C" int hostsim_encode(void *p, const void *pcm, int bits, int n_frames, 
     b.rout = rout.data();
     std::vector<int16_t> xqbuf(ftl * N);
     b.xq = xqbuf.data();
+    std::vector<int32_t> benbuf(ftl * BEN_N);
+    b.ben = benbuf.data();
 
     // staging (what the stage kernel does): history prefix from the state, frames from the caller, new history
     for (int li = 0; li < s->n_streams; li++) {
