@@ -51,12 +51,15 @@ template <class T> __global__ void __launch_bounds__(256) k_stage(LC3K_Batch b)
     }
 }
 
-// per-stream passes: one warp per channel-stream, 4 streams per block
-template <int BITS, bool PRE> __global__ void __launch_bounds__(128, 7) k_pitch(LC3K_Batch b)
+// per-stream passes: one warp per channel-stream.  14 warps per block, 2 blocks per SM: 28 x 148 = 4144 streams are
+// resident at once (the 4096-stream workload runs in one wave), and the warps of a block share instruction fetches.
+#define PITCH_WARPS 14
+template <int BITS, bool PRE> __global__ void __launch_bounds__(32 * PITCH_WARPS, 2) k_pitch(LC3K_Batch b)
 {
-    __shared__ PitchShared sh[4];
+    extern __shared__ __align__(16) unsigned char pitch_smem[];
+    PitchShared *sh = reinterpret_cast<PitchShared *>(pitch_smem);
     const int w = threadIdx.x >> 5;
-    pitch_warp_body<BITS, PRE>(b, blockIdx.x * 4 + w, sh[w]);
+    pitch_warp_body<BITS, PRE>(b, blockIdx.x * PITCH_WARPS + w, sh[w]);
 }
 
 // resampler FIR, frame-parallel: one warp per (channel-stream, frame)
@@ -133,9 +136,17 @@ extern "C" int lc3k_launch_scalar(const LC3K_Batch *b, void *stream)
 }
 extern "C" int lc3k_launch_pitch(const LC3K_Batch *b, void *stream)
 {
-    const int blocks = (b->n_lanes + 3) / 4;
-    if (b->bits == 16) k_pitch<16, true><<<blocks, 128, 0, (cudaStream_t)stream>>>(*b);
-    else k_pitch<24, false><<<blocks, 128, 0, (cudaStream_t)stream>>>(*b);
+    static bool attr_set = false;
+    const size_t smem = PITCH_WARPS * sizeof(PitchShared);
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(k_pitch<16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_pitch<24, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return (int)e;
+        attr_set = true;
+    }
+    const int blocks = (b->n_lanes + PITCH_WARPS - 1) / PITCH_WARPS;
+    if (b->bits == 16) k_pitch<16, true><<<blocks, 32 * PITCH_WARPS, smem, (cudaStream_t)stream>>>(*b);
+    else k_pitch<24, false><<<blocks, 32 * PITCH_WARPS, smem, (cudaStream_t)stream>>>(*b);
     return done();
 }
 extern "C" int lc3k_launch_rate(const LC3K_Batch *b, void *stream)
