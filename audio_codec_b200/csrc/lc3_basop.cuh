@@ -118,6 +118,17 @@ LC3_HD i32 l_shl_p(i32 a, i32 n)
 LC3_HD i32 l_shl_ns(i32 a, i32 n) { return n >= 0 ? (i32)((u32)a << n) : a >> imin(-n, 31); }
 LC3_HD i32 l_shl(i32 a, i32 n) { return n <= 0 ? l_shr_p(a, n < -32 ? 32 : -n) : l_shl_p(a, n); }
 LC3_HD i32 l_shr(i32 a, i32 n) { return n < 0 ? l_shl_p(a, n < -32 ? 32 : -n) : l_shr_p(a, n); }
+// L_shl by a count that stays the same over a loop: the count is split once into a left and a right part (one of them
+// zero), and each element costs a shift, a check shift and a select, without branches.  Equals l_shl(a, n) for every
+// a and n (tests/hostsim/primcheck.cpp); counts above 31 behave like 31 because only 0 and -1 survive a left shift by
+// 31 unchanged, and those two give the same result for any larger count.
+struct ShlPlan { int sl, sr; };
+LC3_HD ShlPlan shl_plan(i32 n) { ShlPlan p = {imin(imax(n, 0), 31), imin(imax(-n, 0), 31)}; return p; }
+LC3_HD i32 l_shl_plan(i32 a, const ShlPlan &p)
+{
+    const i32 l = (i32)((u32)a << p.sl);
+    return (l >> p.sl) != a ? ((a >> 31) ^ LC3_I32_MAX) : (l >> p.sr);
+}
 LC3_HD i32 l_norm(i32 a) { return a == 0 ? 0 : clz32((u32)(a ^ (a >> 31))) - 1; }
 LC3_HD i32 ul_norm(u32 a) { return a == 0 ? 0 : clz32(a); }
 LC3_HD i32 l_mult0(i32 a, i32 b) { return a * b; }

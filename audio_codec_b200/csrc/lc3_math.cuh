@@ -6,22 +6,27 @@
 namespace lc3k {
 
 // BASOP_Util_Log2 (fx/basop_util.c:25-86): log2(x)/64 in Q31
+// the mantissa polynomial of BASOP_Util_Log2 for f = 0 .. 16383 (the only values the normalised argument yields).
+// tests/hostsim/primcheck.cpp runs this and the saturating operator-by-operator form over all 16384 values of f: they
+// agree, i.e. none of the reference's L_mult / L_mac / mult saturations can trigger, and plain arithmetic is exact.
+LC3_HD i32 m_log2_poly(i32 f)
+{
+    i32 acc = 2 * f * rom_ld_coeff[0];
+    i32 p = (f * f) >> 15;
+#pragma unroll
+    for (int k = 1; k < 7; k++) {
+        acc += 2 * p * rom_ld_coeff[k];
+        if (k < 6) p = (p * f) >> 15;
+    }
+    acc = (acc >> 1) + hi16(acc) * 14506;
+    return acc >> 5;
+}
 LC3_HD i32 m_log2(i32 x)
 {
     if (x == 0) return LC3_I32_MIN;
     i32 e = l_norm(x);
     x = (i32)((u32)x << e);
-    i32 f = hi16(l_sub(LC3_I32_MAX, x));
-    i32 acc = l_mult(f, rom_ld_coeff[0]);
-    i32 p = s_mult(f, f);
-#pragma unroll
-    for (int k = 1; k < 7; k++) {
-        acc = l_mac(acc, p, rom_ld_coeff[k]);
-        if (k < 6) p = s_mult(p, f);
-    }
-    acc = l_mac0(acc >> 1, hi16(acc), 14506);
-    acc = acc >> 5;
-    return l_sub(acc, e << 25);
+    return l_sub(m_log2_poly(hi16(l_sub(LC3_I32_MAX, x))), e << 25);
 }
 
 // BASOP_Util_InvLog2 (fx/basop_util.c:89-138): 2^(x/64)

@@ -102,12 +102,25 @@ LC3_HD void est_gain(E en, int lg4, i32 x_max, i32 x_e, i32 nbitsSQ, i32 qgain_o
     gain_from_index(s_add(qgain, qgain_off), gain, gain_e);
 }
 
-// quantise one bin: |x|/gain + 0.375 truncated, sign restored (quantize_spec_fx.c:53-74)
+// quantise one bin: |x|/gain + 0.375 truncated, sign restored (quantize_spec_fx.c:53-74).
+// Reference form:  v = L_shl(Mpy_32_16(L_abs(x), inv_gain), s);  q = mac_r(v, -4096, 1);  sign restored.
+// inv_gain comes from Inv16 and is positive, so with p = (|x| * inv_gain) >> 15 in [0, 2^31):
+//   v = min(p * 2^s, 2^31 - 1)              (the only way L_shl saturates here; s <= 0 is a plain right shift)
+//   q = min(v + 24576, 2^31 - 1) >> 16      (L_mac adds -8192 without saturating since v >= 0; round_fx adds 0x8000
+//                                            and saturates at the top)
+// which is evaluated below in 64/32-bit unsigned arithmetic.  tests/hostsim/primcheck.cpp compares it with the
+// operator-by-operator form on edge values and 10^8 random inputs.
 LC3_HD i32 quant_bin(i32 x, i32 inv_gain, i32 s)
 {
-    i32 v = l_shl(mpy32x16(l_abs(x), inv_gain), s);
-    i32 q = s_mac_r(v, -4096, 1);
-    return x < 0 ? s_neg(q) : q;
+    const u32 ax = x == LC3_I32_MIN ? (u32)LC3_I32_MAX : (u32)(x < 0 ? -x : x);
+    const uint64_t p = ((uint64_t)ax * (u32)inv_gain) >> 15;
+    const int sl = imin(imax(s, 0), 32), sr = imin(imax(-s, 0), 31);
+    uint64_t v = (p << sl) >> sr;
+    if (v > (uint64_t)LC3_I32_MAX) v = LC3_I32_MAX;
+    u32 t = (u32)v + 24576u;
+    if (t > (u32)LC3_I32_MAX) t = (u32)LC3_I32_MAX;
+    const i32 q = (i32)(t >> 16);
+    return x < 0 ? -q : q;
 }
 
 // fx/ari_codec.c:1269-1308

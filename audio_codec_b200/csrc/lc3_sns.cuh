@@ -441,9 +441,11 @@ template <class A> LC3_HD void mdct_shape(A d, const i16 *g, const i16 *g_exp, c
 {
     int j = 0;
     for (int b = 0; b < nbands; b++) {
-        const i32 gg = g[b], ge = g_exp[b];
+        const i32 gg = g[b];
+        const ShlPlan ge = shl_plan(g_exp[b]);
         const int stop = bo[b + 1];
-        for (; j < stop; j++) d[j] = l_shl(mpy32x16k(d[j], gg), ge); // gg > 0 (2^x mantissa)
+#pragma unroll 4
+        for (; j < stop; j++) d[j] = l_shl_plan(mpy32x16k(d[j], gg), ge); // gg > 0 (2^x mantissa)
     }
 }
 

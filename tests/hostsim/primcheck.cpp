@@ -1,0 +1,77 @@
+// TEST TOOLING: equivalence of the arithmetic shortcuts in audio_codec_b200/csrc with the operator-by-operator
+// BASOP forms they replace (the forms the oracle and the reference use).  Exhaustive where the input domain is
+// small, edge values + a large random sample elsewhere.  Prints "ok <name>" per check; exit code 1 on a mismatch.
+#include <cstdio>
+#include <cstdint>
+#include <cstdlib>
+#include "lc3_math.cuh"
+#include "lc3_rate.cuh"
+
+using namespace lc3k;
+
+static uint64_t rng_state = 0x9E3779B97F4A7C15ull;
+static uint32_t rnd() { rng_state ^= rng_state << 13; rng_state ^= rng_state >> 7; rng_state ^= rng_state << 17; return (uint32_t)(rng_state >> 16); }
+
+// ---- operator-by-operator forms
+static i32 quant_bin_ref(i32 x, i32 inv_gain, i32 s)
+{ // quantize_spec_fx.c:53-74
+    i32 v = l_shl(mpy32x16(l_abs(x), inv_gain), s);
+    i32 q = s_mac_r(v, -4096, 1);
+    return x < 0 ? s_neg(q) : q;
+}
+static i32 log2_poly_ref(i32 f)
+{ // basop_util.c:25-86
+    i32 acc = l_mult(f, rom_ld_coeff[0]);
+    i32 p = s_mult(f, f);
+    for (int k = 1; k < 7; k++) {
+        acc = l_mac(acc, p, rom_ld_coeff[k]);
+        if (k < 6) p = s_mult(p, f);
+    }
+    acc = l_mac0(acc >> 1, hi16(acc), 14506);
+    return acc >> 5;
+}
+
+static int fails = 0;
+#define CHECK(name, cond, ...) do { if (!(cond)) { if (fails < 10) { printf("MISMATCH %s: ", name); printf(__VA_ARGS__); printf("\n"); } fails++; } } while (0)
+
+int main(int argc, char **argv)
+{
+    const long n_rand = argc > 1 ? atol(argv[1]) : 20000000;
+
+    // quant_bin: inv_gain is an Inv16 output (positive 16-bit), s any plausible shift and beyond
+    {
+        const i32 edge_x[] = {0, 1, -1, 2, -2, 0x7fff, 0x8000, -0x8000, 0x7fffffff, LC3_I32_MIN, LC3_I32_MIN + 1, 0x40000000, -0x40000000,
+                              0x3fffffff, 12345678, -12345678, 0x7fffa000, 0x7fff9fff, 0x00010000, 0x0000ffff};
+        const i32 edge_g[] = {1, 2, 16384, 16385, 23170, 32766, 32767, 8192, 100};
+        for (i32 x : edge_x) for (i32 g : edge_g) for (i32 s = -40; s <= 40; s++)
+            CHECK("quant_bin", quant_bin(x, g, s) == quant_bin_ref(x, g, s), "x=%d g=%d s=%d", x, g, s);
+        for (long i = 0; i < n_rand; i++) {
+            i32 x = (i32)rnd();
+            if (i & 1) x >>= (rnd() % 31);
+            const i32 g = 1 + (i32)(rnd() % 32767), s = (i32)(rnd() % 56) - 36;
+            CHECK("quant_bin", quant_bin(x, g, s) == quant_bin_ref(x, g, s), "x=%d g=%d s=%d", x, g, s);
+        }
+        printf("ok quant_bin\n");
+    }
+    // m_log2 polynomial: exhaustive over its whole domain
+    {
+        for (i32 f = 0; f < 16384; f++) CHECK("m_log2_poly", m_log2_poly(f) == log2_poly_ref(f), "f=%d", f);
+        printf("ok m_log2_poly\n");
+    }
+    // L_shl with a planned count
+    {
+        const i32 edge[] = {0, 1, -1, 2, -2, 3, -3, 0x7fffffff, LC3_I32_MIN, LC3_I32_MIN + 1, 0x40000000, -0x40000000, 0x3fffffff, -0x40000001,
+                            0x7fff, -0x8000, 0x10000, -0x10000, 123456789, -123456789};
+        for (i32 a : edge) for (i32 n = -70; n <= 70; n++)
+            CHECK("l_shl_plan", l_shl_plan(a, shl_plan(n)) == l_shl(a, n), "a=%d n=%d", a, n);
+        for (long i = 0; i < n_rand; i++) {
+            i32 a = (i32)rnd();
+            if (i & 1) a >>= (rnd() % 32);
+            const i32 n = (i32)(rnd() % 80) - 40;
+            CHECK("l_shl_plan", l_shl_plan(a, shl_plan(n)) == l_shl(a, n), "a=%d n=%d", a, n);
+        }
+        printf("ok l_shl_plan\n");
+    }
+    if (fails) { printf("%d mismatches\n", fails); return 1; }
+    return 0;
+}
