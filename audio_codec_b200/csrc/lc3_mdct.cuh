@@ -60,14 +60,14 @@ LC3_HD i32 mdct_frame(XS xs, i32 x_exp, const i16 *win, int wLen, int memLen, A 
         cmul_half(a1, a2, q1, p0, tw[2 * k], tw[2 * k + 1]);
         cmul_half(a3, a4, q0, p1, tw[2 * k + 2], tw[2 * k + 3]);
         y[lo] = a2; y[lo + 1] = a1;
-        y[hi] = a4; y[hi + 1] = l_neg(a3);
+        y[hi] = a4; y[hi + 1] = -a3; // cmul_half outputs are below 2^31 in magnitude: no L_negate saturation
     }
     y_e = s_add(y_e, cfft<M>(y, w));
 
     int lo = 0, hi = N - 2, idx = step;
     constexpr int M2 = ((M + 1) >> 1) - 1;
     cmul_half(a3, a4, y[hi], y[hi + 1], sn[2 * idx], sn[2 * idx + 1]);
-    y[hi + 1] = l_neg(y[lo + 1] >> 1);
+    y[hi + 1] = -(y[lo + 1] >> 1);
     y[lo] = y[lo] >> 1;
     for (int k = 1; k < M2; k++) {
         y[lo + 1] = a3; y[hi] = a4;
@@ -75,7 +75,7 @@ LC3_HD i32 mdct_frame(XS xs, i32 x_exp, const i16 *win, int wLen, int memLen, A 
         cmul_half(a1, a2, y[lo + 1], y[lo], sn[2 * idx], sn[2 * idx + 1]);
         idx += step;
         cmul_half(a3, a4, y[hi], y[hi + 1], sn[2 * idx], sn[2 * idx + 1]);
-        y[hi + 1] = l_neg(a1);
+        y[hi + 1] = -a1;
         y[lo] = a2;
     }
     y[lo + 1] = a3; y[hi] = a4;
@@ -83,9 +83,9 @@ LC3_HD i32 mdct_frame(XS xs, i32 x_exp, const i16 *win, int wLen, int memLen, A 
     cmul_half(a3, a4, y[lo + 1], y[lo], sn[2 * idx], sn[2 * idx + 1]);
     a1 = mpy32x16k(y[hi], 23170) >> 1;
     a2 = mpy32x16k(y[hi + 1], 23170) >> 1;
-    y[hi] = l_add(a1, a2);
-    y[lo + 1] = l_sub(a1, a2);
-    y[hi + 1] = l_neg(a3);
+    y[hi] = a1 + a2; // |a1|, |a2| < 2^30
+    y[lo + 1] = a1 - a2;
+    y[hi + 1] = -a3;
     y[lo] = a4;
     return s_add(y_e, 2);
 }

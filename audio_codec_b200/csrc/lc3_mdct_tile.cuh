@@ -32,6 +32,7 @@ template <int N> struct MdctTile {
     static constexpr int SC = (N % 3 == 0) ? (N == 480 ? 2 : 4) : (N == 320 ? 2 : 4); // twiddle stride of cfft<M> (lc3_fft.cuh)
     static constexpr int WOFF = (N % 3 == 0) ? 60 : 40;
     static constexpr int FFT_SCALE = (M == 240) ? 9 : 8;
+    static constexpr bool SAT = FftNeedsSat<M>::v; // saturating FFT operators where the overflow bound does not close (lc3_fft.cuh)
     // twiddle tables, copied to shared memory by the kernel: in this mapping their indices differ from lane to lane,
     // which the constant cache serialises (one address per cycle); entries used: pre-twiddle N, post-twiddle
     // 2 * (M/2) * step + 2, column twiddles up to SC * (M - 1) + 2 - WOFF
@@ -121,7 +122,7 @@ template <int N> LC3_HD void mt_pre(i32 *X, const i32 *mx, const i32 *mn, int fr
         i32 a1, a2, a3, a4;
         cmul_half(a1, a2, q1, p0, tw[4 * kk], tw[4 * kk + 1]);
         cmul_half(a3, a4, q0, p1, tw[4 * kk + 2], tw[4 * kk + 3]);
-        cpx o0 = {a2, a1}, o1 = {a4, l_neg(a3)};
+        cpx o0 = {a2, a1}, o1 = {a4, -a3}; // cmul_half outputs are below 2^31 in magnitude
         mt_st2(y + lo, o0); mt_st2(y + hi, o1);
     }
 }
@@ -131,7 +132,7 @@ template <int N> LC3_HD void mt_leaf(i32 *X, int fr, int i)
 {
     typedef MdctTile<N> G;
     i32 *y = X + fr * G::S + 2 * i;
-    fft_leaf<G::LEAF>(
+    fft_leaf<G::LEAF, G::SAT>(
         [&](int m) { cpx c = mt_ld2(y + 18 * m); c.re >>= 5; c.im >>= 5; return c; },
         [&](int m, cpx c) { mt_st2(y + 18 * m, c); });
 }
@@ -151,11 +152,12 @@ template <int N> LC3_HD void mt_col_compute(const i32 *X, int fr, int i, cpx *o,
             v[k].im = a.im >> 1;
         } else {
             const i32 c = W[G::SC * i + G::SC * k * G::LEAF - G::WOFF], d = W[G::SC * i + G::SC * k * G::LEAF + 1 - G::WOFF];
-            v[k].re = l_sub(mpy32x16(a.re, c), mpy32x16(a.im, d)) >> 1;
-            v[k].im = l_add(mpy32x16(a.re, d), mpy32x16(a.im, c)) >> 1;
+            // same column network as fft_n2 (lc3_fft.cuh): plain arithmetic by the bound proved there
+            v[k].re = fs<G::SAT>(mul16<G::SAT>(a.re, c), mul16<G::SAT>(a.im, d)) >> 1;
+            v[k].im = fa<G::SAT>(mul16<G::SAT>(a.re, d), mul16<G::SAT>(a.im, c)) >> 1;
         }
     }
-    dft8<false>(v, o);
+    dft8<false, G::SAT>(v, o);
 }
 template <int N> LC3_HD void mt_col_store(i32 *X, int fr, int i, const cpx *o)
 {
@@ -182,13 +184,13 @@ template <int N> LC3_HD void mt_post(i32 *X, int fr, int l, const MtTabs &T)
             cmul_half(a3, a4, L.im, L.re, sn[2 * p * step], sn[2 * p * step + 1]);
             a1 = mpy32x16k(H.re, 23170) >> 1;
             a2 = mpy32x16k(H.im, 23170) >> 1;
-            oH.re = l_add(a1, a2); oL.im = l_sub(a1, a2); oH.im = l_neg(a3); oL.re = a4;
+            oH.re = a1 + a2; oL.im = a1 - a2; oH.im = -a3; oL.re = a4; // |a1|, |a2| < 2^30; a3 != -2^31 (see cmul_half)
         } else {
             cmul_half(a3, a4, H.re, H.im, sn[2 * (p + 1) * step], sn[2 * (p + 1) * step + 1]);
-            if (p == 0) { oH.im = l_neg(L.im >> 1); oL.re = L.re >> 1; }
+            if (p == 0) { oH.im = -(L.im >> 1); oL.re = L.re >> 1; }
             else {
                 cmul_half(a1, a2, L.im, L.re, sn[2 * p * step], sn[2 * p * step + 1]);
-                oH.im = l_neg(a1); oL.re = a2;
+                oH.im = -a1; oL.re = a2;
             }
             oL.im = a3; oH.re = a4;
         }

@@ -4,7 +4,11 @@
 #include <cstdio>
 #include <cstdint>
 #include <cstdlib>
+#define LC3_FFT_TRACE 1
+#include <vector>
+#include <cmath>
 #include "lc3_math.cuh"
+#include "lc3_fft.cuh"
 #include "lc3_rate.cuh"
 
 using namespace lc3k;
@@ -33,6 +37,52 @@ static i32 log2_poly_ref(i32 f)
 
 static int fails = 0;
 #define CHECK(name, cond, ...) do { if (!(cond)) { if (fails < 10) { printf("MISMATCH %s: ", name); printf(__VA_ARGS__); printf("\n"); } fails++; } } while (0)
+
+// ---- FFT network: no addition can leave the 32-bit range when every input component is bounded by m_in.
+// The network is linear and data independent (no branches on data), so operation k of every run computes the same
+// linear form of the 2*LEN inputs.  Basis runs (one input = amp, the rest 0) give the magnitude of each coefficient;
+// the largest value operation k can take over ALL admissible inputs is sum_i |coef_ki| * m_in, plus rounding.
+// Rounding: every shift / fractional multiply truncates by < 1 unit; the measured deviation from linearity
+// (run at 2*amp against twice the run at amp) bounds what accumulates through the network.
+template <int LEN> static void fft_bound(double m_in)
+{
+    static i32 x[2 * LEN], w[2 * LEN];
+    const i64 amp = 1 << 27;
+    FftTrace::acc = nullptr; FftTrace::n = 0;
+    for (int j = 0; j < 2 * LEN; j++) x[j] = 0;
+    cfft<LEN>(x, w);
+    const int n_ops = FftTrace::n;
+    std::vector<i64> acc(n_ops, 0), one(n_ops), two(n_ops);
+    i64 nonlin = 0;
+    for (int i = 0; i < 2 * LEN; i++) {
+        for (int rep = 0; rep < 2; rep++) {
+            for (int j = 0; j < 2 * LEN; j++) x[j] = 0;
+            x[i] = (i32)(amp << rep);
+            std::vector<i64> &dst = rep ? two : one;
+            std::fill(dst.begin(), dst.end(), 0);
+            FftTrace::acc = dst.data(); FftTrace::cap = n_ops; FftTrace::n = 0;
+            cfft<LEN>(x, w);
+            CHECK("fft ops data independent", FftTrace::n == n_ops, "LEN=%d", LEN);
+        }
+        for (int k = 0; k < n_ops; k++) {
+            acc[k] += one[k];
+            const i64 d = two[k] - 2 * one[k];
+            nonlin = std::max<i64>(nonlin, d < 0 ? -d : d);
+        }
+    }
+    FftTrace::acc = nullptr;
+    // rounding slack: per basis run the recorded |value| is within `nonlin` of |coef| * amp, so the sum over 2*LEN runs is
+    // within 2*LEN*nonlin; a real run deviates from its linear form by at most about the same amount again.
+    double worst = 0;
+    for (int k = 0; k < n_ops; k++) worst = std::max(worst, (double)acc[k] / (double)amp);
+    const double slack = (2.0 * LEN * (double)(nonlin + 1)) * m_in / (double)amp + 4096.0 * (double)(nonlin + 1);
+    const double bound = worst * m_in + slack;
+    printf("fft%-3d ops %5d  max sum|coef| %.4f  nonlinearity %lld  bound %.4f * 2^31\n", LEN, n_ops, worst, (long long)nonlin,
+           bound / 2147483648.0);
+    if (FftNeedsSat<LEN>::v) printf("       -> this length keeps the saturating operators (FftNeedsSat)\n");
+    CHECK("fft bound", FftNeedsSat<LEN>::v || bound < 2147483647.0, "LEN=%d bound=%.0f", LEN, bound);
+}
+
 
 int main(int argc, char **argv)
 {
@@ -71,6 +121,20 @@ int main(int argc, char **argv)
             CHECK("l_shl_plan", l_shl_plan(a, shl_plan(n)) == l_shl(a, n), "a=%d n=%d", a, n);
         }
         printf("ok l_shl_plan\n");
+    }
+    // FFT inputs are cmul_half() outputs: |re|, |im| <= 2^31 * max(|c| + |d|) / 2^16 + 2 over the pre-twiddle table
+    {
+        i32 mx = 0;
+        for (int i = 0; i + 1 < 1520; i += 2) mx = imax(mx, (i32)abs(rom_dct4_twiddle[i]) + (i32)abs(rom_dct4_twiddle[i + 1]));
+        i32 mx2 = 0; // post-twiddle tables (their outputs are only negated / stored)
+        for (int i = 0; i + 1 < 482; i += 2) mx2 = imax(mx2, (i32)abs(rom_sin480[i]) + (i32)abs(rom_sin480[i + 1]));
+        for (int i = 0; i + 1 < 322; i += 2) mx2 = imax(mx2, (i32)abs(rom_sin320[i]) + (i32)abs(rom_sin320[i + 1]));
+        CHECK("twiddle sums", mx <= 46341 && mx2 <= 46341, "mx=%d mx2=%d", mx, mx2);
+        const double m_in = 2147483648.0 * mx / 65536.0 + 2.0;
+        printf("pre-twiddle max |c|+|d| = %d -> FFT input bound %.5f * 2^31\n", mx, m_in / 2147483648.0);
+        fft_bound<10>(m_in); fft_bound<20>(m_in); fft_bound<30>(m_in); fft_bound<40>(m_in); fft_bound<60>(m_in);
+        fft_bound<80>(m_in); fft_bound<120>(m_in); fft_bound<160>(m_in); fft_bound<240>(m_in);
+        printf("ok fft_bound\n");
     }
     if (fails) { printf("%d mismatches\n", fails); return 1; }
     return 0;
