@@ -70,9 +70,9 @@ def profile_enable(on=True):
 
 def profile_read():
     """dict of accumulated kernel milliseconds since profile_enable()"""
-    ms = (C.c_double * 11)()
+    ms = (C.c_double * 13)()
     load_library().lc3plus_profile_read(ms)
-    return dict(zip(("stage", "fir", "scalar", "pitch", "front", "rate", "quant", "back", "span", "calls", "chunks"), list(ms)))
+    return dict(zip(("stage", "fir", "scalar", "pitch", "mdct", "sns", "tns", "rate", "quant", "back", "span", "calls", "chunks"), list(ms)))
 
 
 def set_chunk_frames(n):

@@ -13,9 +13,9 @@
 #define LC3B_MAGIC 0x4c433362u
 #define N_PIPES 3
 #define N_WORK 9
-enum { K_STAGE = 0, K_FIR, K_SCALAR, K_PITCH, K_FRONT, K_RATE, K_QUANT, K_BACK, N_KERNELS };
+enum { K_STAGE = 0, K_FIR, K_SCALAR, K_PITCH, K_FRONT, K_SNS, K_TNS, K_RATE, K_QUANT, K_BACK, N_KERNELS };
 /* kernels that read and write per-stream state: chunk c+1's launch must wait for chunk c's */
-static const int k_stateful[N_KERNELS] = {1 /* input history */, 0, 1 /* high-pass memory */, 1, 0, 1 /* rate-loop feedback */, 0, 0};
+static const int k_stateful[N_KERNELS] = {1 /* input history */, 0, 1 /* high-pass memory */, 1, 0, 0, 0, 1 /* rate-loop feedback */, 0, 0};
 
 struct LC3_Enc { /* lives in the caller's block; device state is referenced by slot */
     uint32_t magic;
@@ -294,7 +294,7 @@ static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_
         for (; g.n_ev < n_chunks * EPC; g.n_ev++) CU(cudaEventCreate(&g.ev[g.n_ev]));
     }
     int (*const launch[N_KERNELS])(const LC3K_Batch *, void *) = {lc3k_launch_stage, lc3k_launch_fir, lc3k_launch_scalar, lc3k_launch_pitch,
-                                                                  lc3k_launch_front, lc3k_launch_rate, lc3k_launch_quant, lc3k_launch_back};
+                                                                  lc3k_launch_front, lc3k_launch_sns, lc3k_launch_tns, lc3k_launch_rate, lc3k_launch_quant, lc3k_launch_back};
     /* everything queued on the main stream so far (state reset, configuration, lane tables, whole-buffer input copy)
      * is ordered before the first chunk of every pipe */
     CU(cudaEventRecord(g.start_ev, g.stream));
@@ -317,6 +317,7 @@ static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_
             }
         for (int k = 0; k < N_KERNELS; k++) {
             if (bits != 16 && (k == K_FIR || k == K_SCALAR)) continue; /* fused into K_PITCH for 24-bit input */
+            if (N < 160 && (k == K_SNS || k == K_TNS)) continue;        /* fused into K_FRONT for the short frames */
             const cudaStream_t st = k_stateful[k] ? ser : par;
             if (st != cur) { /* the chunk's kernels form a chain: hand over between the two streams */
                 CU(cudaEventRecord(g.pipe[p].hop_ev[k], cur));
@@ -347,7 +348,7 @@ static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_
         float ms;
         for (int c = 0; c < n_chunks; c++)
             for (int k = 0; k < N_KERNELS; k++) {
-                if (bits != 16 && (k == K_FIR || k == K_SCALAR)) continue;
+                if ((bits != 16 && (k == K_FIR || k == K_SCALAR)) || (N < 160 && (k == K_SNS || k == K_TNS))) continue;
                 CU(cudaEventElapsedTime(&ms, g.ev[c * EPC + 2 * k], g.ev[c * EPC + 2 * k + 1]));
                 g.prof_ms[k] += ms;
             }

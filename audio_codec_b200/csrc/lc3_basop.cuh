@@ -144,7 +144,9 @@ LC3_HD i32 l_msu0(i32 acc, i32 a, i32 b) { return l_sub(acc, a * b); }
 LC3_HD i32 hi16(i32 a) { return a >> 16; }
 LC3_HD i32 lo16(i32 a) { return (i32)(i16)a; }
 LC3_HD i32 l_dep_h(i32 a) { return (i32)((u32)a << 16); }
-LC3_HD i32 l_round(i32 a) { return l_add(a, 0x8000) >> 16; }
+// round_fx = extract_h(L_add(a, 0x8000)): high half plus the rounding bit; the one saturating case (a >= 0x7FFF8000)
+// is the only way to reach 0x8000.  Checked against the operator form over all 2^32 inputs (primcheck --full).
+LC3_HD i32 l_round(i32 a) { return imin((a >> 16) + ((a >> 15) & 1), 32767); }
 LC3_HD i32 s_mac_r(i32 acc, i32 a, i32 b) { return l_round(l_mac(acc, a, b)); }
 LC3_HD i32 s_msu_r(i32 acc, i32 a, i32 b) { return l_round(l_msu(acc, a, b)); }
 

@@ -37,7 +37,7 @@ __global__ void __launch_bounds__(QT_THREADS) k_quant(LC3K_Batch b)
 // coder loops are data dependent), and a large block holds its SM slot until its slowest warp is done (measured: 2.44 ms
 // at 4 warps per block, 2.76 at 12, 3.52 at 24)
 #define BACK_WARPS 4
-__global__ void __launch_bounds__(32 * BACK_WARPS) k_back(LC3K_Batch b)
+__global__ void __launch_bounds__(32 * BACK_WARPS, 12) k_back(LC3K_Batch b)
 {
     __shared__ u8 lut[4096];
     __shared__ uint16_t cum[1088], freq[1088];

@@ -18,7 +18,6 @@ template <int N, int BITS> __global__ void __launch_bounds__(32 * FRONT_WARPS, 1
 }
 
 // tile path, steps 2 and 3 (lc3_body_frame.cuh): one lane per channel-frame
-extern "C" int lc3k_sns_launch(const LC3K_Batch *b, void *stream); // k_sns lives in lc3_k_sns.cu (one copy for all frame lengths)
 template <int N> __global__ void __launch_bounds__(32 * TNS_WARPS, 1) k_tns(LC3K_Batch b)
 {
     const int warp = blockIdx.x * TNS_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
@@ -75,8 +74,8 @@ template <int N> static int front_launch(const LC3K_Batch *b, cudaStream_t s)
     return (int)cudaGetLastError();
 }
 
-// frame lengths with an 8-column FFT: tile kernel (MDCT + band energies), then SNS and shaping/TNS/energies, each one
-// lane per channel-frame
+// frame lengths with an 8-column FFT: tile kernel (MDCT + band energies); SNS (lc3_k_sns.cu) and shaping/TNS/energies
+// (tns_launch below) follow as their own launches, each one lane per channel-frame
 template <int N> static int front_launch_tiled(const LC3K_Batch *b, cudaStream_t s)
 {
     static bool attr_set = false;
@@ -87,10 +86,14 @@ template <int N> static int front_launch_tiled(const LC3K_Batch *b, cudaStream_t
         if (e != cudaSuccess) return (int)e;
         attr_set = true;
     }
-    const int tiles = b->n_frames * b->n_tiles, blocks = (tiles + TNS_WARPS - 1) / TNS_WARPS;
+    const int tiles = b->n_frames * b->n_tiles;
     if (b->bits == 16) k_mdct<N, 16><<<tiles, 256, smem, s>>>(*b);
     else k_mdct<N, 24><<<tiles, 256, smem, s>>>(*b);
-    { const int e = lc3k_sns_launch(b, s); if (e) return e; }
+    return (int)cudaGetLastError();
+}
+template <int N> static int tns_launch(const LC3K_Batch *b, cudaStream_t s)
+{
+    const int tiles = b->n_frames * b->n_tiles, blocks = (tiles + TNS_WARPS - 1) / TNS_WARPS;
     k_tns<N><<<blocks, 32 * TNS_WARPS, 0, s>>>(*b);
     return (int)cudaGetLastError();
 }

@@ -97,7 +97,9 @@ int lc3k_launch_stage(const LC3K_Batch *b, void *stream);
 int lc3k_launch_fir(const LC3K_Batch *b, void *stream);     /* 16-bit input only (no-op otherwise): resampler FIR, frame-parallel */
 int lc3k_launch_scalar(const LC3K_Batch *b, void *stream);  /* 16-bit input only (no-op otherwise): 50 Hz high-pass recursion, lane per stream */
 int lc3k_launch_pitch(const LC3K_Batch *b, void *stream);   /* pitch analysis + attack detector, warp per stream (24-bit: also the two above) */
-int lc3k_launch_front(const LC3K_Batch *b, void *stream);
+int lc3k_launch_front(const LC3K_Batch *b, void *stream);   /* N >= 160: tile MDCT + band energies; N < 160: the whole spectral front end */
+int lc3k_launch_sns(const LC3K_Batch *b, void *stream);     /* N >= 160 only (no-op otherwise): bandwidth detector + SNS */
+int lc3k_launch_tns(const LC3K_Batch *b, void *stream);     /* N >= 160 only (no-op otherwise): shaping, TNS, quadruple energies */
 int lc3k_launch_rate(const LC3K_Batch *b, void *stream);
 int lc3k_launch_quant(const LC3K_Batch *b, void *stream);   /* gain adjustment + final quantisation, block per tile */
 int lc3k_launch_back(const LC3K_Batch *b, void *stream);

@@ -26,23 +26,31 @@ template <class A, class E> LC3_HD i32 gain_energies(A x, i32 x_e, int lg, E en)
 {
     i32 x_max = 0;
     const int lg4 = lg >> 2;
-    for (int i = 0; i < lg4; i++) {
-        i32 v0 = x[4 * i], v1 = x[4 * i + 1], v2 = x[4 * i + 2], v3 = x[4 * i + 3];
-        i32 m = l_max(l_max(l_abs(v0), l_abs(v1)), l_max(l_abs(v2), l_abs(v3)));
-        x_max = l_max(x_max, m);
-        i32 s = m != 0 ? l_norm(m) : 31;
-        s = s - 2;
-        // the shift leaves 2 bits of headroom, the rounded values are below 2^13 and 1 + 4 * 2 * t^2 < 2^29:
-        // none of the reference's saturating operators (L_shl, round_fx, L_mac) can saturate here
-        i32 e = 1, t;
-        t = (l_shl_ns(v0, s) + 0x8000) >> 16; e += 2 * t * t;
-        t = (l_shl_ns(v1, s) + 0x8000) >> 16; e += 2 * t * t;
-        t = (l_shl_ns(v2, s) + 0x8000) >> 16; e += 2 * t * t;
-        t = (l_shl_ns(v3, s) + 0x8000) >> 16; e += 2 * t * t;
-        s = s_shl(s_sub(x_e, s), 1);
-        if (e == 1 && s < 0) s = 0;
-        t = l_add(m_log2(e), l_shl_p(s, 25) );
-        en[i] = l_add(mpy32x16k(t, 0x436E) >> 6, 0x9CCCD);
+    for (int i0 = 0; i0 < lg4; i0 += 2) { // two quadruples per round: eight loads in flight
+        i32 w[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) w[k] = 4 * i0 + k < lg ? x[4 * i0 + k] : 0;
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            const int i = i0 + h;
+            if (i >= lg4) break;
+            const i32 v0 = w[4 * h], v1 = w[4 * h + 1], v2 = w[4 * h + 2], v3 = w[4 * h + 3];
+            i32 m = l_max(l_max(l_abs(v0), l_abs(v1)), l_max(l_abs(v2), l_abs(v3)));
+            x_max = l_max(x_max, m);
+            i32 s = m != 0 ? l_norm(m) : 31;
+            s = s - 2;
+            // the shift leaves 2 bits of headroom, the rounded values are below 2^13 and 1 + 4 * 2 * t^2 < 2^29:
+            // none of the reference's saturating operators (L_shl, round_fx, L_mac) can saturate here
+            i32 e = 1, t;
+            t = (l_shl_ns(v0, s) + 0x8000) >> 16; e += 2 * t * t;
+            t = (l_shl_ns(v1, s) + 0x8000) >> 16; e += 2 * t * t;
+            t = (l_shl_ns(v2, s) + 0x8000) >> 16; e += 2 * t * t;
+            t = (l_shl_ns(v3, s) + 0x8000) >> 16; e += 2 * t * t;
+            s = s_shl(s_sub(x_e, s), 1);
+            if (e == 1 && s < 0) s = 0;
+            t = l_add(m_log2(e), l_shl_p(s, 25) );
+            en[i] = l_add(mpy32x16k(t, 0x436E) >> 6, 0x9CCCD);
+        }
     }
     return x_max;
 }

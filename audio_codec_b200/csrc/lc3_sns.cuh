@@ -436,16 +436,26 @@ LC3_HD void sns_interp(const i16 *q, i16 *g, i16 *g_exp, int nbands)
     }
 }
 
-// fx/mdct_shaping_fx.c:14-35
+// fx/mdct_shaping_fx.c:14-35.  The bins are loaded eight at a time ahead of their use (the pass is bound by the number
+// of global loads in flight); the band of each bin is tracked with a running index.
 template <class A> LC3_HD void mdct_shape(A d, const i16 *g, const i16 *g_exp, const i16 *bo, int nbands)
 {
-    int j = 0;
-    for (int b = 0; b < nbands; b++) {
-        const i32 gg = g[b];
-        const ShlPlan ge = shl_plan(g_exp[b]);
-        const int stop = bo[b + 1];
-#pragma unroll 4
-        for (; j < stop; j++) d[j] = l_shl_plan(mpy32x16k(d[j], gg), ge); // gg > 0 (2^x mantissa)
+    const int total = bo[nbands];
+    int b = 0, stop = bo[1];
+    i32 gg = g[0];
+    ShlPlan ge = shl_plan(g_exp[0]);
+    for (int base = 0; base < total; base += 8) {
+        i32 v[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[k] = base + k < total ? d[base + k] : 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const int j = base + k;
+            if (j < total) {
+                while (j >= stop) { b++; stop = bo[b + 1]; gg = g[b]; ge = shl_plan(g_exp[b]); }
+                d[j] = l_shl_plan(mpy32x16k(v[k], gg), ge); // gg > 0 (2^x mantissa)
+            }
+        }
     }
 }
 

@@ -5,6 +5,21 @@
 
 namespace lc3k {
 
+// f(x[lo + i]) for i = 0 .. n-1 in order, with the loads issued U at a time ahead of their use: the lane-per-frame
+// passes over the spectrum are bound by the number of global loads in flight, not by bandwidth or arithmetic
+template <int U, class A, class F> LC3_HD void for_batched(A x, int lo, int n, F f)
+{
+    int i = 0;
+    for (; i + U <= n; i += U) {
+        i32 v[U];
+#pragma unroll
+        for (int k = 0; k < U; k++) v[k] = x[lo + i + k];
+#pragma unroll
+        for (int k = 0; k < U; k++) f(v[k]);
+    }
+    for (; i < n; i++) f(x[lo + i]);
+}
+
 // num * (1/den) with one Newton step, <<2 (fx/levinson_fx.c:45-46, :75-76, :150-152)
 LC3_HD i32 div_newton(i32 num, i32 den)
 {
@@ -89,15 +104,15 @@ template <int MAXORD, class A> LC3_HD void tns_coder(TnsOut &o, A x, int bw, int
         for (int sd = 0; sd < nsub; sd++) {
             const int lo = sub_lo[nsub * j + sd], n = sub_hi[nsub * j + sd] - lo;
             Range rg; range_init(rg);
-            for (int i = 0; i < n; i++) range_add(rg, x[lo + i]);
+            for_batched<8>(x, lo, n, [&](i32 v) { range_add(rg, v); });
             const i32 headroom = range_headroom32(rg, 0);
             // Norm32Norm (fx/basop_util.c:534-569): energy with a sequentially adapted pre-shift
             i32 sh = headroom, nrg = 0;
-            for (int i = 0; i < n; i++) {
+            for_batched<8>(x, lo, n, [&](i32 v) {
                 if (nrg >= 0x40000000) { sh = s_sub(sh, 1); nrg = nrg >> 2; }
-                i32 t = l_round(l_shl_ns(x[lo + i], sh)); // sh <= block headroom
-                nrg += t * t;                             // nrg < 2^30 here and t^2 <= 2^30: L_mac0 cannot saturate
-            }
+                i32 t = l_round(l_shl_ns(v, sh)); // sh <= block headroom
+                nrg += t * t;                     // nrg < 2^30 here and t^2 <= 2^30: L_mac0 cannot saturate
+            });
             if (nrg != 0) {
                 i32 s = s_norm(n);
                 nrg = l_add(nrg, l_shl(mpy32x16(0x0000fffd, s_shl(n, s)), s_sub(15, s)));
@@ -129,15 +144,15 @@ template <int MAXORD, class A> LC3_HD void tns_coder(TnsOut &o, A x, int bw, int
             i64 e0 = 0;
 #pragma unroll
             for (int l = 0; l <= MAXORD; l++) { acc[l] = 0; hist[l] = 0; }
-            for (int i = 0; i < n; i++) {
-                i32 v = l_round(l_shl_ns(x[lo + i], shifts)); // shifts <= block headroom
+            for_batched<8>(x, lo, n, [&](i32 xv) {
+                i32 v = l_round(l_shl_ns(xv, shifts)); // shifts <= block headroom
 #pragma unroll
                 for (int l = MAXORD; l > 0; l--) hist[l] = hist[l - 1];
                 hist[0] = v;
                 e0 += (i64)v * v;
 #pragma unroll
                 for (int l = 1; l <= MAXORD; l++) acc[l] += hist[l] * v;
-            }
+            });
             if (e0 <= LC3_I32_MAX) {
                 acc[0] = (i32)e0;
             } else {

@@ -251,7 +251,7 @@ def main():
     except Exception:
         pass
     hbm_peak, peak_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json)") if "hbm_gbs" in peaks else (6650.0, "fallback")
-    kern = {k: prof[k] for k in ("stage", "fir", "scalar", "pitch", "front", "rate", "quant", "back")}
+    kern = {k: prof[k] for k in ("stage", "fir", "scalar", "pitch", "mdct", "sns", "tns", "rate", "quant", "back")}
     top = max(kern, key=kern.get)
     n_launch = prof["chunks"]
     avg_ms = kern[top] / n_launch

@@ -103,7 +103,8 @@ void lc3plus_enc_release(LC3_Enc *encoder);
 /* NEW: number of kernels launched by this process so far (for benchmarks' gpu_launches). */
 long long lc3plus_kernel_launches(void);
 /* NEW: per-kernel device timing with CUDA events on the library's launching stream.  After enable(1), every
- * batch call accumulates into ms[11] = {stage, fir, scalar, pitch, front, rate, quant, back kernel ms (each bracketed by events
+ * batch call accumulates into ms[13] = {stage, fir, scalar, pitch, mdct (the whole front end for frames shorter than 160 samples), sns, tns, rate,
+ * quant, back kernel ms (each bracketed by events
  * on the stream it was launched on; chunks overlap, so these can sum to more than the span), start-of-first-chunk to
  * end-of-last-chunk span ms, calls, chunks}; enable() also clears the accumulators. */
 void lc3plus_profile_enable(int on);

@@ -108,6 +108,20 @@ int main(int argc, char **argv)
         for (i32 f = 0; f < 16384; f++) CHECK("m_log2_poly", m_log2_poly(f) == log2_poly_ref(f), "f=%d", f);
         printf("ok m_log2_poly\n");
     }
+    // round_fx
+    {
+        auto ref = [](i32 a) { return l_add(a, 0x8000) >> 16; };
+        const bool full = argc > 2;
+        if (full) {
+            for (int64_t a = -2147483648LL; a <= 2147483647LL; a++) CHECK("l_round", l_round((i32)a) == ref((i32)a), "a=%d", (i32)a);
+        } else {
+            for (int64_t c : {-2147483648LL, -65536LL, 0LL, 65536LL, 2147418112LL, 2147483647LL})
+                for (int64_t a = std::max<int64_t>(c - 200000, -2147483648LL); a <= std::min<int64_t>(c + 200000, 2147483647LL); a++)
+                    CHECK("l_round", l_round((i32)a) == ref((i32)a), "a=%d", (i32)a);
+            for (long i = 0; i < n_rand; i++) { const i32 a = (i32)rnd(); CHECK("l_round", l_round(a) == ref(a), "a=%d", a); }
+        }
+        printf("ok l_round%s\n", full ? " (all 2^32 inputs)" : "");
+    }
     // L_shl with a planned count
     {
         const i32 edge[] = {0, 1, -1, 2, -2, 3, -3, 0x7fffffff, LC3_I32_MIN, LC3_I32_MIN + 1, 0x40000000, -0x40000000, 0x3fffffff, -0x40000001,
