@@ -255,17 +255,27 @@ template <int BITS, bool PRE> LC3_HD void pitch_warp_body(const LC3K_Batch &b, i
             const i32 p2 = lo > hi ? lo : argmax_index(warp_max64(sh.red.q2));
 
             // ---- F. normalised correlation at the candidates (olpa_fx.c:126-155, :174-205): lane = sample
+            // both candidates in one sweep over the samples; the two normalisations (a serial chain of ~190 operations each)
+            // then run side by side on lanes 0 and 1 instead of one after the other on the whole warp
             i32 nc[2] = {0, 0};
             const int ncand = p != p2 ? 2 : 1;
-            for (int c = 0; c < ncand; c++) {
-                const int lag = c == 0 ? p : p2;
-                LC3_LANES(l)
-                    i32 a0 = 0, a1 = 0, a2 = 0;
-                    for (int m = l; m < acflen6; m += 32) { i32 x = s[m], y = s[m - lag]; a0 += x * y; a1 += y * y; a2 += x * x; }
-                    sh.red.a[l] = a0; sh.red.b[l] = a1; sh.red.c[l] = a2;
-                LC3_LANES_END
+            LC3_LANES(l)
+                i32 a0 = 0, a1 = 0, a2 = 0, b0 = 0, b1 = 0;
+                for (int m = l; m < acflen6; m += 32) {
+                    const i32 x = s[m], y = s[m - p], z = s[m - p2];
+                    a0 += x * y; a1 += y * y; a2 += x * x; b0 += x * z; b1 += z * z;
+                }
+                sh.red.a[l] = a0; sh.red.b[l] = a1; sh.red.c[l] = a2; sh.red.d[l] = b0; sh.xc[l] = b1;
+            LC3_LANES_END
+            {
                 const i32 s0 = warp_sum(sh.red.a), s1 = warp_sum(sh.red.b) + 1, s2 = warp_sum(sh.red.c) + 1;
-                nc[c] = normcorr_q15(s0, s1, s2, 0, 0);
+                const i32 t0 = warp_sum(sh.red.d), t1 = warp_sum(sh.xc) + 1;
+                LC3_LANES(l)
+                    if (l < ncand) sh.red.a[l] = l == 0 ? normcorr_q15(s0, s1, s2, 0, 0) : normcorr_q15(t0, t1, s2, 0, 0);
+                LC3_LANES_END
+                nc[0] = sh.red.a[0];
+                if (ncand == 2) nc[1] = sh.red.a[1];
+                LC3_SYNC;
             }
             normcorr = nc[0];
             if (p != p2 && s_sub(nc[1], s_mult_r(nc[0], 27853)) > 0) { p = p2; normcorr = nc[1]; }
@@ -388,14 +398,20 @@ template <int BITS, bool PRE> LC3_HD void pitch_warp_body(const LC3K_Batch &b, i
                     const int res = pit < 127 ? 1 : 2;
                     int fr0 = pit < 127 ? -3 : -2;
                     if (pit == min_p) fr0 = 0;
-                    i32 best = LC3_I32_MIN;
-                    for (int fr = fr0; fr < 4; fr += res) {
-                        const i16 *h = &rom_ltpf_ac_interp[(fr + 3) * 9];
-                        i32 s = l_mult0(sh.ac[p_int - ac_lo - 4], h[0]);
-                        for (int k = 1; k < 9; k++) s = l_mac0(s, sh.ac[p_int - ac_lo - 4 + k], h[k]);
-                        if (l_sub(s, best) > 0) p_fr = fr;
-                        best = l_max(best, s);
-                    }
+                    // one candidate fraction per lane (at most 7), first strict maximum wins as in the reference's scan
+                    LC3_LANES(l)
+                        const int fr = fr0 + l * res;
+                        i64 key = LC3_I32_MIN * (i64)4294967296LL;
+                        if (fr < 4) {
+                            const i16 *h = &rom_ltpf_ac_interp[(fr + 3) * 9];
+                            i32 s = l_mult0(sh.ac[p_int - ac_lo - 4], h[0]);
+                            for (int k = 1; k < 9; k++) s = l_mac0(s, sh.ac[p_int - ac_lo - 4 + k], h[k]);
+                            if (s != LC3_I32_MIN) key = argmax_key(s, l); // a sum of -2^31 never beats the scan's initial value
+                        }
+                        sh.red.q[l] = key;
+                    LC3_LANES_END
+                    const i64 bk = warp_max64(sh.red.q);
+                    if (bk != LC3_I32_MIN * (i64)4294967296LL) p_fr = fr0 + argmax_index(bk) * res;
                     if (p_fr < 0) { p_int = s_sub(p_int, 1); p_fr = s_add(p_fr, 4); }
                     if (p_int >= 127) p_idx = s_add(s_add(s_shl(p_int, 1), p_fr >> 1), 126);
                     else p_idx = s_sub(s_add(s_shl(p_int, 2), p_fr), 128);
