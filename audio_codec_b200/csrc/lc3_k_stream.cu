@@ -78,7 +78,7 @@ __global__ void __launch_bounds__(128) k_fir(LC3K_Batch b)
 // scalar recursions (high-pass, attack detector): one lane per channel-stream
 __global__ void __launch_bounds__(32) k_scalar(LC3K_Batch b) { scalar_body(b, blockIdx.x, threadIdx.x); }
 
-__global__ void __launch_bounds__(128) k_rate(LC3K_Batch b)
+__global__ void __launch_bounds__(128, 7) k_rate(LC3K_Batch b)
 {
     __shared__ RateShared sh[4];
     __shared__ u8 lut[4096];

@@ -13,10 +13,10 @@
 
 namespace lc3k {
 
+constexpr int RATE_MAXT = (LC3K_MAX_N / 2 + 31) / 32; // tuples per lane (8; yLen <= 400 uses 7)
+
 struct RateShared {
     WarpRed red;
-    i32 en[LC3K_MAX_N / 4];      // per-quadruple log-energies of the frame
-    i16 xq[LC3K_MAX_N];
     u8 tv[LC3K_MAX_N / 2 + 2];   // magnitude class of each tuple, offset by 2 (tv[0] = tv[1] = 0)
 };
 
@@ -71,33 +71,36 @@ LC3_HD void rate_warp_body(const LC3K_Batch &b, int li, RateShared &sh, const u8
             i32 offset = l_dep_h(s_add(255, qgain_off));
             const i32 target = l_shl_p(l_mult(0x7D71, nbitsSQ), 1);
             i32 fac = 0x1000000;
+            // |en| < 2^25 by construction (gain_energies: (mpy32x16k(t, 0x436E) >> 6) + 0x9CCCD for any 32-bit t) and
+            // |offset| < 2^24 (a gain index in [0, 255] << 16 minus at most 255 << 16): en - offset cannot saturate
+            // and a quadruple's cost is below 2^27 (tests/hostsim/primcheck.cpp: rate_bounds).
+            // The four quadruples of a lane stay in registers over the eight steps.
+            LC3_PERLANE(i32, enr, 4);
             LC3_LANES(l)
-                for (int i = l; i < lg4; i += 32) sh.en[i] = en[i];
+#pragma unroll
+                for (int k = 0; k < 4; k++) LC3_PL(enr, k, l) = l + 32 * k < lg4 ? en[l + 32 * k] : -(1 << 30);
             LC3_LANES_END
             for (int it = 0; it < 8; it++) {
                 fac = fac >> 1;
                 offset = l_sub(offset, fac);
                 // One pass: every quadruple at or above the threshold adds its own cost; the ones below it cost
-                // 0x3C7AE each, but only underneath the highest one above it -- and there are
-                // top + 1 - (number above) of those, so they need no second pass.
+                // 0x3C7AE each, but only underneath the highest one above it -- top + 1 - (number above) of those,
+                // so each one above carries -0x3C7AE and the reduction needs no count.
                 LC3_LANES(l)
-                    i32 top = -1, cnt = 0;
-                    i64 est = 0;
-                    for (int i = l; i < lg4; i += 32) {
-                        const i32 t = l_sub(sh.en[i], offset);
+                    i32 top = -1, est = 0; // four terms below 2^27
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        const i32 t = LC3_PL(enr, k, l) - offset;
                         if (t >= 0x9CCCD) {
-                            top = i; cnt++;
-                            est += t;
-                            const i32 d2 = l_sub(t, 0x460000);
-                            if (d2 >= 0) est += d2;
+                            top = l + 32 * k;
+                            est += t - 0x3C7AE + imax(t - 0x460000, 0);
                         }
                     }
-                    // a lane holds at most 4 quadruples, each term < 2^33: the total splits into two 32-bit sums
-                    sh.red.a[l] = (i32)(est & 0xFFFFF); sh.red.b[l] = (i32)(est >> 20); sh.red.c[l] = cnt; sh.red.d[l] = top;
+                    sh.red.a[l] = est & 0xFFFF; sh.red.b[l] = est >> 16; sh.red.d[l] = top;
                 LC3_LANES_END
                 const i32 top = warp_max(sh.red.d);
-                i64 est64 = ((i64)warp_sum(sh.red.b) << 20) + warp_sum(sh.red.a);
-                if (top >= 0) est64 += (i64)0x3C7AE * (top + 1 - warp_sum(sh.red.c));
+                i64 est64 = ((i64)warp_sum(sh.red.b) << 16) + warp_sum(sh.red.a);
+                if (top >= 0) est64 += (i64)0x3C7AE * (top + 1);
                 const i32 est = clamp64(est64);
                 if (est > target && top >= 0) offset = l_add(offset, fac);
             }
@@ -112,35 +115,39 @@ LC3_HD void rate_warp_body(const LC3K_Batch &b, int li, RateShared &sh, const u8
         i32 ge = gain_e;
         const i32 inv = m_inv16(gain, &ge);
         const i32 s = s_sub(s_add(x_e, ge), 15);
+        // lane l owns tuples l, l + 32, ...: their magnitudes stay in its registers between the two phases
+        LC3_PERLANE(i32, ab, RATE_MAXT);
         LC3_LANES(l)
             i32 last = 0;
-            for (int i = l; i < nt; i += 32) {
-                const i32 q = quant_bin(d[i], inv, s);
-                sh.xq[i] = (i16)q;
-                if (q != 0 && i >= 2) last = (i | 1) + 1; // find_last_nz_pair: pairs below bin 2 are not looked at
-            }
-            sh.red.a[l] = last;
-            if (l < 2) sh.tv[l] = 0;
-        LC3_LANES_END
-        const i32 lastnz = imax(warp_max(sh.red.a), 2);
-        LC3_LANES(l) // magnitude class of every tuple (the value the reference folds into the next context)
-            for (int k = 2 * l; k < lastnz; k += 64) {
-                const i32 a1 = s_abs(sh.xq[k]), b1 = s_abs(sh.xq[k + 1]), mx = imax(a1, b1);
+#pragma unroll
+            for (int m = 0; m < RATE_MAXT; m++) {
+                const int k = 2 * l + 64 * m;
+                if (k >= nt) break;
+                const i32 a1 = s_abs((i16)quant_bin(d[k], inv, s)), b1 = s_abs((i16)quant_bin(d[k + 1], inv, s)), mx = imax(a1, b1);
+                LC3_PL(ab, m, l) = a1 | (b1 << 16);
+                // magnitude class of the tuple (the value the reference folds into the next two contexts)
                 i32 t;
                 if (mx == 0) t = 1;
                 else if (mx < 4) t = a1 + b1 + 1;
                 else if (mx < 8) t = 2 * ((a1 >> 1) + (b1 >> 1)) + 1;
                 else t = 12 + imin(13 - s_norm(mx), 3);
                 sh.tv[2 + (k >> 1)] = (u8)t;
+                if (mx != 0 && k >= 2) last = k + 2; // find_last_nz_pair: the pair below bin 2 is not looked at
             }
+            sh.red.a[l] = last;
+            if (l < 2) sh.tv[l] = 0;
         LC3_LANES_END
+        const i32 lastnz = imax(warp_max(sh.red.a), 2);
         LC3_LANES(l)
             i32 nb = 0;
-            for (int k = 2 * l; k < lastnz; k += 64) {
+#pragma unroll
+            for (int m = 0; m < RATE_MAXT; m++) {
+                const int k = 2 * l + 64 * m;
+                if (k >= lastnz) break;
                 const int j = k >> 1;
                 i32 t = ((i32)sh.tv[j] << 4) + sh.tv[j + 1] + rateFlag; // tv[j] = class of tuple j-2, tv[j+1] = of j-1
                 if (k > nt_half) t += 1 << 8;
-                const i32 a1 = s_abs(sh.xq[k]), b1 = s_abs(sh.xq[k + 1]), mx = imax(a1, b1);
+                const i32 a1 = LC3_PL(ab, m, l) & 0xffff, b1 = LC3_PL(ab, m, l) >> 16, mx = imax(a1, b1);
                 if (mx == 0) { nb += ari_bits(ari_lut, ari_bitstab, t, 0); continue; }
                 i32 lev, am, bm;
                 if (mx < 4) {

@@ -19,6 +19,9 @@ namespace lc3k {
 #define LC3_LANE0 if ((threadIdx.x & 31) == 0) {
 #define LC3_LANE0_END } __syncwarp();
 #define LC3_SYNC __syncwarp()
+// a small per-lane array that lives across LANES phases: registers on the device, [n][32] on the host
+#define LC3_PERLANE(T, name, n) T name[n]
+#define LC3_PL(name, k, l) name[k]
 LC3_HD i32 warp_max(const i32 *red) { return __reduce_max_sync(0xffffffffu, red[threadIdx.x & 31]); }
 LC3_HD i32 warp_min(const i32 *red) { return __reduce_min_sync(0xffffffffu, red[threadIdx.x & 31]); }
 LC3_HD i32 warp_sum(const i32 *red) { return __reduce_add_sync(0xffffffffu, red[threadIdx.x & 31]); }
@@ -42,6 +45,8 @@ LC3_HD i64 warp_max64(const i64 *red)
 #define LC3_LANE0 {
 #define LC3_LANE0_END }
 #define LC3_SYNC ((void)0)
+#define LC3_PERLANE(T, name, n) T name[n][32]
+#define LC3_PL(name, k, l) name[k][l]
 LC3_HD i32 warp_max(const i32 *red) { i32 v = red[0]; for (int i = 1; i < 32; i++) v = red[i] > v ? red[i] : v; return v; }
 LC3_HD i32 warp_min(const i32 *red) { i32 v = red[0]; for (int i = 1; i < 32; i++) v = red[i] < v ? red[i] : v; return v; }
 LC3_HD i32 warp_sum(const i32 *red) { i32 v = 0; for (int i = 0; i < 32; i++) v += red[i]; return v; }

@@ -150,6 +150,17 @@ int main(int argc, char **argv)
         fft_bound<80>(m_in); fft_bound<120>(m_in); fft_bound<160>(m_in); fft_bound<240>(m_in);
         printf("ok fft_bound\n");
     }
+    // rate-loop bisection (lc3_rate_warp.cuh): the quadruple energy written by gain_energies() is
+    // (mpy32x16k(t, 0x436E) >> 6) + 0x9CCCD, monotone in t, so its range is set by the two extremes of t
+    {
+        const i32 lo = l_add(mpy32x16k(LC3_I32_MIN, 0x436E) >> 6, 0x9CCCD), hi = l_add(mpy32x16k(LC3_I32_MAX, 0x436E) >> 6, 0x9CCCD);
+        CHECK("rate_bounds", lo > -(1 << 25) && hi < (1 << 25), "lo=%d hi=%d", lo, hi);
+        // offset = (255 + qgain_off) << 16 with 255 + qgain_off in [0, 255], moved by at most 255 << 16 either way
+        const int64_t off_max = (int64_t)(255 + 255) << 16, t_max = (int64_t)hi + off_max, t_min = (int64_t)lo - off_max;
+        CHECK("rate_bounds", t_max < (1 << 26) && t_min > -(1 << 26), "t range");
+        CHECK("rate_bounds", 4 * (2 * t_max) < 2147483647LL, "lane sum"); // four quadruples per lane, each t + (t - 0x460000)
+        printf("ok rate_bounds en in [%d, %d]\n", lo, hi);
+    }
     if (fails) { printf("%d mismatches\n", fails); return 1; }
     return 0;
 }
