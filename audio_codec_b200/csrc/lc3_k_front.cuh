@@ -1,6 +1,7 @@
 // spectral front-end kernels, instantiated per frame length in lc3_k_front_*.cu (split for parallel builds)
 #pragma once
 #include <cuda_runtime.h>
+#include <cstdio>
 #include "lc3_body_frame.cuh"
 
 using namespace lc3k;
@@ -21,8 +22,15 @@ template <int N, int BITS> __global__ void __launch_bounds__(32 * FRONT_WARPS, 1
 template <int N> __global__ void __launch_bounds__(32 * TNS_WARPS, 1) k_tns(LC3K_Batch b)
 {
     const int warp = blockIdx.x * TNS_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+#ifdef LC3_DBG_TNS
+    if (lane == 0 && warp < 16384) { lc3k_dbg[8 * warp + 6] = 0; lc3k_dbg[8 * warp + 7] = 0; }
+    LC3_DBG_MARK(0);
+#endif
     if (warp >= b.n_frames * b.n_tiles) return;
     tns_body<N>(b, warp / b.n_tiles, warp % b.n_tiles, lane);
+#ifdef LC3_DBG_TNS
+    LC3_DBG_MARK(5);
+#endif
 }
 
 // MDCT of one tile (32 channel-frames) per block, spectrum in shared memory (lc3_mdct_tile.cuh).  In the twiddle,

@@ -3,6 +3,18 @@
 #pragma once
 #include "lc3_math.cuh"
 
+#if defined(LC3_DBG_TNS) && defined(__CUDACC__)
+static __device__ unsigned long long lc3k_dbg[8 * 16384];
+#endif
+#if defined(LC3_DBG_TNS) && defined(__CUDA_ARCH__)
+#define LC3_DBG_MARK(k) do { __syncwarp(); unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); \
+    const int w_ = blockIdx.x * 24 + (threadIdx.x >> 5); if ((threadIdx.x & 31) == 0 && w_ < 16384) lc3k_dbg[8 * w_ + (k)] = t_; } while (0)
+#define LC3_DBG_COUNT(k) do { const int w_ = blockIdx.x * 24 + (threadIdx.x >> 5); if (w_ < 16384) atomicAdd(&lc3k_dbg[8 * w_ + (k)], 1ull); } while (0)
+#else
+#define LC3_DBG_MARK(k) ((void)0)
+#define LC3_DBG_COUNT(k) ((void)0)
+#endif
+
 namespace lc3k {
 
 // f(x[lo + i]) for i = 0 .. n-1 in order, with the loads issued U at a time ahead of their use: the lane-per-frame
@@ -156,6 +168,7 @@ template <int MAXORD, class A> LC3_HD void tns_coder(TnsOut &o, A x, int bw, int
             if (e0 <= LC3_I32_MAX) {
                 acc[0] = (i32)e0;
             } else {
+                LC3_DBG_COUNT(6);
 #pragma unroll
                 for (int l = 0; l <= MAXORD; l++) { acc[l] = 0; hist[l] = 0; }
                 for (int i = 0; i < n; i++) {
@@ -176,7 +189,9 @@ template <int MAXORD, class A> LC3_HD void tns_coder(TnsOut &o, A x, int bw, int
             }
         }
 
+        if (j == 0) LC3_DBG_MARK(2);
         levinson<MAXORD>(Ac, rxx, rc, &epsP);
+        if (j == 0) LC3_DBG_MARK(3);
         const i32 sh = l_norm(epsP);
         i32 gain;
         {
@@ -186,6 +201,7 @@ template <int MAXORD, class A> LC3_HD void tns_coder(TnsOut &o, A x, int bw, int
         }
 
         if (gain > (0x30000000 >> sh)) {
+            LC3_DBG_COUNT(7);
             if (lpc_weighting != 0 && gain < (0x40000000 >> sh)) {
                 i32 alpha = l_add(0x6CCCCCCD, mpy32x32(0x13333333, l_shl_p(l_sub(l_shl(gain, sh), 0x30000000), 3)));
                 i32 w = alpha;
@@ -214,23 +230,29 @@ template <int MAXORD, class A> LC3_HD void tns_coder(TnsOut &o, A x, int bw, int
 #pragma unroll
             for (int i = 0; i < MAXORD; i++) k[i] = i < ord ? (i32)rom_tns_quant_pts[ix[i]] : 0;
             const int stop = (o.nfilt == 2 && j == 0) ? startfreq[1] : xLen;
-            // FIR lattice of order ord (fx/tns_coder_fx.c:288-311); stages beyond ord are skipped
-            for (int i = startfreq[j]; i < stop; i++) {
-                i32 v = x[i], save = v;
+            // FIR lattice of order ord (fx/tns_coder_fx.c:288-311).  Stages at and beyond ord have k = 0: they add
+            // nothing to v, and the only thing to keep from them is that their memory is left alone (it runs on into
+            // the second filter, whose order may be higher), so every lane walks the same eight stages without
+            // branching on its own order.  Bins go through four at a time so that the loads are in flight together.
+            auto lattice = [&](i32 v) -> i32 {
+                i32 save = v;
 #pragma unroll
                 for (int s = 0; s < MAXORD; s++) {
-                    if (s < ord - 1) {
-                        i32 t = l_add(state[s], mpy32x16(v, k[s]));
-                        v = l_add(v, mpy32x16(state[s], k[s]));
-                        state[s] = save;
-                        save = t;
-                    } else if (s == ord - 1) {
-                        v = l_add(v, mpy32x16(state[s], k[s]));
-                        state[s] = save;
-                    }
+                    const i32 st = state[s];
+                    const i32 t = l_add(st, mpy32x16(v, k[s]));
+                    v = l_add(v, mpy32x16(st, k[s]));
+                    state[s] = s < ord ? save : st;
+                    save = t; // not used past stage ord - 1
                 }
-                x[i] = v;
+                return v;
+            };
+            int i = startfreq[j];
+            for (; i + 4 <= stop; i += 4) {
+                i32 v0 = x[i], v1 = x[i + 1], v2 = x[i + 2], v3 = x[i + 3];
+                v0 = lattice(v0); v1 = lattice(v1); v2 = lattice(v2); v3 = lattice(v3);
+                x[i] = v0; x[i + 1] = v1; x[i + 2] = v2; x[i + 3] = v3;
             }
+            for (; i < stop; i++) x[i] = lattice(x[i]);
         } else {
             o.bits = s_add(o.bits, 1);
             o.order[j] = 0;
