@@ -24,7 +24,8 @@ class LC3Error(RuntimeError):
 
 
 def library_path():
-    return os.path.join(_HERE, "liblc3plus_b200.so")
+    """The in-tree library; LC3PLUS_B200_LIB selects another build of it (the profiling build, csrc/Makefile TIMING=1)."""
+    return os.environ.get("LC3PLUS_B200_LIB") or os.path.join(_HERE, "liblc3plus_b200.so")
 
 
 def load_library():

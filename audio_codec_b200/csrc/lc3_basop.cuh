@@ -12,6 +12,8 @@
 // library contains the CUDA build only.
 #pragma once
 #include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
 
 #if defined(__CUDACC__)
 #define LC3_HD __device__ __forceinline__
@@ -81,6 +83,15 @@ LC3_HD i32 s_lshr(i32 a, i32 n) { return (i32)(i16)((a & 0xffff) >> n); }
 LC3_HD i32 sx16(i32 a) { return (i32)(i16)a; }   // extract_l: keep the low 16 bits, sign-extended
 
 // ---- 32-bit operators
+// a + b where the caller has shown that the sum fits 32 bits.  The host build (tests/hostsim) checks the claim on
+// every call and stops at the first sum that would have wrapped.
+LC3_HD i32 add_proved(i32 a, i32 b)
+{
+#if !defined(__CUDA_ARCH__)
+    if ((i64)a + b != (i64)(i32)((u32)a + (u32)b)) { fprintf(stderr, "add_proved: %d + %d leaves 32 bits\n", a, b); abort(); }
+#endif
+    return (i32)((u32)a + (u32)b);
+}
 LC3_HD i32 l_add(i32 a, i32 b)
 {
 #if defined(__CUDA_ARCH__)

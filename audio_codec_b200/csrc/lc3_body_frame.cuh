@@ -35,7 +35,6 @@ template <int N, int BITS> LC3_HD void front_body(const LC3K_Batch &b, int f, in
     sns_quantize(scf, scf_idx, scf_q);
     sns_interp(scf_q, g, g_exp, b.nbands);
     mdct_shape(d, g, g_exp, bands, b.nbands);
-    LC3_DBG_MARK(1);
 
     const int cut = cfg[CFG_BW_CUTOFF_BIN];
     if (cut) { // lc3_enc_set_bandwidth was used (fx/cutoff_bandwidth.c:14-28, fx/enc_lc3.c:164-168)
@@ -49,7 +48,6 @@ template <int N, int BITS> LC3_HD void front_body(const LC3K_Batch &b, int f, in
     TnsOut tns;
     if (b.dms_idx == 0) tns_coder<8>(tns, d, bw, cfg[CFG_LPC_WEIGHTING], b.nsub, b.dms_idx);
     else tns_coder<4>(tns, d, bw, cfg[CFG_LPC_WEIGHTING], b.nsub, b.dms_idx);
-    LC3_DBG_MARK(4);
 
     SV<i32> en4 = tile_view(b.en4, ft, N / 4, lane);
     const i32 x_max = gain_energies(d, d_exp, b.yLen, en4);
@@ -101,7 +99,6 @@ template <int N> LC3_HD void tns_body(const LC3K_Batch &b, int f, int tile, int 
     i16 g[64], g_exp[64];
     for (int i = 0; i < b.nbands; i++) { const i32 v = eo[i]; g[i] = (i16)(v & 0xffff); g_exp[i] = (i16)(v >> 16); }
     mdct_shape(d, g, g_exp, bands, b.nbands);
-    LC3_DBG_MARK(1);
 
     const int cut = cfg[CFG_BW_CUTOFF_BIN];
     if (cut) { // lc3_enc_set_bandwidth was used (fx/cutoff_bandwidth.c:14-28, fx/enc_lc3.c:164-168)
@@ -115,7 +112,6 @@ template <int N> LC3_HD void tns_body(const LC3K_Batch &b, int f, int tile, int 
     TnsOut tns;
     if (b.dms_idx == 0) tns_coder<8>(tns, d, bw, cfg[CFG_LPC_WEIGHTING], b.nsub, b.dms_idx);
     else tns_coder<4>(tns, d, bw, cfg[CFG_LPC_WEIGHTING], b.nsub, b.dms_idx);
-    LC3_DBG_MARK(4);
 
     SV<i32> en4 = tile_view(b.en4, ft, N / 4, lane);
     const i32 x_max = gain_energies(d, d_exp, b.yLen, en4);

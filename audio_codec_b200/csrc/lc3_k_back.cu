@@ -23,6 +23,7 @@ __global__ void __launch_bounds__(QT_THREADS) k_quant(LC3K_Batch b)
     for (int i = t; i < 4096; i += QT_THREADS) m.lut[i] = (u8)rom_ari_lookup[i];
     for (int i = t; i < 1088; i += QT_THREADS) m.bits[i] = rom_ari_bits[i];
     const int f = blockIdx.x / b.n_tiles, tile = blockIdx.x % b.n_tiles;
+    LC3_DBG_ENTER(0, w == 0 ? (int)blockIdx.x : LC3_DBG_ROWS);
     if (t < 32) qt_setup(b, f, tile, t, sh.fr[t]);
     __syncthreads();
     qt_quantise(b, f, tile, t, sh);
@@ -31,6 +32,7 @@ __global__ void __launch_bounds__(QT_THREADS) k_quant(LC3K_Batch b)
     for (int j = 0; j < 4; j++) qt_analyse(sh.fr[w + 8 * j], sh.xq + (w + 8 * j) * QT_ROW, b.yLen, sh.w[w], m.lut, m.bits);
     __syncthreads();
     qt_store(b, f, tile, t, sh);
+    LC3_DBG_LEAVE();
 }
 
 // small blocks here, unlike k_front / k_sns / k_tns: the warps of this kernel run for very different times (the entropy
@@ -47,8 +49,11 @@ __global__ void __launch_bounds__(32 * BACK_WARPS, 12) k_back(LC3K_Batch b)
     const int warp = blockIdx.x * BACK_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (warp >= b.n_frames * b.n_tiles) return;
     AriTabs T = {lut, cum, freq};
+    LC3_DBG_ENTER(1, warp);
     back_body(b, warp / b.n_tiles, warp % b.n_tiles, lane, T);
+    LC3_DBG_LEAVE();
 }
+LC3_DBG_READER(back)
 
 static int done() { return (int)cudaGetLastError(); }
 

@@ -1,7 +1,6 @@
 // spectral front-end kernels, instantiated per frame length in lc3_k_front_*.cu (split for parallel builds)
 #pragma once
 #include <cuda_runtime.h>
-#include <cstdio>
 #include "lc3_body_frame.cuh"
 
 using namespace lc3k;
@@ -22,15 +21,10 @@ template <int N, int BITS> __global__ void __launch_bounds__(32 * FRONT_WARPS, 1
 template <int N> __global__ void __launch_bounds__(32 * TNS_WARPS, 1) k_tns(LC3K_Batch b)
 {
     const int warp = blockIdx.x * TNS_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-#ifdef LC3_DBG_TNS
-    if (lane == 0 && warp < 16384) { lc3k_dbg[8 * warp + 6] = 0; lc3k_dbg[8 * warp + 7] = 0; }
-    LC3_DBG_MARK(0);
-#endif
     if (warp >= b.n_frames * b.n_tiles) return;
+    LC3_DBG_ENTER(0, warp);
     tns_body<N>(b, warp / b.n_tiles, warp % b.n_tiles, lane);
-#ifdef LC3_DBG_TNS
-    LC3_DBG_MARK(5);
-#endif
+    LC3_DBG_LEAVE();
 }
 
 // MDCT of one tile (32 channel-frames) per block, spectrum in shared memory (lc3_mdct_tile.cuh).  In the twiddle,
@@ -51,6 +45,7 @@ template <int N, int BITS> __global__ void __launch_bounds__(256, 2) k_mdct(LC3K
         for (int i = t; i < G::W_LEN; i += G::THREADS) s_W[i] = R.W[i];
     }
     const MtTabs T = {s_tw, s_sn, s_W};
+    LC3_DBG_ENTER(1, w == 0 ? (int)blockIdx.x : LC3_DBG_ROWS); // one row per tile, written by its first warp
     mt_fold<N, BITS>(b, f, tile, t, X, mx, mn);
     __syncthreads();
 #pragma unroll 1
@@ -72,6 +67,7 @@ template <int N, int BITS> __global__ void __launch_bounds__(256, 2) k_mdct(LC3K
     mt_bands<N>(b, t, X, ben, bexp, smx);
     __syncthreads();
     mt_store<N>(b, f, tile, t, X, mx, mn, ben, bexp, smx);
+    LC3_DBG_LEAVE();
 }
 
 template <int N> static int front_launch(const LC3K_Batch *b, cudaStream_t s)

@@ -2,7 +2,5 @@
 #include "lc3_k_front.cuh"
 
 extern "C" int lc3k_front_480(const LC3K_Batch *b, void *stream) { return front_launch_tiled<480>(b, (cudaStream_t)stream); }
+LC3_DBG_READER(front)
 extern "C" int lc3k_tns_480(const LC3K_Batch *b, void *stream) { return tns_launch<480>(b, (cudaStream_t)stream); }
-#ifdef LC3_DBG_TNS
-extern "C" int lc3k_dbg_read(void *dst) { return (int)cudaMemcpyFromSymbol(dst, lc3k_dbg, sizeof(lc3k_dbg)); }
-#endif

@@ -12,8 +12,11 @@ __global__ void __launch_bounds__(32 * SNS_WARPS, 1) k_sns(LC3K_Batch b)
 {
     const int warp = blockIdx.x * SNS_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (warp >= b.n_frames * b.n_tiles) return;
+    LC3_DBG_ENTER(0, warp);
     sns_body(b, warp / b.n_tiles, warp % b.n_tiles, lane);
+    LC3_DBG_LEAVE();
 }
+LC3_DBG_READER(sns)
 
 extern "C" int lc3k_sns_launch(const LC3K_Batch *b, void *stream)
 {

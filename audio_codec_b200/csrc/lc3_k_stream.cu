@@ -59,7 +59,9 @@ template <int BITS, bool PRE> __global__ void __launch_bounds__(32 * PITCH_WARPS
     extern __shared__ __align__(16) unsigned char pitch_smem[];
     PitchShared *sh = reinterpret_cast<PitchShared *>(pitch_smem);
     const int w = threadIdx.x >> 5;
+    LC3_DBG_ENTER(0, (int)blockIdx.x * PITCH_WARPS + w);
     pitch_warp_body<BITS, PRE>(b, blockIdx.x * PITCH_WARPS + w, sh[w]);
+    LC3_DBG_LEAVE();
 }
 
 // resampler FIR, frame-parallel: one warp per (channel-stream, frame)
@@ -87,8 +89,11 @@ __global__ void __launch_bounds__(128, 7) k_rate(LC3K_Batch b)
     for (int i = threadIdx.x; i < 1088; i += 128) bits[i] = rom_ari_bits[i];
     __syncthreads();
     const int w = threadIdx.x >> 5;
+    LC3_DBG_ENTER(1, (int)blockIdx.x * 4 + w);
     rate_warp_body(b, blockIdx.x * 4 + w, sh[w], lut, bits);
+    LC3_DBG_LEAVE();
 }
+LC3_DBG_READER(stream)
 
 __global__ void k_reset(i32 *st32, i16 *st16, i16 *hist16, i32 *hist32, const i32 *slots, int n)
 {

@@ -3,17 +3,7 @@
 #pragma once
 #include "lc3_math.cuh"
 
-#if defined(LC3_DBG_TNS) && defined(__CUDACC__)
-static __device__ unsigned long long lc3k_dbg[8 * 16384];
-#endif
-#if defined(LC3_DBG_TNS) && defined(__CUDA_ARCH__)
-#define LC3_DBG_MARK(k) do { __syncwarp(); unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); \
-    const int w_ = blockIdx.x * 24 + (threadIdx.x >> 5); if ((threadIdx.x & 31) == 0 && w_ < 16384) lc3k_dbg[8 * w_ + (k)] = t_; } while (0)
-#define LC3_DBG_COUNT(k) do { const int w_ = blockIdx.x * 24 + (threadIdx.x >> 5); if (w_ < 16384) atomicAdd(&lc3k_dbg[8 * w_ + (k)], 1ull); } while (0)
-#else
-#define LC3_DBG_MARK(k) ((void)0)
-#define LC3_DBG_COUNT(k) ((void)0)
-#endif
+#include "lc3_dbg.cuh"
 
 namespace lc3k {
 
@@ -109,14 +99,19 @@ template <int MAXORD, class A> LC3_HD void tns_coder(TnsOut &o, A x, int bw, int
     if (bw >= 3 && dms_idx <= 1) { o.nfilt = 2; startfreq[1] = xLen >> 1; }
 #pragma unroll
     for (int i = 0; i < 8; i++) state[i] = 0; // lattice memory runs on from filter 0 into filter 1
+    i64 state_bound = 0;                      // >= |state[i]| for every i
 
     for (int j = 0; j < o.nfilt; j++) {
 #pragma unroll
         for (int i = 0; i <= MAXORD; i++) rxx[i] = 0;
+        i64 x_bound = 0;   // >= |x[i]| over the bins of this filter, known when every subdivision was scanned
+        bool scanned = true;
         for (int sd = 0; sd < nsub; sd++) {
             const int lo = sub_lo[nsub * j + sd], n = sub_hi[nsub * j + sd] - lo;
             Range rg; range_init(rg);
             for_batched<8>(x, lo, n, [&](i32 v) { range_add(rg, v); });
+            x_bound = x_bound > rg.mx ? x_bound : (i64)rg.mx;
+            x_bound = x_bound > -(i64)rg.mn ? x_bound : -(i64)rg.mn;
             const i32 headroom = range_headroom32(rg, 0);
             // Norm32Norm (fx/basop_util.c:534-569): energy with a sequentially adapted pre-shift
             i32 sh = headroom, nrg = 0;
@@ -138,6 +133,7 @@ template <int MAXORD, class A> LC3_HD void tns_coder(TnsOut &o, A x, int bw, int
                 rxx[0] = LC3_I32_MAX;
 #pragma unroll
                 for (int i = 1; i <= MAXORD; i++) rxx[i] = 0;
+                scanned = sd == nsub - 1;
                 break;
             }
             t = s_sub(shift, l_norm(nrg));
@@ -168,7 +164,6 @@ template <int MAXORD, class A> LC3_HD void tns_coder(TnsOut &o, A x, int bw, int
             if (e0 <= LC3_I32_MAX) {
                 acc[0] = (i32)e0;
             } else {
-                LC3_DBG_COUNT(6);
 #pragma unroll
                 for (int l = 0; l <= MAXORD; l++) { acc[l] = 0; hist[l] = 0; }
                 for (int i = 0; i < n; i++) {
@@ -189,9 +184,7 @@ template <int MAXORD, class A> LC3_HD void tns_coder(TnsOut &o, A x, int bw, int
             }
         }
 
-        if (j == 0) LC3_DBG_MARK(2);
         levinson<MAXORD>(Ac, rxx, rc, &epsP);
-        if (j == 0) LC3_DBG_MARK(3);
         const i32 sh = l_norm(epsP);
         i32 gain;
         {
@@ -201,7 +194,6 @@ template <int MAXORD, class A> LC3_HD void tns_coder(TnsOut &o, A x, int bw, int
         }
 
         if (gain > (0x30000000 >> sh)) {
-            LC3_DBG_COUNT(7);
             if (lpc_weighting != 0 && gain < (0x40000000 >> sh)) {
                 i32 alpha = l_add(0x6CCCCCCD, mpy32x32(0x13333333, l_shl_p(l_sub(l_shl(gain, sh), 0x30000000), 3)));
                 i32 w = alpha;
@@ -234,25 +226,42 @@ template <int MAXORD, class A> LC3_HD void tns_coder(TnsOut &o, A x, int bw, int
             // nothing to v, and the only thing to keep from them is that their memory is left alone (it runs on into
             // the second filter, whose order may be higher), so every lane walks the same eight stages without
             // branching on its own order.  Bins go through four at a time so that the loads are in flight together.
-            auto lattice = [&](i32 v) -> i32 {
-                i32 save = v;
+            //
+            // Saturation: with |input| and |memory| <= M, a stage's two outputs are bounded by M (1 + |k|) + 1 (the
+            // product is rounded down), so M grows stage by stage to a bound on every value the filter can form.
+            // The subdivisions scanned above tile the filter's bins (tests/test_rom_bounds.py) and give M's start.
+            // The shaped spectrum has about nine bits of headroom, so the bound stays below 2^31 in practice and the
+            // L_add of the reference is a plain addition; otherwise the saturating form runs.  k is never -32768
+            // (tests/test_rom_bounds.py), so Mpy_32_16's one saturating case cannot occur either.
+            i64 M = x_bound > state_bound ? x_bound : state_bound;
 #pragma unroll
-                for (int s = 0; s < MAXORD; s++) {
-                    const i32 st = state[s];
-                    const i32 t = l_add(st, mpy32x16(v, k[s]));
-                    v = l_add(v, mpy32x16(st, k[s]));
-                    state[s] = s < ord ? save : st;
-                    save = t; // not used past stage ord - 1
+            for (int i = 0; i < MAXORD; i++) M += ((M * (k[i] < 0 ? -k[i] : k[i])) >> 15) + 2;
+            const bool plain = scanned && M <= LC3_I32_MAX;
+            state_bound = plain ? M : (i64)LC3_I32_MAX + 1;
+            auto run = [&](auto sat) {
+                constexpr bool SAT = decltype(sat)::value;
+                auto lattice = [&](i32 v) -> i32 {
+                    i32 save = v;
+#pragma unroll
+                    for (int s = 0; s < MAXORD; s++) {
+                        const i32 st = state[s];
+                        const i32 p = mpy32x16k(v, k[s]), q = mpy32x16k(st, k[s]);
+                        const i32 t = SAT ? l_add(st, p) : add_proved(st, p);
+                        v = SAT ? l_add(v, q) : add_proved(v, q);
+                        state[s] = s < ord ? save : st;
+                        save = t; // not used past stage ord - 1
+                    }
+                    return v;
+                };
+                int i = startfreq[j];
+                for (; i + 4 <= stop; i += 4) {
+                    i32 v0 = x[i], v1 = x[i + 1], v2 = x[i + 2], v3 = x[i + 3];
+                    v0 = lattice(v0); v1 = lattice(v1); v2 = lattice(v2); v3 = lattice(v3);
+                    x[i] = v0; x[i + 1] = v1; x[i + 2] = v2; x[i + 3] = v3;
                 }
-                return v;
+                for (; i < stop; i++) x[i] = lattice(x[i]);
             };
-            int i = startfreq[j];
-            for (; i + 4 <= stop; i += 4) {
-                i32 v0 = x[i], v1 = x[i + 1], v2 = x[i + 2], v3 = x[i + 3];
-                v0 = lattice(v0); v1 = lattice(v1); v2 = lattice(v2); v3 = lattice(v3);
-                x[i] = v0; x[i + 1] = v1; x[i + 2] = v2; x[i + 3] = v3;
-            }
-            for (; i < stop; i++) x[i] = lattice(x[i]);
+            if (plain) run(std::false_type()); else run(std::true_type());
         } else {
             o.bits = s_add(o.bits, 1);
             o.order[j] = 0;

@@ -44,6 +44,38 @@ def make_streams_fast(n_streams, n_samples, fs, frame_len, bits=16, n_unique=64)
     return out
 
 
+def make_bursts(n_streams, n_samples, fs, bits=16, seed=99, n_unique=64):
+    """Transient-rich streams (timing robustness, not in the reference's stimulus set): a harmonic tone gated by a
+    random on/off envelope with abrupt onsets every 20-120 ms plus band-limited noise bursts and clicks, so that
+    the temporal-noise-shaping, attack and pitch-change paths run in most frames instead of a few."""
+    full = 32767.0 if bits == 16 else 8388607.0
+    t = np.arange(n_samples, dtype=np.float64) / fs
+    base = np.empty((min(n_unique, n_streams), n_samples), dtype=np.int16 if bits == 16 else np.int32)
+    for i in range(base.shape[0]):
+        rng = np.random.RandomState(seed + i)
+        env = np.zeros(n_samples)
+        pos, on = 0, False
+        while pos < n_samples:
+            seg = int(fs * rng.uniform(0.02, 0.12))
+            if on:
+                env[pos:pos + seg] = rng.uniform(0.2, 1.0) * np.exp(-np.arange(min(seg, n_samples - pos)) / (fs * rng.uniform(0.01, 0.08)))
+            on = not on
+            pos += seg
+        f0 = rng.uniform(80, 400) * (1 + 0.2 * np.sin(2 * np.pi * rng.uniform(0.5, 3) * t))
+        ph = 2 * np.pi * np.cumsum(f0) / fs
+        x = sum(np.sin(k * ph) / k for k in range(1, 8)) * 0.3 + rng.normal(0, 0.25, n_samples)
+        x = x * env
+        clicks = rng.randint(0, n_samples, max(1, n_samples // (fs // 5)))
+        x[clicks] += rng.uniform(-1, 1, len(clicks))
+        base[i] = np.clip(x * full * 0.7, -full - 1, full).astype(base.dtype)
+    if n_streams <= base.shape[0]:
+        return base
+    out = np.empty((n_streams, n_samples), dtype=base.dtype)
+    for i in range(n_streams):
+        out[i] = np.roll(base[i % base.shape[0]], (i // base.shape[0]) * 97)
+    return out
+
+
 def make_torture(n_samples, fs, bits=16, seed=7):
     """Adversarial streams for the saturation / headroom paths: [10, n_samples].
     full-scale noise, full-scale square, Nyquist alternation, negative-rail DC, sparse impulses, silence then

@@ -188,3 +188,17 @@ def test_adversarial_signals(fs, dms, br, bits):
     for s in range(pcm.shape[0]):
         want = _oracle(fs, 1, dms, br, bits, pcm[s])
         assert np.array_equal(out[s, :, :want.shape[1]], want), f"stream {s}"
+
+
+@pytest.mark.parametrize("fs,dms,br,bits", [(48000, 100, 128000, 16), (32000, 100, 32000, 16), (48000, 50, 96000, 24), (16000, 25, 64000, 16)])
+def test_transient_rich_signals(fs, dms, br, bits):
+    """Gated tones, noise bursts and clicks (synth.make_bursts): TNS, attack handling and pitch changes in most frames."""
+    import audio_codec_b200 as ac
+    from audio_codec_b200.synth import make_bursts
+    N, nf = _frame_len(fs, dms), 40
+    pcm = make_bursts(40, nf * N, fs, bits)[:, None, :]
+    encs = [ac.Encoder(fs, 1, dms, br) for _ in range(pcm.shape[0])]
+    out = _batch(ac, encs, nf, pcm, bits)
+    for s in range(pcm.shape[0]):
+        want = _oracle(fs, 1, dms, br, bits, pcm[s])
+        assert np.array_equal(out[s, :, :want.shape[1]], want), f"stream {s}"

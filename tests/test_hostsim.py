@@ -85,3 +85,17 @@ def test_bodies_equal_oracle_on_adversarial_signals(L, fs, dms, br, bits):
     b = hs.oracle_encode(fs, dms, [(br, nf)], pcm, bits)[0]
     bad = np.argwhere((a != b).any(2))
     assert len(bad) == 0, f"first mismatch (stream, frame) = {bad[0]}"
+
+
+@pytest.mark.parametrize("fs,dms,br,bits", [(48000, 100, 128000, 16), (32000, 100, 32000, 16), (48000, 50, 96000, 24), (16000, 25, 64000, 16)])
+def test_bodies_equal_oracle_on_transient_rich_signals(L, fs, dms, br, bits):
+    """Gated tones, noise bursts and clicks: temporal noise shaping, the attack detector (low rates) and pitch
+    changes are active in most frames, unlike in the reference's stationary stimulus."""
+    from audio_codec_b200.synth import make_bursts
+    N = fs // 100 * dms // 100
+    nf = 30
+    pcm = make_bursts(12, nf * N, fs, bits)
+    a = hs.sim_encode(L, fs, dms, [(br, nf)], pcm, bits)[0]
+    b = hs.oracle_encode(fs, dms, [(br, nf)], pcm, bits)[0]
+    bad = np.argwhere((a != b).any(2))
+    assert len(bad) == 0, f"first mismatch (stream, frame) = {bad[0]}"

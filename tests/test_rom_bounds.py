@@ -33,3 +33,22 @@ def test_constants_used_with_unchecked_multiply_are_not_minus_one():
     """mpy32x16k / mpy32x32k skip the (-1 x -1) saturation test: their constant operands must differ from the minimum."""
     for name in ("rom_hp50_num", "rom_hp50_den", "rom_ltpf_inter_filt", "rom_tns_quant_pts"):
         assert -32768 not in _tab(name), name
+
+
+def test_tns_subdivisions_tile_the_filter_bins():
+    """lc3_tns.cuh takes max |x| over a TNS filter's bins from the range scans of its subdivisions: for every frame
+    duration and bandwidth they must cover [start frequency, stop) without gaps (fx/tns_coder_fx.c:66-75, :288)."""
+    lo_t, hi_t, cut = _tab("rom_tns_sub_start"), _tab("rom_tns_sub_stop"), _tab("rom_bw_cutoff_bin")
+    for dms_idx in range(3):
+        nsub = 3 if dms_idx == 0 else 2
+        for bw in range(5):
+            xlen = cut[bw] >> dms_idx
+            nfilt = 2 if (bw >= 3 and dms_idx <= 1) else 1
+            start = [12 >> dms_idx, xlen >> 1]
+            base = (dms_idx * 5 + bw) * 6
+            for j in range(nfilt):
+                stop = start[1] if (nfilt == 2 and j == 0) else xlen
+                lo = [lo_t[base + nsub * j + sd] for sd in range(nsub)]
+                hi = [hi_t[base + nsub * j + sd] for sd in range(nsub)]
+                assert lo[0] <= start[j] and hi[-1] >= stop, (dms_idx, bw, j, lo, hi, start[j], stop)
+                assert all(hi[sd] >= lo[sd + 1] for sd in range(nsub - 1)), (dms_idx, bw, j, lo, hi)
