@@ -53,6 +53,14 @@ def load_library():
         L.lc3plus_last_error.restype = C.c_char_p
         L.lc3plus_set_chunk_frames.argtypes = [C.c_int]
         L.lc3plus_enc_release.restype = None
+        L.lc3plus_container_header.restype = C.c_size_t
+        L.lc3plus_container_header.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint32]
+        L.lc3plus_container_frames.restype = C.c_size_t
+        L.lc3plus_container_frames.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_size_t, C.c_int, C.c_void_p, C.c_int]
+        L.lc3plus_write_bitstream_file.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                                   C.c_int, C.c_uint32, C.c_void_p, C.c_int, C.c_size_t, C.c_int,
+                                                   C.c_void_p]
+        L.lc3plus_read_switching_file.argtypes = [C.c_char_p, C.c_void_p, C.c_int]
         _LIB = L
     return _LIB
 
@@ -169,3 +177,51 @@ def enc_batch(encoders, n_frames, pcm, stream_stride_bytes, bits, out, out_strea
                             out_stream_stride_bytes, nb)
     if r:
         raise LC3Error(r, "lc3plus_enc_batch")
+
+
+# ---- bitstream containers of the reference tool (include/lc3plus_b200.h); host only
+
+def container_header(samplerate, bitrate, channels, frame_dms, epmode=0, signal_len=0):
+    """The 18-byte .lc3plus header (fx/codec_exe.c:742-746)."""
+    buf = np.zeros(18, dtype=np.uint8)
+    n = load_library().lc3plus_container_header(buf.ctypes.data, samplerate, bitrate, channels, frame_dms, epmode, signal_len)
+    return buf[:n].tobytes()
+
+
+def container_frames(frames, num_bytes=None, g192=False):
+    """frames: uint8 [n_frames, stride]; num_bytes: optional per-frame sizes (default: the row length)."""
+    L = load_library()
+    frames = np.ascontiguousarray(frames, dtype=np.uint8)
+    nb = np.ascontiguousarray(num_bytes, dtype=np.int32) if num_bytes is not None else None
+    args = (frames.ctypes.data, frames.shape[0], frames.shape[1], frames.shape[1], nb.ctypes.data if nb is not None else None,
+            1 if g192 else 0)
+    need = L.lc3plus_container_frames(None, *args)
+    buf = np.zeros(max(need, 1), dtype=np.uint8)
+    got = L.lc3plus_container_frames(buf.ctypes.data, *args)
+    if got != need or (need == 0 and frames.shape[0] > 0):
+        raise LC3Error(7, "lc3plus_container_frames")
+    return buf[:need].tobytes()
+
+
+def write_bitstream_file(path, samplerate, bitrate, channels, frame_dms, signal_len, frames, num_bytes=None, epmode=0,
+                         g192=False, cfg_path=None):
+    """lc3plus_write_bitstream_file: the file the reference tool writes for these frames (fx/codec_exe.c:255-260, :490)."""
+    frames = np.ascontiguousarray(frames, dtype=np.uint8)
+    nb = np.ascontiguousarray(num_bytes, dtype=np.int32) if num_bytes is not None else None
+    r = load_library().lc3plus_write_bitstream_file(os.fsencode(path), os.fsencode(cfg_path) if cfg_path else None,
+                                                    1 if g192 else 0, samplerate, bitrate, channels, frame_dms, epmode,
+                                                    signal_len, frames.ctypes.data, frames.shape[0], frames.shape[1],
+                                                    frames.shape[1], nb.ctypes.data if nb is not None else None)
+    if r:
+        raise LC3Error(r, "lc3plus_write_bitstream_file")
+
+
+def read_switching_file(path):
+    """int64 values of a switching file (fx/codec_exe.c:968-977); frame f uses values[f % len(values)]."""
+    L = load_library()
+    n = L.lc3plus_read_switching_file(os.fsencode(path), None, 0)
+    if n < 0:
+        raise OSError(f"cannot open {path}")
+    v = np.zeros(max(n, 1), dtype=np.int64)
+    L.lc3plus_read_switching_file(os.fsencode(path), v.ctypes.data, n)
+    return v[:n]

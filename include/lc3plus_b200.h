@@ -115,6 +115,35 @@ const char *lc3plus_last_error(void);
  * flight at once, each on its own CUDA stream with its own work buffers. */
 void lc3plus_set_chunk_frames(int channel_frames);
 
+/* ---- Bitstream containers of the reference command-line tool.  Host-only helpers: they
+ * never touch the device.  Little endian on every host. */
+#define LC3PLUS_CONTAINER_HEADER_BYTES 18
+/* NEW (replaces open_bitstream_writer's header, fx/codec_exe.c:726-751; layout ETSI/Readme.txt:308-325): writes
+ * the 18-byte configuration header {0xcc1c, 18, samplerate/100, bitrate/100, channels, frame_ms*100, epmode,
+ * signal_len lo, signal_len hi} to dst and returns 18; dst == NULL only returns the size.  frame_dms is the
+ * frame duration in 0.1 ms units (25, 50, 100) as in lc3_enc_set_frame_dms. */
+size_t lc3plus_container_header(void *dst, int samplerate, int bitrate, int channels, int frame_dms, int epmode,
+                                uint32_t signal_len);
+/* NEW (replaces write_bitstream_frame / write_bitstream_frame_G192, fx/codec_exe.c:799-843): packs n_frames coded
+ * frames (frame f at (uint8_t*)frames + f*frame_stride_bytes, num_bytes[f] bytes, or bytes_per_frame when
+ * num_bytes is NULL) into dst, each preceded by its uint16 byte count, or, with g192 != 0, as G.192 words (sync
+ * 0x6B21, bit count, one 16-bit word per bit, LSB of each byte first).  Returns the bytes written; dst == NULL
+ * only returns the size; 0 on a bad size. */
+size_t lc3plus_container_frames(void *dst, const void *frames, int n_frames, size_t frame_stride_bytes,
+                                int bytes_per_frame, const int *num_bytes, int g192);
+/* NEW: header + frames into the file `path` exactly as the reference tool writes it (fx/codec_exe.c:255-260,
+ * :418-437).  With g192 != 0 the header goes to cfg_path (NULL: path with ".cfg" appended,
+ * fx/codec_exe.c:720-723) and `path` holds only the G.192 frames. */
+LC3_Error lc3plus_write_bitstream_file(const char *path, const char *cfg_path, int g192, int samplerate, int bitrate,
+                                       int channels, int frame_dms, int epmode, uint32_t signal_len,
+                                       const void *frames, int n_frames, size_t frame_stride_bytes,
+                                       int bytes_per_frame, const int *num_bytes);
+/* NEW (replaces loopy_read64's file, fx/codec_exe.c:968-977): reads the int64 values of a bitrate / bandwidth /
+ * epmode switching file.  Returns how many values the file holds (the first max_values are stored in values; values
+ * may be NULL to count), -1 if it cannot be opened.  The reference takes one value per frame and wraps around:
+ * frame f uses values[f % count] (per channel for bitrates, fx/codec_exe.c:342-347). */
+int lc3plus_read_switching_file(const char *path, int64_t *values, int max_values);
+
 #ifdef __cplusplus
 }
 #endif
