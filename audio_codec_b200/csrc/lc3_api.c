@@ -227,12 +227,13 @@ static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_
     size_t n_lanes = 0;
     for (int i = 0; i < n; i++) n_lanes += encs[idx[i]]->cfg.channels;
     if (lanes_reserve(n_lanes)) return 1;
-    int any_bfi = 0;
+    int any_bfi = 0, max_bytes = 0;
     size_t l = 0;
     for (int i = 0; i < n; i++) {
         const struct LC3_Enc *e = encs[idx[i]];
         int nb = lc3cfg_num_bytes(&e->cfg), boff = 0;
         for (int ch = 0; ch < e->cfg.channels; ch++, l++) {
+            if (e->cfg.ch[ch][CFG_TARGET_BYTES] > max_bytes) max_bytes = e->cfg.ch[ch][CFG_TARGET_BYTES];
             g.h_slot[l] = e->slot[ch];
             g.h_poff[l] = (int64_t)((size_t)idx[i] * stride / sb) + (int64_t)ch * n_frames * N;
             g.h_ooff[l] = (int64_t)((size_t)idx[i] * ostride) + boff;
@@ -253,6 +254,7 @@ static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_
     b.bits = bits;
     b.n_lanes = (int)n_lanes;
     b.n_tiles = (int)((n_lanes + 31) / 32);
+    b.max_bytes = max_bytes;
     b.slot = g.d_slot; b.cfg = g.cfg; b.st32 = g.st32; b.st16 = g.st16; b.hist16 = g.hist16; b.hist32 = g.hist32;
     b.pcm = d_pcm; b.pcm_off = g.d_poff; b.out = d_out; b.out_off = g.d_ooff; b.out_stride = g.d_ostride;
 

@@ -7,17 +7,33 @@
 
 namespace lc3k {
 
-struct BackWriter { u8 *p; i32 bp, mask; }; // backward bit writer: LSB first, byte pointer descending
-LC3_HD void put_bit(BackWriter &w, i32 bit)
+// Frame bytes of one lane.  LocalBytes: a plain per-lane array (host build, fallback).  The kernel uses a shared-memory
+// view (lc3_k_back.cu) in which every lane owns one bank, so the lane-varying byte positions of the two writers never
+// conflict and the finished frames can be copied out by the whole warp.
+struct LocalBytes {
+    u8 *p;
+    LC3_HDM i32 get(int i) const { return p[i]; }
+    LC3_HDM void set(int i, i32 v) const { p[i] = (u8)v; }
+    LC3_HDM void zero(int n) const { for (int i = 0; i < n; i++) p[i] = 0; }
+};
+
+// backward bit writer: LSB first, byte pointer descending (fx/ari_codec.c:1311-1345).  Bits collect in `acc` (n of them,
+// starting at the current byte's bit 0) and leave as whole bytes; bw_close ORs the last partial byte into place.
+template <class B> struct BackWriter { B buf; i32 bp; u32 acc; i32 n; };
+template <class B> LC3_HD void bw_flush(BackWriter<B> &w)
 {
-    if (bit > 0) w.p[w.bp] |= (u8)w.mask;
-    w.mask <<= 1;
-    if (w.mask == 0x100) { w.mask = 1; w.bp--; }
+    while (w.n >= 8) { w.buf.set(w.bp, (i32)(w.acc & 0xffu)); w.bp--; w.acc >>= 8; w.n -= 8; }
 }
-LC3_HD void put_bits(BackWriter &w, i32 v, int n)
+template <class B> LC3_HD void put_bits(BackWriter<B> &w, i32 v, int n)
+{ // n <= 16
+    w.acc |= ((u32)v & ((1u << n) - 1u)) << w.n;
+    w.n += n;
+    bw_flush(w);
+}
+template <class B> LC3_HD void put_bit(BackWriter<B> &w, i32 bit) { put_bits(w, bit > 0 ? 1 : 0, 1); }
+template <class B> LC3_HD void bw_close(BackWriter<B> &w)
 {
-    v &= 0xffff;
-    for (int k = 0; k < n; k++) { put_bit(w, v & 1); v >>= 1; }
+    if (w.n > 0) w.buf.set(w.bp, w.buf.get(w.bp) | (i32)(w.acc & 0xffu));
 }
 
 struct SideInfo {
@@ -25,12 +41,14 @@ struct SideInfo {
     i32 scf[7];
 };
 
-// fx/enc_entropy.c:19-152.  bytes[] must be zeroed over targetBytes by the caller.
-LC3_HD void side_info(BackWriter &w, u8 *bytes, i32 nbbits, int L, const SideInfo &si, int fs_idx)
+// fx/enc_entropy.c:19-152.  The frame's bytes must be zeroed over targetBytes by the caller.
+template <class B>
+LC3_HD void side_info(BackWriter<B> &w, B bytes, i32 nbbits, int L, const SideInfo &si, int fs_idx)
 {
-    w.p = bytes;
+    w.buf = bytes;
     w.bp = s_sub(nbbits, 1) >> 3;
-    w.mask = s_shl(1, s_sub(8, s_sub(nbbits, w.bp << 3)));
+    w.acc = 0;
+    w.n = s_sub(8, s_sub(nbbits, w.bp << 3)); // first bit position inside the last byte (mask = 1 << n in the reference)
 
     if (si.bw_bits > 0) put_bits(w, si.bw, si.bw_bits);
     const int nb_lastnz = s_sub(14, s_norm(s_neg(L)));
@@ -69,14 +87,14 @@ LC3_HD void side_info(BackWriter &w, u8 *bytes, i32 nbbits, int L, const SideInf
 }
 
 // ---- range coder (fx/ari_codec.c:1374-1527)
-struct RangeCoder { u32 low, range; i32 cache, carry, carry_count; u8 *p; i32 bp; };
+template <class B> struct RangeCoder { u32 low, range; i32 cache, carry, carry_count; B p; i32 bp; };
 
-LC3_HD void rc_shift(RangeCoder &s)
+template <class B> LC3_HD void rc_shift(RangeCoder<B> &s)
 { // emit one byte with deferred carry resolution (fx/ari_codec.c:1374-1406)
     if (s.low < 0x00ff0000u || s.carry == 1) {
-        if (s.cache >= 0) s.p[s.bp++] = (u8)(s.cache + s.carry);
+        if (s.cache >= 0) s.p.set(s.bp++, s.cache + s.carry);
         while (s.carry_count > 0) {
-            s.p[s.bp++] = (u8)((s.carry + 0xff) & 255);
+            s.p.set(s.bp++, (s.carry + 0xff) & 255);
             s.carry_count--;
         }
         s.cache = (i32)(s.low >> 16);
@@ -92,7 +110,7 @@ LC3_HD u32 add24(u32 a, u32 b, int &wrap)
     wrap = r < x;
     return r >> 8;
 }
-LC3_HD void rc_encode(RangeCoder &s, u32 cum, u32 freq)
+template <class B> LC3_HD void rc_encode(RangeCoder<B> &s, u32 cum, u32 freq)
 { // fx/ari_codec.c:1408-1446
     u32 r = s.range >> 10;
     int carry;
@@ -104,17 +122,17 @@ LC3_HD void rc_encode(RangeCoder &s, u32 cum, u32 freq)
         rc_shift(s);
     }
 }
-LC3_HD void put_fwd(u8 *p, i32 bp, i32 v, int n)
+template <class B> LC3_HD void put_fwd(B p, i32 bp, i32 v, int n)
 { // overwrite the top n bits of p[bp] with the top n bits of v's low byte (fx/ari_codec.c:1348-1368)
-    i32 t = p[bp], mask = 0x80;
+    i32 t = p.get(bp), mask = 0x80;
     for (int k = 0; k < n; k++) {
         t |= mask;
         if ((v & mask) == 0) t -= mask;
         mask >>= 1;
     }
-    p[bp] = (u8)t;
+    p.set(bp, t);
 }
-LC3_HD void rc_finish(RangeCoder &s)
+template <class B> LC3_HD void rc_finish(RangeCoder<B> &s)
 { // fx/ari_codec.c:1448-1527
     i32 bits = s_sub(ul_norm(s.range), 7);
     u32 mask = 0x00ffffffu >> bits;
@@ -134,27 +152,30 @@ LC3_HD void rc_finish(RangeCoder &s)
     for (; bits > 0; bits -= 8) rc_shift(s);
     bits = s_add(bits, 8);
     if (s.carry_count > 0) {
-        s.p[s.bp++] = (u8)s.cache;
-        for (; s.carry_count > 1; s.carry_count--) s.p[s.bp++] = 0xff;
+        s.p.set(s.bp++, s.cache);
+        for (; s.carry_count > 1; s.carry_count--) s.p.set(s.bp++, 0xff);
         put_fwd(s.p, s.bp, s_lshr(0xff, s_sub(8, bits)), bits);
     } else {
         put_fwd(s.p, s.bp, s.cache, bits);
     }
 }
 
-struct AriTabs { const u8 *lut; const uint16_t *cum, *freq; };
-LC3_HD void enc_sym(RangeCoder &s, const AriTabs &T, int ctx, int sym)
-{
-    const int row = T.lut[ctx] * 17 + sym;
-    rc_encode(s, T.cum[row], T.freq[row]);
-}
+// lut: context -> probability model (fx ari_spec_lookup); cf[model*17 + symbol] = freq << 16 | cumfreq (ari_spec_freq / _cumfreq)
+struct AriTabs { const u8 *lut; const u32 *cf; };
 LC3_HD i32 res_bit(const u32 *res, int i) { return (i32)((res[i >> 5] >> (i & 31)) & 1u); }
 
 // fx/ari_codec.c:94-406.  lsbs: scratch for the diverted LSB plane (2*L bits, packed).
 // The context / escape level / MSB symbol of each tuple (the reference's codingdata[], written by its quantiser,
 // fx/quantize_spec_fx.c:100-190) are recomputed here from the quantised bins as the loop goes.
-template <class XQ>
-LC3_HD void ari_encode(u8 *bytes, BackWriter &w, i32 nbbits, XQ xq, int nt, i32 rateFlag, const TnsOut &tns, i32 lastnz,
+//
+// The reference walks the tuples and, per tuple, codes `lev` escape symbols and one MSB symbol, with sign / bit-plane
+// bits going to the backward writer in between.  Here ONE loop iteration codes ONE range-coder symbol (a single call
+// site of the coder), so the 32 lanes of a warp -- 32 different frames -- stay converged through the coder whatever
+// their tuples look like; only the short "fetch the next tuple" block is predicated.  The forward (range coder) and
+// backward (bits) streams are independent, so only the order inside each stream has to match the reference, and it does:
+// per tuple, bit planes in rising level, then the signs.
+template <class B, class XQ>
+LC3_HD void ari_encode(B bytes, BackWriter<B> &w, i32 nbbits, XQ xq, int nt, i32 rateFlag, const TnsOut &tns, i32 lastnz,
                        const u32 *res, i32 nres, i32 lsbMode, int lpc_weighting, const AriTabs &T, u32 *lsbs)
 {
     int nlsbs = 0;
@@ -164,7 +185,7 @@ LC3_HD void ari_encode(u8 *bytes, BackWriter &w, i32 nbbits, XQ xq, int nt, i32 
         nlsbs++;
         if ((nlsbs & 31) == 0) { lsbs[(nlsbs >> 5) - 1] = lword; lword = 0; }
     };
-    RangeCoder s = {0, 0x00ffffffu, -1, 0, 0, bytes, 0};
+    RangeCoder<B> s = {0, 0x00ffffffu, -1, 0, 0, bytes, 0};
 
     for (int n = 0; n < tns.nfilt; n++) {
         if (tns.order[n] <= 0) continue;
@@ -178,71 +199,59 @@ LC3_HD void ari_encode(u8 *bytes, BackWriter &w, i32 nbbits, XQ xq, int nt, i32 
 
     const int nt_half = nt >> 1;
     i32 c = 0;
-    for (int k = 0; k < lastnz; k += 2) {
-        const i32 a = xq[k], b = xq[k + 1];
-        const i32 a1 = s_abs(a), b1 = s_abs(b), mx = imax(a1, b1);
-        int ctx = c + rateFlag;
-        if (k > nt_half) ctx += 1 << 8;
-        if (mx == 0) { enc_sym(s, T, ctx, 0); c = ((c & 0xf) << 4) + 1; continue; }
-        i32 lev, msb;
-        if (mx < 4) {
-            lev = 0; msb = a1 + (b1 << 2);
-            c = ((c & 0xf) << 4) + a1 + b1 + 1;
-        } else if (mx < 8) {
-            lev = 1; msb = (a1 >> 1) + ((b1 >> 1) << 2);
-            c = ((c & 0xf) << 4) + 2 * ((a1 >> 1) + (b1 >> 1)) + 1;
-        } else {
-            lev = 13 - s_norm(mx); msb = (a1 >> lev) + ((b1 >> lev) << 2);
-            c = ((c & 0xf) << 4) + 12 + imin(lev, 3);
+    int k = 0, l = 0, lev = 0, ctx = 0;
+    i32 a = 0, b = 0, a1 = 0, b1 = 0, msb = 0;
+    i32 na = 0, nb = 0, nna = 0, nnb = 0; // the next two tuples, fetched two tuples ahead of their use
+    if (lastnz > 0) {
+        na = xq[0]; nb = xq[1];
+        const int k2 = 2 < lastnz ? 2 : 0;
+        nna = xq[k2]; nnb = xq[k2 + 1];
+    }
+    while (k < lastnz) {
+        if (l == 0) { // next tuple: level, MSB symbol, context (fx/quantize_spec_fx.c:100-190)
+            a = na; b = nb; na = nna; nb = nnb;
+            const int kn = k + 4 < lastnz ? k + 4 : k;
+            nna = xq[kn]; nnb = xq[kn + 1];
+            a1 = s_abs(a); b1 = s_abs(b);
+            const i32 mx = imax(a1, b1);
+            ctx = c + rateFlag;
+            if (k > nt_half) ctx += 1 << 8;
+            lev = mx < 4 ? 0 : (mx < 8 ? 1 : 13 - s_norm(mx));
+            msb = (a1 >> lev) + ((b1 >> lev) << 2);
+            const i32 t = mx == 0 ? 1 : (lev == 0 ? a1 + b1 + 1 : (lev == 1 ? 2 * ((a1 >> 1) + (b1 >> 1)) + 1 : 12 + imin(lev, 3)));
+            c = ((c & 0xf) << 4) + t;
         }
-        if (lev == 0) {
-            enc_sym(s, T, ctx, msb);
-            if (a != 0) put_bit(w, (a >> 15) & 1);
-            if (b != 0) put_bit(w, (b >> 15) & 1);
-            continue;
+        const bool last = l == lev; // this iteration codes the MSB symbol, the earlier ones an escape each
+        {
+            const int row = T.lut[ctx + rom_ari_esc_nb[l < 3 ? l : 3]] * 17 + (last ? msb : 16);
+            const u32 cf = T.cf[row];
+            rc_encode(s, cf & 0xffffu, cf >> 16);
         }
-        if (lsbMode == 0) {
-            for (int l = 0; l < lev; l++) { // escape symbol + one LSB plane per level
-                enc_sym(s, T, ctx + rom_ari_esc_nb[l < 3 ? l : 3], 16);
-                if (lev == 1) { put_bit(w, a & 1); put_bit(w, b & 1); }
-                else { put_bit(w, (a1 >> l) & 1); put_bit(w, (b1 >> l) & 1); }
-            }
-            enc_sym(s, T, ctx + rom_ari_esc_nb[lev < 3 ? lev : 3], msb);
-            if (a != 0) put_bit(w, (a >> 15) & 1);
-            if (b != 0) put_bit(w, (b >> 15) & 1);
-        } else { // lowest bit-plane is diverted to the lsbs[] side buffer
-            const i32 am = lev == 1 ? (msb & 3) : (a1 >> 1), bm = lev == 1 ? (msb >> 2) : (b1 >> 1);
-            const i32 ta = lev == 1 ? (a & 1) : (a1 & 1), tb = lev == 1 ? (b & 1) : (b1 & 1);
-            if (lev == 1) {
-                enc_sym(s, T, ctx, 16);
-                enc_sym(s, T, ctx + rom_ari_esc_nb[1], msb);
+        if (!last) { // bit plane l of both magnitudes
+            const i32 ta = (a1 >> l) & 1, tb = (b1 >> l) & 1;
+            if (lsbMode != 0 && l == 0) { // lowest plane diverted to lsbs[]; a value that is +-1 takes its sign along
+                const i32 am = a1 >> 1, bm = b1 >> 1;
                 push_lsb(ta);
-                if (am == 0 && ta > 0) { if (a > 0) push_lsb(0); if (a < 0) push_lsb(1); }
-                if (am != 0) put_bit(w, (a >> 15) & 1);
+                if (am == 0 && ta > 0) push_lsb(a < 0 ? 1 : 0);
                 push_lsb(tb);
-                if (bm == 0 && tb > 0) { if (b > 0) push_lsb(0); if (b < 0) push_lsb(1); }
-                if (bm != 0) put_bit(w, (b >> 15) & 1);
+                if (bm == 0 && tb > 0) push_lsb(b < 0 ? 1 : 0);
             } else {
-                push_lsb(ta);
-                if (am == 0 && ta > 0) { if (a > 0) push_lsb(0); if (a < 0) push_lsb(1); }
-                push_lsb(tb);
-                if (bm == 0 && tb > 0) { if (b > 0) push_lsb(0); if (b < 0) push_lsb(1); }
-                enc_sym(s, T, ctx + rom_ari_esc_nb[0], 16);
-                for (int l = 1; l < lev; l++) {
-                    enc_sym(s, T, ctx + rom_ari_esc_nb[l < 3 ? l : 3], 16);
-                    put_bit(w, (a1 >> l) & 1);
-                    put_bit(w, (b1 >> l) & 1);
-                }
-                enc_sym(s, T, ctx + rom_ari_esc_nb[lev < 3 ? lev : 3], msb);
-                if (am != 0) put_bit(w, (a >> 15) & 1);
-                if (bm != 0) put_bit(w, (b >> 15) & 1);
+                put_bits(w, ta | (tb << 1), 2);
             }
+            l++;
+        } else { // signs of the values whose sign has not gone with a diverted LSB
+            const bool div = lsbMode != 0 && lev > 0;
+            const i32 sa = (div ? (a1 >> 1) : a1) != 0, sb = (div ? (b1 >> 1) : b1) != 0;
+            const i32 na_ = (a >> 15) & 1, nb_ = (b >> 15) & 1;
+            put_bits(w, sa ? (na_ | (nb_ << 1)) : nb_, sa + sb);
+            k += 2;
+            l = 0;
         }
     }
     if (nlsbs & 31) lsbs[nlsbs >> 5] = lword;
 
     // bits still free between the two cursors (in sync with the decoder)
-    const i32 nbits_side = s_sub(nbbits, s_add(w.bp << 3, s_sub(s_norm(w.mask), 6)));
+    const i32 nbits_side = s_sub(nbbits, s_add(w.bp << 3, s_sub(8, w.n)));
     i32 extra = s_sub(ul_norm(s.range), 6);
     if (s.cache >= 0) extra = s_add(extra, 8);
     if (s.carry_count > 0) extra = s_add(extra, s.carry_count << 3);
@@ -250,7 +259,12 @@ LC3_HD void ari_encode(u8 *bytes, BackWriter &w, i32 nbbits, XQ xq, int nt, i32 
 
     const u32 *src = lsbMode == 0 ? res : lsbs;
     const int m = imin(lsbMode == 0 ? nres : nlsbs, n);
-    for (int i = 0; i < m; i++) put_bit(w, res_bit(src, i));
+    for (int i = 0; i < m; i += 8) { // eight at a time
+        const int cnt = imin(8, m - i);
+        const u32 v = src[i >> 5] >> (i & 31); // i is a multiple of 8: the group never straddles two words
+        put_bits(w, (i32)(v & 0xffu), cnt);
+    }
+    bw_close(w);
     rc_finish(s);
 }
 

@@ -122,10 +122,14 @@ template <int N> LC3_HD void tns_body(const LC3K_Batch &b, int f, int tile, int 
 }
 
 // ---- back end: fx/enc_lc3.c:196-242 (adjust gain, final quantisation, residual, noise factor, entropy coding)
-LC3_HD void back_body(const LC3K_Batch &b, int f, int tile, int lane, const AriTabs &T)
+// The finished frame is left in `bytes` (see lc3_bits.cuh); returns its size and, in dst, where the caller must copy it
+// (0: lane not in use).
+template <class B>
+LC3_HD i32 back_body(const LC3K_Batch &b, int f, int tile, int lane, const AriTabs &T, B bytes, u8 *&dst)
 {
     const int li = tile * LC3K_LANES + lane;
-    if (li >= b.n_lanes) return;
+    dst = nullptr;
+    if (li >= b.n_lanes) return 0;
     const int slot = b.slot[li];
     SV<const i32> cfg = slot_view(b.cfg, slot, CFG_N);
     const size_t ft = frame_tile(b, f, tile);
@@ -163,15 +167,14 @@ LC3_HD void back_body(const LC3K_Batch &b, int f, int tile, int lane, const AriT
     si.bfi_ext = b.bfi ? b.bfi[(size_t)(b.frame0 + f) * b.n_lanes + li] : 0;
     for (int i = 0; i < 7; i++) si.scf[i] = fo[FO_SCF + i];
 
-    u8 bytes[440];
-    for (int i = 0; i < target_bytes; i++) bytes[i] = 0;
-    BackWriter w;
+    bytes.zero(target_bytes);
+    BackWriter<B> w;
     side_info(w, bytes, total_bits, b.yLen, si, b.fs_idx);
     const i32 rateFlag = s_sub(total_bits, s_add(160, s_imult(b.fs_idx, 160))) > 0 ? 2 << 8 : 0;
     ari_encode(bytes, w, total_bits, xq, b.yLen, rateFlag, tns, q.lastnz, res, nres, q.lsbMode, lpc_weighting, T, lsbs);
 
-    u8 *dst = b.out + b.out_off[li] + (size_t)(b.frame0 + f) * b.out_stride[li];
-    for (int i = 0; i < target_bytes; i++) dst[i] = bytes[i];
+    dst = b.out + b.out_off[li] + (size_t)(b.frame0 + f) * b.out_stride[li];
+    return target_bytes;
 }
 
 } // namespace lc3k

@@ -35,22 +35,51 @@ __global__ void __launch_bounds__(QT_THREADS) k_quant(LC3K_Batch b)
     LC3_DBG_LEAVE();
 }
 
+// Frame bytes in shared memory: word w of lane L sits at word w*33 + L of the warp's region.  A lane's bytes are always
+// in "its" bank column shifted by w, so accesses with one index for the whole warp never conflict, lane-varying indices
+// (the two writers of different frames sit at different bytes) conflict only by chance, and a whole row can be read by the
+// 32 lanes (w = lane) without conflict for the copy-out.
+struct SmemBytes {
+    u8 *base; // warp region + 4*lane
+    __device__ i32 get(int i) const { return base[(i >> 2) * 132 + (i & 3)]; }
+    __device__ void set(int i, i32 v) const { base[(i >> 2) * 132 + (i & 3)] = (u8)v; }
+    __device__ void zero(int n) const { for (int w = 0; w < (n + 3) >> 2; w++) *reinterpret_cast<u32 *>(base + w * 132) = 0; }
+};
+
 // small blocks here, unlike k_front / k_sns / k_tns: the warps of this kernel run for very different times (the entropy
-// coder loops are data dependent), and a large block holds its SM slot until its slowest warp is done (measured: 2.44 ms
-// at 4 warps per block, 2.76 at 12, 3.52 at 24)
-#define BACK_WARPS 4
-__global__ void __launch_bounds__(32 * BACK_WARPS, 12) k_back(LC3K_Batch b)
+// coder loops are data dependent), and a large block holds its SM slot until its slowest warp is done
+#ifndef BACK_WARPS
+#define BACK_WARPS 8
+#endif
+#define BACK_SMEM_MAX (100 * 1024)
+static int back_smem_bytes(int max_bytes) { return 4096 + 1088 * 4 + BACK_WARPS * ((max_bytes + 3) / 4) * 132; }
+__global__ void __launch_bounds__(32 * BACK_WARPS) k_back(LC3K_Batch b)
 {
-    __shared__ u8 lut[4096];
-    __shared__ uint16_t cum[1088], freq[1088];
+    extern __shared__ __align__(16) unsigned char bk_smem[];
+    u32 *cf = reinterpret_cast<u32 *>(bk_smem);
+    u8 *lut = bk_smem + 1088 * 4, *frames = lut + 4096;
     for (int i = threadIdx.x; i < 4096; i += 32 * BACK_WARPS) lut[i] = (u8)rom_ari_lookup[i];
-    for (int i = threadIdx.x; i < 1088; i += 32 * BACK_WARPS) { cum[i] = rom_ari_cumfreq[i]; freq[i] = rom_ari_freq[i]; }
+    for (int i = threadIdx.x; i < 1088; i += 32 * BACK_WARPS) cf[i] = (u32)rom_ari_freq[i] << 16 | rom_ari_cumfreq[i];
     __syncthreads();
-    const int warp = blockIdx.x * BACK_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    const int wib = threadIdx.x >> 5, warp = blockIdx.x * BACK_WARPS + wib, lane = threadIdx.x & 31;
     if (warp >= b.n_frames * b.n_tiles) return;
-    AriTabs T = {lut, cum, freq};
+    AriTabs T = {lut, cf};
     LC3_DBG_ENTER(1, warp);
-    back_body(b, warp / b.n_tiles, warp % b.n_tiles, lane, T);
+    u8 *region = frames + (size_t)wib * ((b.max_bytes + 3) / 4) * 132;
+    u8 *dst;
+    const i32 nb = back_body(b, warp / b.n_tiles, warp % b.n_tiles, lane, T, SmemBytes{region + 4 * lane}, dst);
+    __syncwarp();
+    // copy-out by the whole warp, one frame (row) at a time
+    for (int r = 0; r < 32; r++) {
+        const i32 n = __shfl_sync(0xffffffffu, nb, r);
+        u8 *d = reinterpret_cast<u8 *>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(dst), r));
+        if (n == 0) continue;
+        if (((reinterpret_cast<unsigned long long>(d) | (unsigned)n) & 3) == 0) {
+            for (int w = lane; w < (n >> 2); w += 32) reinterpret_cast<u32 *>(d)[w] = *reinterpret_cast<const u32 *>(region + w * 132 + 4 * r);
+        } else {
+            for (int i = lane; i < n; i += 32) d[i] = region[(i >> 2) * 132 + 4 * r + (i & 3)];
+        }
+    }
     LC3_DBG_LEAVE();
 }
 LC3_DBG_READER(back)
@@ -70,7 +99,15 @@ extern "C" int lc3k_launch_quant(const LC3K_Batch *b, void *stream)
 }
 extern "C" int lc3k_launch_back(const LC3K_Batch *b, void *stream)
 {
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(k_back, cudaFuncAttributeMaxDynamicSharedMemorySize, BACK_SMEM_MAX);
+        if (e != cudaSuccess) return (int)e;
+        attr_set = true;
+    }
     const int warps = b->n_frames * b->n_tiles, blocks = (warps + BACK_WARPS - 1) / BACK_WARPS;
-    k_back<<<blocks, 32 * BACK_WARPS, 0, (cudaStream_t)stream>>>(*b);
+    const int smem = back_smem_bytes(b->max_bytes);
+    if (smem > BACK_SMEM_MAX) return (int)cudaErrorInvalidValue;
+    k_back<<<blocks, 32 * BACK_WARPS, smem, (cudaStream_t)stream>>>(*b);
     return done();
 }

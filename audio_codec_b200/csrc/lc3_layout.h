@@ -62,6 +62,7 @@ typedef struct {
     int fs_idx, dms, dms_idx, N, yLen, nbands, fs, W_off, W_len, mdct_mem_len, bands_off, nsub, ltpf_mem_in_len,
         r12k8_mem_in_len, bw_bits, bits /* 16 | 24 */;
     int n_lanes, n_tiles, n_frames;
+    int max_bytes;            /* largest CFG_TARGET_BYTES of the bucket's lanes (sizes k_back's shared-memory frame buffers) */
     int frame0;               /* index of this chunk's first frame within the caller's batch */
     /* state pool */
     const int32_t *slot;      /* [n_lanes] */

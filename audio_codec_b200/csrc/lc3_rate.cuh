@@ -255,7 +255,8 @@ LC3_HD int adjust_gain(i32 &gg, i32 gg_min, i32 gg_off, i32 &gain, i32 &gain_e, 
     return change;
 }
 
-// fx/residual_coding_fx.c:14-75; bits packed LSB-first into res[] words; returns their count
+// fx/residual_coding_fx.c:14-75; bits packed LSB-first into res[] words; returns their count.
+// Bins are fetched eight at a time (the loads of a group are independent, so their latencies overlap).
 template <class A, class XQ>
 LC3_HD i32 residual_bits(i32 x_e, A x, XQ xq, i32 gain, i32 gain_e, int L, i32 target, i32 nBits, u32 *res)
 {
@@ -263,14 +264,20 @@ LC3_HD i32 residual_bits(i32 x_e, A x, XQ xq, i32 gain, i32 gain_e, int L, i32 t
     if (m > L) m = L;
     const i32 s = s_sub(s_add(15, gain_e), x_e);
     u32 word = 0;
-    for (int i = 0; i < L; i++) {
-        i32 q = xq[i];
-        if (q == 0) continue;
-        u32 bit = l_sub(x[i], l_shl(l_mult(q, gain), s)) >= 0;
-        word |= bit << (n & 31);
-        n++;
-        if ((n & 31) == 0) { res[(n >> 5) - 1] = word; word = 0; }
-        if (n == m) break;
+    bool done = false;
+    for (int i0 = 0; i0 < L && !done; i0 += 8) {
+        i32 q[8], xv[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) { const int i = imin(i0 + j, L - 1); q[j] = xq[i]; xv[j] = x[i]; }
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            if (done || i0 + j >= L || q[j] == 0) continue;
+            u32 bit = l_sub(xv[j], l_shl(l_mult(q[j], gain), s)) >= 0;
+            word |= bit << (n & 31);
+            n++;
+            if ((n & 31) == 0) { res[(n >> 5) - 1] = word; word = 0; }
+            if (n == m) done = true;
+        }
     }
     if (n & 31) res[n >> 5] = word;
     return n;
@@ -299,11 +306,23 @@ LC3_HD i32 noise_factor(i32 x_e, A x, XQ xq, i32 gg, i32 gg_e, int bw, int dms, 
     i32 nz = -2 * width - 1;
     i32 sum = 0, isum = 0;
     for (k = start - width; k < start + width; k++) nz = xq[k] != 0 ? -2 * width - 1 : s_add(nz, 1);
-    // first sweep: count the selected bins, sum their |x| and (for the split variant) their indices
-    for (k = start; k < N; k++) {
-        if (k < N - width) nz = xq[k + width] != 0 ? -2 * width - 1 : s_add(nz, 1);
-        else nz = s_add(nz, 1);
-        if (nz >= 0) { c++; sum = l_add(sum, l_abs(x[k])); isum = l_add(isum, k); }
+    // first sweep: count the selected bins, sum their |x| and (for the split variant) their indices.  Eight bins per
+    // group, fetched up front (independent loads); bins from N - width on see zeros ahead of them, as in the reference
+    for (int k0 = start; k0 < N; k0 += 8) {
+        i32 q[8], xv[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const int kk = k0 + j;
+            q[j] = kk < N - width ? (i32)xq[kk + width] : 0;
+            xv[j] = x[imin(kk, N - 1)];
+        }
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const int kk = k0 + j;
+            if (kk >= N) break;
+            nz = q[j] != 0 ? -2 * width - 1 : s_add(nz, 1);
+            if (nz >= 0) { c++; sum = l_add(sum, l_abs(xv[j])); isum = l_add(isum, kk); }
+        }
     }
     i32 fac = 0;
     if (c != 0) {

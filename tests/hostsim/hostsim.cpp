@@ -163,7 +163,9 @@ extern "C" int hostsim_encode(void *p, const void *pcm, int bits, int n_frames, 
             for (int i = 0; i < N; i++) h[i] = t[n_frames * N + i];
         }
     }
-    AriTabs T = {(const u8 *)rom_ari_lookup, rom_ari_cumfreq, rom_ari_freq};
+    static u32 ari_cf[1088];
+    for (int i = 0; i < 1088; i++) ari_cf[i] = (u32)rom_ari_freq[i] << 16 | rom_ari_cumfreq[i];
+    AriTabs T = {(const u8 *)rom_ari_lookup, ari_cf};
     static PitchShared psh;
     static RateShared rsh;
     const bool lane_serial = getenv("HOSTSIM_LANE_SERIAL") != 0; // older one-lane-per-stream bodies, kept for debugging
@@ -215,7 +217,11 @@ extern "C" int hostsim_encode(void *p, const void *pcm, int bits, int n_frames, 
                 for (int j = 0; j < 4; j++)
                     qt_analyse(qs.fr[w + 8 * j], qs.xq + (w + 8 * j) * QT_ROW, b.yLen, qs.w[w], (const u8 *)rom_ari_lookup, rom_ari_bits);
             for (int t = 0; t < QT_THREADS; t++) qt_store(b, f, tile, t, qs);
-            for (int lane = 0; lane < 32; lane++) back_body(b, f, tile, lane, T);
+            for (int lane = 0; lane < 32; lane++) {
+                u8 frame[440], *dst;
+                const i32 nb = back_body(b, f, tile, lane, T, LocalBytes{frame}, dst);
+                for (int i = 0; i < nb; i++) dst[i] = frame[i];
+            }
         }
     return 0;
 }
