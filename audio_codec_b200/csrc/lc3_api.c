@@ -310,26 +310,48 @@ static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_
         b.n_frames = n_frames - f0 < fc ? n_frames - f0 : fc;
         b.pcm_t = w[0]; b.pout = (int32_t *)w[1]; b.spec = (int32_t *)w[2]; b.fout = (int32_t *)w[3];
         b.en4 = (int32_t *)w[4]; b.rout = (int32_t *)w[5]; b.r12 = (int16_t *)w[6]; b.xq = (int16_t *)w[7]; b.ben = (int32_t *)w[8];
-        cudaStream_t cur = par;
         if (cp && cp->h_pcm) /* this chunk's columns of every stream's PCM rows, one rectangle per channel */
             for (int ch = 0; ch < c0->channels; ch++) {
                 const size_t off = ((size_t)ch * n_frames + f0) * N * sb;
                 CU(cudaMemcpy2DAsync((char *)d_pcm + off, stride, (const char *)cp->h_pcm + off, stride, (size_t)b.n_frames * N * sb,
                                      (size_t)n, cudaMemcpyHostToDevice, par));
             }
-        for (int k = 0; k < N_KERNELS; k++) {
+        /* The chunk's kernels form a small graph over the two streams.  16-bit input, long frames: the tile MDCT needs only
+         * the staged samples, so it is issued right behind the FIR on `par` and runs beside the per-stream high-pass and
+         * pitch passes on `ser`; SNS then waits for both (it takes the attack flag from the pitch pass).  Otherwise (24-bit
+         * input: the block exponent comes from the pitch pass; short frames: one fused front-end kernel) it is a chain. */
+        const int split = bits == 16 && N >= 160;
+        static const int order_chain[N_KERNELS] = {K_STAGE, K_FIR, K_SCALAR, K_PITCH, K_FRONT, K_SNS, K_TNS, K_RATE, K_QUANT, K_BACK};
+        static const int order_split[N_KERNELS] = {K_STAGE, K_FIR, K_FRONT, K_SCALAR, K_PITCH, K_SNS, K_TNS, K_RATE, K_QUANT, K_BACK};
+        /* producers on the OTHER stream that kernel k must wait for (same-stream producers are ordered by the stream) */
+        static const int dep_chain[N_KERNELS][2] = {{-1, -1}, {K_STAGE, -1}, {K_FIR, -1}, {-1, -1}, {K_PITCH, -1}, {-1, -1}, {-1, -1},
+                                                    {K_TNS, K_FRONT}, {K_RATE, -1}, {-1, -1}};
+        static const int dep_split[N_KERNELS][2] = {{-1, -1}, {K_STAGE, -1}, {K_FIR, -1}, {-1, -1}, {-1, -1}, {K_PITCH, -1}, {-1, -1},
+                                                    {K_TNS, -1}, {K_RATE, -1}, {-1, -1}};
+        const int *order = split ? order_split : order_chain;
+        int ran[N_KERNELS] = {0};
+        cudaStream_t first = NULL;
+        for (int o = 0; o < N_KERNELS; o++) {
+            const int k = order[o];
             if (bits != 16 && (k == K_FIR || k == K_SCALAR)) continue; /* fused into K_PITCH for 24-bit input */
             if (N < 160 && (k == K_SNS || k == K_TNS)) continue;        /* fused into K_FRONT for the short frames */
             const cudaStream_t st = k_stateful[k] ? ser : par;
-            if (st != cur) { /* the chunk's kernels form a chain: hand over between the two streams */
-                CU(cudaEventRecord(g.pipe[p].hop_ev[k], cur));
-                CU(cudaStreamWaitEvent(st, g.pipe[p].hop_ev[k], 0));
-                cur = st;
+            if (!first) { /* the input copy above went to `par`: the first kernel (K_STAGE on `ser`) waits for it */
+                first = st;
+                if (st != par) {
+                    CU(cudaEventRecord(g.pipe[p].hop_ev[N_KERNELS], par));
+                    CU(cudaStreamWaitEvent(st, g.pipe[p].hop_ev[N_KERNELS], 0));
+                }
             }
+            const int *dep = split ? dep_split[k] : dep_chain[k];
+            for (int j = 0; j < 2; j++)
+                if (dep[j] >= 0 && ran[dep[j]] && (k_stateful[dep[j]] ? ser : par) != st) CU(cudaStreamWaitEvent(st, g.pipe[p].hop_ev[dep[j]], 0));
             if (k_stateful[k] && c > 0) CU(cudaStreamWaitEvent(st, g.pipe[(c - 1) % N_PIPES].state_ev[k], 0));
             if (g.prof_on) CU(cudaEventRecord(g.ev[c * EPC + 2 * k], st));
             CU((cudaError_t)launch[k](&b, st));
             if (g.prof_on) CU(cudaEventRecord(g.ev[c * EPC + 2 * k + 1], st));
+            CU(cudaEventRecord(g.pipe[p].hop_ev[k], st));
+            ran[k] = 1;
             if (k_stateful[k] && c + 1 < n_chunks) CU(cudaEventRecord(g.pipe[p].state_ev[k], st));
         }
         /* K_BACK ran on `par` */

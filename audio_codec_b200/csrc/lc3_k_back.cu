@@ -51,7 +51,7 @@ struct SmemBytes {
 #ifndef BACK_WARPS
 #define BACK_WARPS 8
 #endif
-#define BACK_SMEM_MAX (100 * 1024)
+#define BACK_SMEM_MAX (4096 + 1088 * 4 + BACK_WARPS * (440 / 4) * 132) /* frames of up to 440 bytes */
 static int back_smem_bytes(int max_bytes) { return 4096 + 1088 * 4 + BACK_WARPS * ((max_bytes + 3) / 4) * 132; }
 __global__ void __launch_bounds__(32 * BACK_WARPS) k_back(LC3K_Batch b)
 {

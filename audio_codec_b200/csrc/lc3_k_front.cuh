@@ -66,7 +66,7 @@ template <int N, int BITS> __global__ void __launch_bounds__(256, 2) k_mdct(LC3K
     __syncthreads();
     mt_bands<N>(b, t, X, ben, bexp, smx);
     __syncthreads();
-    mt_store<N>(b, f, tile, t, X, mx, mn, ben, bexp, smx);
+    mt_store<N, BITS>(b, f, tile, t, X, mx, mn, ben, bexp, smx);
     LC3_DBG_LEAVE();
 }
 

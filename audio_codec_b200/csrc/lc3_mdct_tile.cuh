@@ -91,8 +91,9 @@ template <int N, int BITS> LC3_HD void mt_fold(const LC3K_Batch &b, int f, int t
     i32 *y = X + lane * G::S;
     Range rg; range_init(rg);
     if (li < b.n_lanes) {
-        SV<const i32> po = tile_view((const i32 *)b.pout, frame_tile(b, f, tile), PO_N, lane);
-        PcmView<BITS> xs = pcm_view<BITS>(b, tile, lane, f, po[PO_X_EXP]);
+        // 16-bit input has the fixed exponent 15 (fx/enc_lc3.c:60-62), so this kernel does not wait for the pitch pass
+        const i32 x_exp = BITS == 16 ? 15 : tile_view((const i32 *)b.pout, frame_tile(b, f, tile), PO_N, lane)[PO_X_EXP];
+        PcmView<BITS> xs = pcm_view<BITS>(b, tile, lane, f, x_exp);
         const i16 *win = &rom_win[b.W_off];
         const int memLen = b.mdct_mem_len, z = 2 * N - b.W_len;
         for (int i = part; i < m; i += G::PARTS) { // same three expressions as mdct_frame()
@@ -220,7 +221,7 @@ template <int N> LC3_HD void mt_bands(const LC3K_Batch &b, int t, const i32 *X, 
 }
 
 // ---- store: thread t = (tile lane, part): spectrum, block exponent, aligned band energies and their exponent
-template <int N> LC3_HD void mt_store(const LC3K_Batch &b, int f, int tile, int t, const i32 *X, const i32 *mx, const i32 *mn,
+template <int N, int BITS> LC3_HD void mt_store(const LC3K_Batch &b, int f, int tile, int t, const i32 *X, const i32 *mx, const i32 *mn,
                                       const i32 *ben, const i32 *bexp, const i32 *smx)
 {
     typedef MdctTile<N> G;
@@ -230,7 +231,7 @@ template <int N> LC3_HD void mt_store(const LC3K_Batch &b, int f, int tile, int 
     const i32 *y = X + lane * G::S;
     SV<i32> d = tile_view(b.spec, ft, N, lane);
     for (int e = part; e < N; e += G::PARTS) d[e] = y[mt_ridx(e)];
-    const i32 x_exp = tile_view((const i32 *)b.pout, ft, PO_N, lane)[PO_X_EXP];
+    const i32 x_exp = BITS == 16 ? 15 : tile_view((const i32 *)b.pout, ft, PO_N, lane)[PO_X_EXP];
     const i32 d_exp = s_add(s_add(s_sub(s_sub(x_exp, 2), mt_shift<N>(mx, mn, lane)), G::FFT_SCALE), 2);
     i32 smax = -31;
     for (int p = 0; p < G::PARTS; p++) smax = imax(smax, smx[p * 32 + lane]);

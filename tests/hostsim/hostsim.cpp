@@ -49,7 +49,7 @@ template <int N, int BITS> static void run_mdct_tile(const LC3K_Batch &b, int f,
     for (int t = 0; t < G::THREADS; t++) { const int w = t >> 5, l = t & 31; for (int j = 0; j < 4; j++) mt_post<N>(X, w + 8 * j, l, T); }
     i32 *smx = mn + G::PARTS * 32, *ben = smx + G::PARTS * 32, *bexp = ben + 32 * G::BROW;
     for (int t = 0; t < G::THREADS; t++) mt_bands<N>(b, t, X, ben, bexp, smx);
-    for (int t = 0; t < G::THREADS; t++) mt_store<N>(b, f, tile, t, X, mx, mn, ben, bexp, smx);
+    for (int t = 0; t < G::THREADS; t++) mt_store<N, BITS>(b, f, tile, t, X, mx, mn, ben, bexp, smx);
 }
 template <int BITS> static void run_front_tile(const LC3K_Batch &b, int f, int tile)
 { // same split as front_launch_tiled / front_launch
