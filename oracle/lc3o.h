@@ -35,6 +35,8 @@ void lc3o_enc_free(lc3o_enc *e);
 int lc3o_enc_set_frame_dms(lc3o_enc *e, int dms);
 int lc3o_enc_set_bitrate(lc3o_enc *e, int bitrate);
 int lc3o_enc_set_bandwidth(lc3o_enc *e, int bandwidth);
+int lc3o_enc_set_ep_mode(lc3o_enc *e, int epmode);          /* 0..4, fx/lc3.h:288 */
+int lc3o_enc_set_ep_mode_request(lc3o_enc *e, int epmr);    /* 0..3, fx/lc3.h:300 */
 int lc3o_enc_get_input_samples(const lc3o_enc *e);
 int lc3o_enc_get_num_bytes(const lc3o_enc *e);
 int lc3o_enc_get_delay(const lc3o_enc *e);

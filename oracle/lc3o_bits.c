@@ -4,10 +4,30 @@
  * the quantised spectrum written forwards from byte 0 (fx/ari_codec.c:94-406, :1348-1527). */
 #include "lc3o_internal.h"
 
-typedef struct { uint8_t *p; i16 bp, mask; } bwr; /* backward bit writer */
+/* Partial concealment (error protection modes 3 and 4): where the block of `bytes` least-sensitive payload bytes starts.
+ * The reference finds it by running its DECODER over the frame it has just written (fx/enc_lc3.c:247-259,
+ * processAriDecoder_fx in mode 1) and stopping when the bytes not yet consumed between the decoder's forward (range
+ * coder) and backward (side bits) read positions number exactly `bytes` (check_pc_bytes, fx/ari_codec.c:1823-1872).
+ * The decoder consumes bytes in the order the encoder produces symbols and bits -- three bytes up front
+ * (ac_dec_init_fx, :1559-1580), one per renormalisation shift of a decoded symbol (ac_dec_update_fx, :1776-1795), one
+ * whenever a side bit is read from a fresh byte -- so the encoder can count along: cl = bytes the decoder has read from
+ * the left so far; the writer's own position is the decoder's backward position. */
+typedef struct { int bytes, cl, b_left; } pc_t;
+
+typedef struct { uint8_t *p; i16 bp, mask; pc_t *pc; } bwr; /* backward bit writer */
+
+static void pc_from_left(pc_t *pc, const bwr *w)
+{ /* check_pc_bytes(from_left = 1) before the decoder reads byte cl */
+    if (!pc || pc->bytes <= 0) return;
+    const int side = w->bp + (w->mask == 1);
+    if (pc->b_left < 0 && side - 1 - pc->cl == pc->bytes) pc->b_left = pc->cl + 1;
+    pc->cl++;
+}
 
 static void put_bit(bwr *w, int bit)
 {
+    if (w->pc && w->pc->bytes > 0 && w->mask == 1 && w->pc->b_left < 0 && w->bp - w->pc->cl == w->pc->bytes)
+        w->pc->b_left = w->pc->cl; /* check_pc_bytes(from_left = 0): the decoder is about to open byte bp */
     if (bit > 0) w->p[w->bp] |= (uint8_t)w->mask;
     w->mask = (i16)(w->mask << 1);
     if (w->mask == 0x100) w->mask = 1;
@@ -26,6 +46,7 @@ void o_side_info(uint8_t *bytes, i16 *bp_side, i16 *mask_side, i16 nbbits, i16 t
     static const i16 lastnz_trigger[5] = {63, 127, 127, 255, 255};
     bwr w;
     w.p = bytes;
+    w.pc = NULL;
     w.bp = s_shr(s_sub(nbbits, 1), 3);
     w.mask = s_shl(1, s_sub(8, s_sub(nbbits, s_shl(w.bp, 3))));
     memset(bytes, 0, targetBytes);
@@ -68,7 +89,7 @@ void o_side_info(uint8_t *bytes, i16 *bp_side, i16 *mask_side, i16 nbbits, i16 t
 }
 
 /* ------------------------------------------------------------------ range coder */
-typedef struct { u32 low, range; i16 cache, carry, carry_count; uint8_t *p; i16 bp; } rc_t;
+typedef struct { u32 low, range; i16 cache, carry, carry_count; uint8_t *p; i16 bp; pc_t *pc; const bwr *w; } rc_t;
 
 /* fx/ari_codec.c:1374-1406 : emit one byte (with deferred carry resolution) */
 static void rc_shift(rc_t *s)
@@ -106,6 +127,7 @@ static void rc_encode(rc_t *s, u32 cum, u32 freq)
     while (s->range < (1u << 16)) {
         s->range <<= 8;
         rc_shift(s);
+        pc_from_left(s->pc, s->w); /* the decoder shifts one byte in for every byte shifted out here */
     }
 }
 
@@ -156,15 +178,17 @@ static inline void enc_sym(rc_t *s, int ctx, int sym)
     rc_encode(s, rom_ari_cumfreq[row], rom_ari_freq[row]);
 }
 
-/* fx/ari_codec.c:94-406 */
-void o_ari_encode(uint8_t *bytes, i16 bp_side, i16 mask_side, i16 nbbits, const i16 *xq, const i16 *tns_order,
-                  i16 nfilt, const i16 *tns_idx, i16 lastnz, const i16 *cd, const uint8_t *res, i16 nres,
-                  i16 lsbMode, int lpc_weighting)
+/* fx/ari_codec.c:94-406.  n_pc > 0: also returns where the partial-concealment block starts (see pc_t), else -1. */
+int o_ari_encode(uint8_t *bytes, i16 bp_side, i16 mask_side, i16 nbbits, const i16 *xq, const i16 *tns_order,
+                 i16 nfilt, const i16 *tns_idx, i16 lastnz, const i16 *cd, const uint8_t *res, i16 nres,
+                 i16 lsbMode, int lpc_weighting, int n_pc)
 {
     i16 lsb[2 * LC3O_MAX_N];
     int nlsbs = 0;
-    bwr w = {bytes, bp_side, mask_side};
-    rc_t s = {0, 0x00ffffffu, -1, 0, 0, bytes, 0};
+    pc_t pc = {(n_pc + 1) >> 1, 0, -1};
+    bwr w = {bytes, bp_side, mask_side, &pc};
+    rc_t s = {0, 0x00ffffffu, -1, 0, 0, bytes, 0, &pc, &w};
+    for (int i = 0; i < 3; i++) pc_from_left(&pc, &w); /* ac_dec_init_fx */
 
     for (int n = 0; n < nfilt; n++) {
         if (tns_order[n] <= 0) continue;
@@ -240,5 +264,8 @@ void o_ari_encode(uint8_t *bytes, i16 bp_side, i16 mask_side, i16 nbbits, const 
         int m = s_min((i16)nlsbs, n);
         for (int i = 0; i < m; i++) put_bit(&w, lsb[i]);
     }
+    s.pc = NULL; /* the termination bytes are not decoder reads */
     rc_finish(&s);
+    if (pc.bytes <= 0) return -1;
+    return pc.b_left >= 0 ? pc.b_left : w.bp - pc.bytes; /* fx/ari_codec.c:1133-1141 */
 }

@@ -2,7 +2,7 @@
  * Encoder setup and per-frame driver: restates fx/setup_enc_lc3.c:38-281 (configuration derived from
  * sample rate / frame size / bitrate), fx/lc3.c:124-267 (argument checks and error order),
  * fx/scale_signal24_fx.c:13-92 (24-bit input block scaling) and fx/enc_lc3.c:15-315 (stage order).
- * Error protection (epmode > 0) is out of scope.
+ * Error protection (epmode 1-4): sizes and the channel coder are in lc3o_fec.c.
  *
  * The oracle's own API (lc3o_*) is what tests/ call; it is deliberately not the product's C ABI.
  */
@@ -17,6 +17,7 @@ typedef struct {
     i32 tbits_off;
     i16 target_bytes, total_bits, tbits_init, tbits_ari, lpc_weighting, ltpf_enable, qgain_off;
     i16 mem_tbits, mem_specbits, x_exp, resamp_exp, attack_handling;
+    i16 n_pccw, n_pc; /* partial concealment: codewords / nibbles (error protection modes 3 and 4) */
     o_attdec_state att;
     o_pitch_state pitch;
 } chan_t;
@@ -25,6 +26,7 @@ struct lc3o_enc {
     int fs, fs_in, fs_idx, bitrate, channels, dms, dms_idx, br_set;
     int N, yLen, W_size, la_zeroes, mdct_mem_len, nbands, nsub, ltpf_mem_in_len, bw_bits, r12k8_mem_in_len;
     int bandwidth, bw_cutoff_bin, bw_index;
+    int epmode, epmr, ccc; /* error protection mode, mode request, combined channel coding */
     const i16 *W, *bands;
     chan_t ch[2];
 };
@@ -48,7 +50,7 @@ static void set_frame_params(lc3o_enc *e)
     e->bands = &rom_bands_offset[rom_bands_offset_off[k]];
 }
 
-/* fx/setup_enc_lc3.c:130-281 (epmode 0 only) */
+/* fx/setup_enc_lc3.c:130-281 */
 static int update_bitrate(lc3o_enc *e, int bitrate)
 {
     int minBR = (int)(20 * 8.0 * (10000.0 / e->dms) * (e->fs_in == 44100 ? 441. / 480 : 1));
@@ -58,10 +60,28 @@ static int update_bitrate(lc3o_enc *e, int bitrate)
     if (bitrate < minBR || bitrate > maxBR) return LC3O_BITRATE_ERROR;
     e->bitrate = bitrate;
     e->br_set = 1;
-    int total = (int)((int32_t)bitrate * e->N / (8 * e->fs_in));
+    const int slot_total = (int)((int32_t)bitrate * e->N / (8 * e->fs_in));
+    e->ccc = e->channels > 1 && e->epmode && bitrate * e->N / (8 * e->fs_in) <= 160;
+    if (e->epmode > 0) {
+        int mb = bitrate * e->N / (8 * e->fs_in * e->channels);
+        if (mb < 40 || mb > 300) return LC3O_BITRATE_ERROR; /* FEC_SLOT_BYTES_MIN / _MAX */
+    }
+    int total = slot_total;
+    if (e->ccc) {
+        total = o_fec_data_size(e->epmode, 1, slot_total);
+        e->ch[0].n_pccw = (i16)o_fec_n_pccw(slot_total, e->epmode, 1);
+        e->ch[0].n_pc = (i16)o_fec_n_pc(e->epmode, e->ch[0].n_pccw, slot_total);
+    }
     for (int c = 0; c < e->channels; c++) {
         chan_t *s = &e->ch[c];
-        s->target_bytes = (i16)(total / e->channels + (c < (total % e->channels)));
+        const int channel_bytes = total / e->channels + (c < (total % e->channels));
+        if (e->ccc) {
+            s->target_bytes = (i16)channel_bytes;
+        } else {
+            s->target_bytes = (i16)o_fec_data_size(e->epmode, 0, channel_bytes);
+            s->n_pccw = (i16)o_fec_n_pccw(channel_bytes, e->epmode, 0);
+            s->n_pc = (i16)o_fec_n_pc(e->epmode, s->n_pccw, channel_bytes);
+        }
         if (s->target_bytes < 20 || s->target_bytes > 435) return LC3O_BITRATE_ERROR;
         s->total_bits = s_shl(s->target_bytes, 3);
         s->tbits_init = s_sub(s->total_bits, (i16)(38 + 8 + 3 + e->bw_bits));
@@ -140,6 +160,22 @@ int lc3o_enc_set_bitrate(lc3o_enc *e, int bitrate)
     if (!e) return LC3O_NULL_ERROR;
     if (bitrate <= 0) return LC3O_BITRATE_ERROR;
     return update_bitrate(e, bitrate);
+}
+
+/* fx/lc3.c:199-214 */
+int lc3o_enc_set_ep_mode(lc3o_enc *e, int epmode)
+{
+    if (!e) return LC3O_NULL_ERROR;
+    if ((unsigned)epmode > 4) return 9; /* LC3_EPMODE_ERROR */
+    e->epmode = epmode;
+    return e->br_set ? update_bitrate(e, e->bitrate) : LC3O_OK;
+}
+int lc3o_enc_set_ep_mode_request(lc3o_enc *e, int epmr)
+{
+    if (!e) return LC3O_NULL_ERROR;
+    if ((unsigned)epmr > 3) return 12; /* LC3_EPMR_ERROR */
+    e->epmr = epmr;
+    return LC3O_OK;
 }
 
 /* fx/lc3.c:226-244 */
@@ -250,8 +286,10 @@ static void encode_channel(lc3o_enc *e, chan_t *s, int bps, const void *in, uint
 
     o_side_info(bytes, &bp_side, &mask_side, s->tbits_ari, s->target_bytes, e->yLen, (i16)e->bw_bits, nfilt, lsbMode,
                 lastnz, tns_order, fac_ns, qgain, bw, ltpf_idx, scf_idx, bfi_ext, e->fs_idx);
-    o_ari_encode(bytes, bp_side, mask_side, s->tbits_ari, xq, tns_order, nfilt, tns_idx, lastnz, cd, res, nres,
-                 lsbMode, s->lpc_weighting);
+    const int n_pc = (!e->ccc && s->n_pc > 0) ? s->n_pc : 0; /* fx/enc_lc3.c:247-259 */
+    const int b_left = o_ari_encode(bytes, bp_side, mask_side, s->tbits_ari, xq, tns_order, nfilt, tns_idx, lastnz, cd, res, nres,
+                                    lsbMode, s->lpc_weighting, n_pc);
+    if (n_pc > 0) o_reorder(bytes, s->n_pccw, s->n_pc, b_left);
     if (tr) {
         memcpy(tr->spec, d, sizeof(d)); memcpy(tr->xq, xq, sizeof(xq)); memcpy(tr->scf_idx, scf_idx, sizeof(scf_idx));
         tr->bw = bw; tr->tns_bits = tns_bits; tr->ltpf_bits = ltpf_bits; tr->qgain = qgain; tr->lastnz = lastnz;
@@ -266,9 +304,20 @@ static int encode(lc3o_enc *e, void **in, int bps, uint8_t *out, int *num_bytes,
     for (int c = 0; c < e->channels; c++) if (!in[c]) return LC3O_NULL_ERROR;
     if (!e->br_set) return LC3O_BITRATE_UNSET_ERROR;
     int bfi_ext = *num_bytes == -1, n = 0;
+    const int total = (int)((int32_t)e->bitrate * e->N / (8 * e->fs_in));
     for (int c = 0; c < e->channels; c++) {
         encode_channel(e, &e->ch[c], bps, in[c], out + n, bfi_ext, tr);
-        n += e->ch[c].target_bytes;
+        if (e->epmode && !e->ccc) { /* one channel-coded slot per channel */
+            const int slot = total / e->channels + (c < (total % e->channels));
+            o_fec_encode(e->epmode, e->epmr, out + n, e->ch[c].target_bytes, slot, e->ch[c].n_pccw);
+            n += slot;
+        } else {
+            n += e->ch[c].target_bytes;
+        }
+    }
+    if (e->epmode > 0 && e->ccc) { /* both channels in one slot */
+        o_fec_encode(e->epmode, e->epmr, out, n, total, e->ch[0].n_pccw);
+        n = total;
     }
     *num_bytes = n;
     return LC3O_OK;

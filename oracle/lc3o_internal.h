@@ -87,7 +87,14 @@ i16 o_noise_factor(i16 x_e, const i32 *x, const i16 *xq, i16 gg, i16 gg_e, int b
 void o_side_info(uint8_t *bytes, i16 *bp_side, i16 *mask_side, i16 nbbits, i16 targetBytes, int L, i16 bw_bits,
                  i16 nfilt, i16 lsbMode, i16 lastnz, const i16 *tns_order, i16 fac_ns, i16 gg, i16 bw,
                  const i16 *ltpf_idx, const i32 *scf_idx, int bfi_ext, int fs_idx);
-void o_ari_encode(uint8_t *bytes, i16 bp_side, i16 mask_side, i16 nbbits, const i16 *xq, const i16 *tns_order,
-                  i16 nfilt, const i16 *tns_idx, i16 lastnz, const i16 *cdata, const uint8_t *res, i16 nres,
-                  i16 lsbMode, int lpc_weighting);
+int o_ari_encode(uint8_t *bytes, i16 bp_side, i16 mask_side, i16 nbbits, const i16 *xq, const i16 *tns_order,
+                 i16 nfilt, const i16 *tns_idx, i16 lastnz, const i16 *cdata, const uint8_t *res, i16 nres,
+                 i16 lsbMode, int lpc_weighting, int n_pc);
+
+/* ---- lc3o_fec.c (fx/al_fec.c encoder half, fx/reorder_bitstream_fx.c) */
+int o_fec_n_pccw(int slot_bytes, int mode, int ccc);
+int o_fec_data_size(int mode, int ccc, int slot_bytes);
+int o_fec_n_pc(int mode, int n_pccw, int slot_bytes);
+void o_fec_encode(int mode, int epmr, uint8_t *iobuf, int data_bytes, int slot_bytes, int n_pccw);
+void o_reorder(uint8_t *bytes, int n_pccw, int n_pc, int b_left);
 #endif

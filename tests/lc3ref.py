@@ -37,7 +37,8 @@ def oracle_lib():
         _ora = C.CDLL(ORACLE_SO)
         _ora.lc3o_enc_new.restype = C.c_void_p
         _ora.lc3o_enc_free.argtypes = [C.c_void_p]
-        for n in ("lc3o_enc_set_frame_dms", "lc3o_enc_set_bitrate", "lc3o_enc_set_bandwidth"):
+        for n in ("lc3o_enc_set_frame_dms", "lc3o_enc_set_bitrate", "lc3o_enc_set_bandwidth", "lc3o_enc_set_ep_mode",
+                  "lc3o_enc_set_ep_mode_request"):
             getattr(_ora, n).argtypes = [C.c_void_p, C.c_int]
         for n in ("lc3o_enc_get_input_samples", "lc3o_enc_get_num_bytes", "lc3o_enc_get_delay",
                   "lc3o_enc_get_real_bitrate"):
@@ -92,6 +93,12 @@ class RefEnc(_Base):
     def set_bandwidth(self, bw):
         return ref_lib().lc3_enc_set_bandwidth(self.h, bw)
 
+    def set_ep_mode(self, epmode):
+        return ref_lib().lc3_enc_set_ep_mode(self.h, epmode)
+
+    def set_ep_mode_request(self, epmr):
+        return ref_lib().lc3_enc_set_ep_mode_request(self.h, epmr)
+
     @property
     def frame_len(self):
         return ref_lib().lc3_enc_get_input_samples(self.h)
@@ -127,6 +134,12 @@ class OracleEnc(_Base):
 
     def set_bandwidth(self, bw):
         return oracle_lib().lc3o_enc_set_bandwidth(self.h, bw)
+
+    def set_ep_mode(self, epmode):
+        return oracle_lib().lc3o_enc_set_ep_mode(self.h, epmode)
+
+    def set_ep_mode_request(self, epmr):
+        return oracle_lib().lc3o_enc_set_ep_mode_request(self.h, epmr)
 
     @property
     def frame_len(self):
