@@ -131,6 +131,13 @@ class Encoder:
     def set_bandwidth(self, bw):
         return load_library().lc3_enc_set_bandwidth(self.h, bw)
 
+    def set_ep_mode(self, epmode):
+        """lc3_enc_set_ep_mode: 0 off, 1..4 (fx/lc3.h:74-82); changes num_bytes' payload share, not num_bytes."""
+        return load_library().lc3_enc_set_ep_mode(self.h, epmode)
+
+    def set_ep_mode_request(self, epmr):
+        return load_library().lc3_enc_set_ep_mode_request(self.h, epmr)
+
     @property
     def frame_len(self):
         return load_library().lc3_enc_get_input_samples(self.h)

@@ -227,18 +227,19 @@ static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_
     size_t n_lanes = 0;
     for (int i = 0; i < n; i++) n_lanes += encs[idx[i]]->cfg.channels;
     if (lanes_reserve(n_lanes)) return 1;
-    int any_bfi = 0, max_bytes = 0;
+    int any_bfi = 0, max_bytes = 0, any_ep = 0;
     size_t l = 0;
     for (int i = 0; i < n; i++) {
         const struct LC3_Enc *e = encs[idx[i]];
         int nb = lc3cfg_num_bytes(&e->cfg), boff = 0;
+        any_ep |= e->cfg.epmode;
         for (int ch = 0; ch < e->cfg.channels; ch++, l++) {
             if (e->cfg.ch[ch][CFG_TARGET_BYTES] > max_bytes) max_bytes = e->cfg.ch[ch][CFG_TARGET_BYTES];
             g.h_slot[l] = e->slot[ch];
             g.h_poff[l] = (int64_t)((size_t)idx[i] * stride / sb) + (int64_t)ch * n_frames * N;
             g.h_ooff[l] = (int64_t)((size_t)idx[i] * ostride) + boff;
             g.h_ostride[l] = nb;
-            boff += e->cfg.ch[ch][CFG_TARGET_BYTES];
+            boff += lc3cfg_out_bytes(&e->cfg, ch);
         }
         if (num_bytes_in)
             for (int f = 0; f < n_frames && !any_bfi; f++) any_bfi = num_bytes_in[(size_t)idx[i] * n_frames + f] == -1;
@@ -354,7 +355,8 @@ static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_
             ran[k] = 1;
             if (k_stateful[k] && c + 1 < n_chunks) CU(cudaEventRecord(g.pipe[p].state_ev[k], st));
         }
-        /* K_BACK ran on `par` */
+        /* K_BACK ran on `par`; error protection, if any lane asks for it, codes the finished payloads in place */
+        if (any_ep) { CU((cudaError_t)lc3k_launch_fec(&b, par)); g.launches++; }
         if (cp && cp->h_out) {
             const size_t nb = (size_t)lc3cfg_num_bytes(c0), off = (size_t)f0 * nb;
             CU(cudaMemcpy2DAsync((char *)cp->h_out + off, ostride, d_out + off, ostride, (size_t)b.n_frames * nb, (size_t)n,
@@ -564,16 +566,22 @@ LC3_Error lc3_enc_set_bandwidth(LC3_Enc *encoder, int bandwidth)
     return (LC3_Error)r;
 }
 LC3_Error lc3_enc_set_ep_mode(LC3_Enc *encoder, LC3_EpMode epmode)
-{ /* fx/lc3.c:199-205; only LC3_EP_OFF is implemented */
+{ /* fx/lc3.c:199-205 */
     if (encoder == NULL) return LC3_NULL_ERROR;
     if ((unsigned)epmode > LC3_EP_HIGH) return LC3_EPMODE_ERROR;
-    return epmode == LC3_EP_OFF ? LC3_OK : LC3_EPMODE_ERROR;
+    if (encoder->magic != LC3B_MAGIC) return LC3_ERROR;
+    int r = lc3cfg_set_ep_mode(&encoder->cfg, (int)epmode);
+    if (r == 0) encoder->dirty = 1;
+    return (LC3_Error)r;
 }
 LC3_Error lc3_enc_set_ep_mode_request(LC3_Enc *encoder, LC3_EpModeRequest epmr)
-{ /* fx/lc3.c:207-213; the request is only carried in error-protected frames */
+{ /* fx/lc3.c:207-213; the request is carried in error-protected frames */
     if (encoder == NULL) return LC3_NULL_ERROR;
     if ((unsigned)epmr > LC3_EPMR_HIGH) return LC3_EPMR_ERROR;
-    return LC3_OK;
+    if (encoder->magic != LC3B_MAGIC) return LC3_ERROR;
+    int r = lc3cfg_set_ep_mode_request(&encoder->cfg, (int)epmr);
+    if (r == 0) encoder->dirty = 1;
+    return (LC3_Error)r;
 }
 
 /* one frame through the batch engine: gather the caller's per-channel pointers into a planar block */

@@ -86,6 +86,25 @@ LC3_HD void side_info(BackWriter<B> &w, B bytes, i32 nbbits, int L, const SideIn
     put_bits(w, si.fac_ns, 3);
 }
 
+// ---- partial concealment (error protection modes 3 and 4).  The reference runs its decoder over the frame it has just
+// written (fx/enc_lc3.c:247-259) to find where the block of `bytes` least-sensitive payload bytes starts: the point at which
+// the bytes not yet consumed between the decoder's forward (range coder) and backward (side bits) read positions number
+// exactly `bytes` (check_pc_bytes, fx/ari_codec.c:1823-1872).  The decoder consumes bytes in the order the encoder makes
+// symbols and bits -- three up front (ac_dec_init_fx), one per renormalisation shift of a symbol (ac_dec_update_fx), one
+// whenever a side bit comes from a fresh byte -- so the encoder counts along instead: cl = bytes read from the left so far.
+struct PcTrack { i32 bytes, cl, b_left; };
+template <class B> LC3_HD void pc_from_left(PcTrack &pc, const BackWriter<B> &w)
+{ // before the decoder reads byte cl
+    const i32 side = w.bp + (w.n == 0 ? 1 : 0);
+    if (pc.b_left < 0 && side - 1 - pc.cl == pc.bytes) pc.b_left = pc.cl + 1;
+    pc.cl++;
+}
+template <class B> LC3_HD void pc_from_right(PcTrack &pc, const BackWriter<B> &w, int cnt)
+{ // before cnt (<= 8) bits are appended: at most one of them opens a fresh byte
+    const i32 first = (8 - w.n) & 7; // index of the first bit that lands on a byte start
+    if (first < cnt && pc.b_left < 0 && (w.bp - (w.n == 0 ? 0 : 1)) - pc.cl == pc.bytes) pc.b_left = pc.cl;
+}
+
 // ---- range coder (fx/ari_codec.c:1374-1527)
 template <class B> struct RangeCoder { u32 low, range; i32 cache, carry, carry_count; B p; i32 bp; };
 
@@ -110,7 +129,7 @@ LC3_HD u32 add24(u32 a, u32 b, int &wrap)
     wrap = r < x;
     return r >> 8;
 }
-template <class B> LC3_HD void rc_encode(RangeCoder<B> &s, u32 cum, u32 freq)
+template <class B> LC3_HD void rc_encode(RangeCoder<B> &s, u32 cum, u32 freq, PcTrack &pc, const BackWriter<B> &w)
 { // fx/ari_codec.c:1408-1446
     u32 r = s.range >> 10;
     int carry;
@@ -120,6 +139,7 @@ template <class B> LC3_HD void rc_encode(RangeCoder<B> &s, u32 cum, u32 freq)
     while (s.range < (1u << 16)) {
         s.range <<= 8;
         rc_shift(s);
+        if (pc.bytes > 0) pc_from_left(pc, w); // the decoder shifts a byte in for every byte shifted out here
     }
 }
 template <class B> LC3_HD void put_fwd(B p, i32 bp, i32 v, int n)
@@ -174,10 +194,13 @@ LC3_HD i32 res_bit(const u32 *res, int i) { return (i32)((res[i >> 5] >> (i & 31
 // their tuples look like; only the short "fetch the next tuple" block is predicated.  The forward (range coder) and
 // backward (bits) streams are independent, so only the order inside each stream has to match the reference, and it does:
 // per tuple, bit planes in rising level, then the signs.
+// n_pc > 0 (partial concealment, see PcTrack): returns the first byte of the concealment block, else -1.
 template <class B, class XQ>
-LC3_HD void ari_encode(B bytes, BackWriter<B> &w, i32 nbbits, XQ xq, int nt, i32 rateFlag, const TnsOut &tns, i32 lastnz,
-                       const u32 *res, i32 nres, i32 lsbMode, int lpc_weighting, const AriTabs &T, u32 *lsbs)
+LC3_HD i32 ari_encode(B bytes, BackWriter<B> &w, i32 nbbits, XQ xq, int nt, i32 rateFlag, const TnsOut &tns, i32 lastnz,
+                      const u32 *res, i32 nres, i32 lsbMode, int lpc_weighting, const AriTabs &T, u32 *lsbs, i32 n_pc)
 {
+    PcTrack pc = {(n_pc + 1) >> 1, 0, -1};
+    if (pc.bytes > 0) for (int i = 0; i < 3; i++) pc_from_left(pc, w); // ac_dec_init_fx, fx/ari_codec.c:1559-1580
     int nlsbs = 0;
     u32 lword = 0;
     auto push_lsb = [&](i32 b) {
@@ -190,10 +213,10 @@ LC3_HD void ari_encode(B bytes, BackWriter<B> &w, i32 nbbits, XQ xq, int nt, i32
     for (int n = 0; n < tns.nfilt; n++) {
         if (tns.order[n] <= 0) continue;
         const int o = tns.order[n] - 1;
-        rc_encode(s, (u32)rom_tns_order_cumfreq[lpc_weighting * 8 + o], (u32)rom_tns_order_freq[lpc_weighting * 8 + o]);
+        rc_encode(s, (u32)rom_tns_order_cumfreq[lpc_weighting * 8 + o], (u32)rom_tns_order_freq[lpc_weighting * 8 + o], pc, w);
         for (int k = 0; k < tns.order[n]; k++) {
             const int ix = k * 17 + tns.idx[8 * n + k];
-            rc_encode(s, (u32)rom_tns_coef_cumfreq[ix], (u32)rom_tns_coef_freq[ix]);
+            rc_encode(s, (u32)rom_tns_coef_cumfreq[ix], (u32)rom_tns_coef_freq[ix], pc, w);
         }
     }
 
@@ -225,7 +248,7 @@ LC3_HD void ari_encode(B bytes, BackWriter<B> &w, i32 nbbits, XQ xq, int nt, i32
         {
             const int row = T.lut[ctx + rom_ari_esc_nb[l < 3 ? l : 3]] * 17 + (last ? msb : 16);
             const u32 cf = T.cf[row];
-            rc_encode(s, cf & 0xffffu, cf >> 16);
+            rc_encode(s, cf & 0xffffu, cf >> 16, pc, w);
         }
         if (!last) { // bit plane l of both magnitudes
             const i32 ta = (a1 >> l) & 1, tb = (b1 >> l) & 1;
@@ -236,6 +259,7 @@ LC3_HD void ari_encode(B bytes, BackWriter<B> &w, i32 nbbits, XQ xq, int nt, i32
                 push_lsb(tb);
                 if (bm == 0 && tb > 0) push_lsb(b < 0 ? 1 : 0);
             } else {
+                if (pc.bytes > 0) pc_from_right(pc, w, 2);
                 put_bits(w, ta | (tb << 1), 2);
             }
             l++;
@@ -243,6 +267,7 @@ LC3_HD void ari_encode(B bytes, BackWriter<B> &w, i32 nbbits, XQ xq, int nt, i32
             const bool div = lsbMode != 0 && lev > 0;
             const i32 sa = (div ? (a1 >> 1) : a1) != 0, sb = (div ? (b1 >> 1) : b1) != 0;
             const i32 na_ = (a >> 15) & 1, nb_ = (b >> 15) & 1;
+            if (pc.bytes > 0) pc_from_right(pc, w, sa + sb);
             put_bits(w, sa ? (na_ | (nb_ << 1)) : nb_, sa + sb);
             k += 2;
             l = 0;
@@ -262,10 +287,24 @@ LC3_HD void ari_encode(B bytes, BackWriter<B> &w, i32 nbbits, XQ xq, int nt, i32
     for (int i = 0; i < m; i += 8) { // eight at a time
         const int cnt = imin(8, m - i);
         const u32 v = src[i >> 5] >> (i & 31); // i is a multiple of 8: the group never straddles two words
+        if (pc.bytes > 0) pc_from_right(pc, w, cnt);
         put_bits(w, (i32)(v & 0xffu), cnt);
     }
+    const i32 b_left = pc.bytes <= 0 ? -1 : (pc.b_left >= 0 ? pc.b_left : w.bp - pc.bytes); // fx/ari_codec.c:1133-1141
     bw_close(w);
     rc_finish(s);
+    return b_left;
+}
+
+// fx/reorder_bitstream_fx.c:16-56: the concealment block [b_left, b_left + block) moves to the front, the bytes before it
+// follow.  In place: a rotation of the first b_left + block bytes, done as three reversals.
+template <class B> LC3_HD void reorder_payload(B bytes, i32 n_pc, i32 b_left)
+{
+    const int block = (n_pc + 1) >> 1, L = b_left + block;
+    auto rev = [&](int lo, int hi) { // [lo, hi)
+        for (hi--; lo < hi; lo++, hi--) { const i32 t = bytes.get(lo); bytes.set(lo, bytes.get(hi)); bytes.set(hi, t); }
+    };
+    rev(0, L); rev(0, block); rev(block, L);
 }
 
 } // namespace lc3k

@@ -1,5 +1,6 @@
 // Frame-parallel passes: one lane encodes the spectral half of one channel-frame.
 #pragma once
+#include "lc3_fec.cuh"
 #include "lc3_stages.cuh"
 #include "lc3_mdct_tile.cuh"
 
@@ -171,10 +172,26 @@ LC3_HD i32 back_body(const LC3K_Batch &b, int f, int tile, int lane, const AriTa
     BackWriter<B> w;
     side_info(w, bytes, total_bits, b.yLen, si, b.fs_idx);
     const i32 rateFlag = s_sub(total_bits, s_add(160, s_imult(b.fs_idx, 160))) > 0 ? 2 << 8 : 0;
-    ari_encode(bytes, w, total_bits, xq, b.yLen, rateFlag, tns, q.lastnz, res, nres, q.lsbMode, lpc_weighting, T, lsbs);
+    // partial concealment only with error protection per channel (fx/enc_lc3.c:247-259)
+    const i32 n_pc = (cfg[CFG_EP] != 0 && (cfg[CFG_EP] >> 8) == 0 && cfg[CFG_N_PCCW] > 0) ? cfg[CFG_N_PC] : 0;
+    const i32 b_left = ari_encode(bytes, w, total_bits, xq, b.yLen, rateFlag, tns, q.lastnz, res, nres, q.lsbMode, lpc_weighting, T,
+                                  lsbs, n_pc);
+    if (n_pc > 0) reorder_payload(bytes, n_pc, b_left);
 
     dst = b.out + b.out_off[li] + (size_t)(b.frame0 + f) * b.out_stride[li];
     return target_bytes;
+}
+
+// ---- error protection of the lane's finished payload, in place in the caller's output (fx/enc_lc3.c:282-312)
+LC3_HD void fec_body(const LC3K_Batch &b, int f, int tile, int lane)
+{
+    const int li = tile * LC3K_LANES + lane;
+    if (li >= b.n_lanes) return;
+    SV<const i32> cfg = slot_view(b.cfg, b.slot[li], CFG_N);
+    const i32 ep = cfg[CFG_EP], slot_bytes = cfg[CFG_SLOT_BYTES];
+    if (ep == 0 || slot_bytes == 0) return; // off, or channel 1 of a jointly coded frame
+    u8 *io = b.out + b.out_off[li] + (size_t)(b.frame0 + f) * b.out_stride[li];
+    fec_encode_slot(ep & 15, (ep >> 4) & 15, io, cfg[CFG_EP_DATA_BYTES], slot_bytes, cfg[CFG_N_PCCW]);
 }
 
 } // namespace lc3k

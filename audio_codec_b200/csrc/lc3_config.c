@@ -75,8 +75,36 @@ int lc3cfg_set_frame_dms(LC3Cfg *c, int dms)
     return E_OK;
 }
 
+/* ---- error-protection sizes (fx/al_fec.c:203-358) */
+static int fec_n_codewords(int slot_bytes) { return (2 * slot_bytes + 14) / 15; }
+static int fec_round16(int32_t v) { return (int)((v + 0x8000) >> 16); } /* round_fx of a value far from saturation */
+static int fec_n_pccw(int slot_bytes, int mode, int ccc)
+{ /* :203-229 */
+    int n = 0;
+    if (mode == 3) n = fec_round16(2 * 2636 * slot_bytes - 117377);
+    else if (mode == 4) n = fec_round16(2 * 2178 * slot_bytes - 129115);
+    return (ccc == 1 || slot_bytes < 80) ? 0 : n;
+}
+static int fec_data_size(int mode, int ccc, int slot_bytes)
+{ /* :288-327 */
+    int p = slot_bytes;
+    if (mode > 0) {
+        p -= mode == 1 ? 1 : (mode - 1) * fec_n_codewords(slot_bytes);
+        p -= (slot_bytes == 40 && mode > 1) ? 2 : 3;
+        if (ccc == 0 && mode > 2 && slot_bytes >= 80) p -= 2;
+    }
+    return p;
+}
+static int fec_n_pc(int mode, int n_pccw, int slot_bytes)
+{ /* :329-358 */
+    if (mode == 1 || slot_bytes < 80) return 0;
+    int n_cw = fec_n_codewords(slot_bytes), pc = n_pccw * -2 * (mode - 1);
+    for (int i = 0; i < n_pccw; i++) pc += (2 * slot_bytes - (n_cw - i - 1) - 1) / n_cw + 1;
+    return pc;
+}
+
 int lc3cfg_set_bitrate(LC3Cfg *c, int bitrate)
-{ /* fx/lc3.c:186-191, fx/setup_enc_lc3.c:130-281 (epmode 0) */
+{ /* fx/lc3.c:186-191, fx/setup_enc_lc3.c:130-281 */
     if (!c) return E_NULL;
     if (bitrate <= 0) return E_BITRATE;
     int minBR = (int)(20 * 8.0 * (10000.0 / c->dms) * (c->fs_in == 44100 ? 441. / 480 : 1));
@@ -86,10 +114,28 @@ int lc3cfg_set_bitrate(LC3Cfg *c, int bitrate)
     if (bitrate < minBR || bitrate > maxBR) return E_BITRATE;
     c->bitrate = bitrate;
     c->br_set = 1;
-    int total = (int)((int32_t)bitrate * c->N / (8 * c->fs_in));
+    const int slot_total = (int)((int32_t)bitrate * c->N / (8 * c->fs_in));
+    c->ccc = c->channels > 1 && c->epmode && bitrate * c->N / (8 * c->fs_in) <= 160;
+    if (c->epmode > 0) {
+        int mb = bitrate * c->N / (8 * c->fs_in * c->channels);
+        if (mb < 40 || mb > 300) return E_BITRATE; /* FEC_SLOT_BYTES_MIN / _MAX, fx/defines.h:146-147 */
+    }
+    int total = c->ccc ? fec_data_size(c->epmode, 1, slot_total) : slot_total;
     for (int ch = 0; ch < c->channels; ch++) {
         int32_t *w = c->ch[ch];
-        int tb = total / c->channels + (ch < (total % c->channels));
+        const int channel_bytes = total / c->channels + (ch < (total % c->channels));
+        int tb = channel_bytes;
+        w[CFG_EP] = c->epmode ? (c->epmode | c->epmr << 4 | c->ccc << 8) : 0;
+        w[CFG_SLOT_BYTES] = 0; w[CFG_EP_DATA_BYTES] = 0; w[CFG_N_PCCW] = 0; w[CFG_N_PC] = 0;
+        if (c->epmode && c->ccc) { /* one slot for the whole frame, coded from channel 0's lane; no partial concealment */
+            if (ch == 0) { w[CFG_SLOT_BYTES] = slot_total; w[CFG_EP_DATA_BYTES] = total; }
+        } else if (c->epmode) {
+            tb = fec_data_size(c->epmode, 0, channel_bytes);
+            w[CFG_SLOT_BYTES] = channel_bytes;
+            w[CFG_EP_DATA_BYTES] = tb;
+            w[CFG_N_PCCW] = fec_n_pccw(channel_bytes, c->epmode, 0);
+            w[CFG_N_PC] = fec_n_pc(c->epmode, w[CFG_N_PCCW], channel_bytes);
+        }
         if (tb < 20 || tb > 435) return E_BITRATE;
         int bits = tb * 8;
         int ti = bits - (38 + 8 + 3 + c->bw_bits) - (17 - norm_s(c->yLen - 1));
@@ -131,6 +177,30 @@ int lc3cfg_set_bandwidth(LC3Cfg *c, int bandwidth)
         }
     }
     return E_OK;
+}
+
+int lc3cfg_set_ep_mode(LC3Cfg *c, int epmode)
+{ /* fx/lc3.c:199-205 */
+    if (!c) return E_NULL;
+    if ((unsigned)epmode > 4) return 9; /* LC3_EPMODE_ERROR */
+    c->epmode = epmode;
+    return c->br_set ? lc3cfg_set_bitrate(c, c->bitrate) : E_OK;
+}
+
+int lc3cfg_set_ep_mode_request(LC3Cfg *c, int epmr)
+{ /* fx/lc3.c:207-213 */
+    if (!c) return E_NULL;
+    if ((unsigned)epmr > 3) return 12; /* LC3_EPMR_ERROR */
+    c->epmr = epmr;
+    for (int ch = 0; ch < c->channels; ch++)
+        if (c->ch[ch][CFG_EP]) c->ch[ch][CFG_EP] = (c->ch[ch][CFG_EP] & ~0xf0) | epmr << 4;
+    return E_OK;
+}
+
+/* fx/enc_lc3.c:279-299: a channel's slot with error protection per channel, else its payload */
+int lc3cfg_out_bytes(const LC3Cfg *c, int ch)
+{
+    return (c->epmode && !c->ccc) ? c->ch[ch][CFG_SLOT_BYTES] : c->ch[ch][CFG_TARGET_BYTES];
 }
 
 int lc3cfg_num_bytes(const LC3Cfg *c) { return c ? (int)((int32_t)c->bitrate * c->N / (8 * c->fs_in)) : 0; }

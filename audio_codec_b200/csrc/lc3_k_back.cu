@@ -84,6 +84,14 @@ __global__ void __launch_bounds__(32 * BACK_WARPS) k_back(LC3K_Batch b)
 }
 LC3_DBG_READER(back)
 
+// error protection of the finished payloads (lc3_fec.cuh), lane per channel-frame, in place in the caller's output
+__global__ void __launch_bounds__(128) k_fec(LC3K_Batch b)
+{
+    const int warp = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (warp >= b.n_frames * b.n_tiles) return;
+    fec_body(b, warp / b.n_tiles, warp % b.n_tiles, lane);
+}
+
 static int done() { return (int)cudaGetLastError(); }
 
 extern "C" int lc3k_launch_quant(const LC3K_Batch *b, void *stream)
@@ -95,6 +103,12 @@ extern "C" int lc3k_launch_quant(const LC3K_Batch *b, void *stream)
         attr_set = true;
     }
     k_quant<<<b->n_frames * b->n_tiles, QT_THREADS, sizeof(QuantSmem), (cudaStream_t)stream>>>(*b);
+    return done();
+}
+extern "C" int lc3k_launch_fec(const LC3K_Batch *b, void *stream)
+{
+    const int warps = b->n_frames * b->n_tiles;
+    k_fec<<<(warps + 3) / 4, 128, 0, (cudaStream_t)stream>>>(*b);
     return done();
 }
 extern "C" int lc3k_launch_back(const LC3K_Batch *b, void *stream)

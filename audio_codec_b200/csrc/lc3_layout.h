@@ -19,7 +19,11 @@
 /* per-slot configuration derived from sample rate / frame size / bitrate (int32 words) */
 enum {
     CFG_TARGET_BYTES = 0, CFG_TOTAL_BITS, CFG_TBITS_INIT, CFG_LPC_WEIGHTING, CFG_LTPF_ENABLE, CFG_QGAIN_OFF,
-    CFG_ATTACK, CFG_BW_CUTOFF_BIN /* 0: no limit */, CFG_BW_INDEX, CFG_N = 12
+    CFG_ATTACK, CFG_BW_CUTOFF_BIN /* 0: no limit */, CFG_BW_INDEX,
+    /* error protection (fx/setup_enc_lc3.c:155-206): CFG_EP = epmode | epmr << 4 | combined channel coding << 8 (0: off);
+     * CFG_SLOT_BYTES = bytes of the channel-coded slot this lane's payload goes into (combined channel coding: the whole
+     * frame on channel 0, 0 on channel 1); CFG_N_PCCW / CFG_N_PC = partial-concealment codewords / nibbles */
+    CFG_EP, CFG_SLOT_BYTES, CFG_EP_DATA_BYTES /* payload bytes that go into the slot */, CFG_N_PCCW, CFG_N_PC, CFG_N = 16
 };
 
 /* per-slot scalar state (int32 words) */
@@ -104,6 +108,7 @@ int lc3k_launch_tns(const LC3K_Batch *b, void *stream);     /* N >= 160 only (no
 int lc3k_launch_rate(const LC3K_Batch *b, void *stream);
 int lc3k_launch_quant(const LC3K_Batch *b, void *stream);   /* gain adjustment + final quantisation, block per tile */
 int lc3k_launch_back(const LC3K_Batch *b, void *stream);
+int lc3k_launch_fec(const LC3K_Batch *b, void *stream);     /* error protection of the finished payloads, in place in the output (only when a lane has CFG_EP) */
 /* set the listed state slots to their power-on values (fx/setup_enc_lc3.c:38-66) */
 int lc3k_launch_reset(int32_t *st32, int16_t *st16, int16_t *hist16, int32_t *hist32, const int32_t *slots, int n, void *stream);
 #ifdef __cplusplus

@@ -13,8 +13,9 @@
  *   - `scratch` is accepted and ignored.
  *   - There is no CPU fallback: every encode call needs a CUDA device and returns LC3_ERROR if the
  *     device path fails.
- *   - Error protection (lc3_enc_set_ep_mode with a mode other than LC3_EP_OFF) is not implemented and
- *     returns LC3_EPMODE_ERROR.
+ *   - Error protection (lc3_enc_set_ep_mode, modes 1-4, and lc3_enc_set_ep_mode_request) is implemented on the
+ *     device as in the reference: payload size reduced to fec_get_data_size, partial-concealment block moved to the
+ *     front (modes 3/4, slots of 80 bytes and more), Reed-Solomon coded slot of lc3_enc_get_num_bytes bytes.
  */
 #ifndef LC3PLUS_B200_H
 #define LC3PLUS_B200_H

@@ -114,6 +114,16 @@ extern "C" int hostsim_set_bitrate(void *p, int bitrate)
     s->cfg.attack_reset[0] = 0;
     return 0;
 }
+extern "C" int hostsim_set_ep(void *p, int epmode, int epmr)
+{ // error protection mode and mode request (lc3_enc_set_ep_mode / _request); call before hostsim_set_bitrate
+    Sim *s = (Sim *)p;
+    int r = lc3cfg_set_ep_mode(&s->cfg, epmode);
+    if (!r) r = lc3cfg_set_ep_mode_request(&s->cfg, epmr);
+    if (!r && s->cfg.br_set)
+        for (int i = 0; i < s->n_slots; i++)
+            for (int k = 0; k < CFG_N; k++) slot_view(s->cfgw.data(), i, CFG_N)[k] = s->cfg.ch[0][k];
+    return r;
+}
 extern "C" int hostsim_frame_len(void *p) { return ((Sim *)p)->cfg.N; }
 extern "C" int hostsim_num_bytes(void *p) { return lc3cfg_num_bytes(&((Sim *)p)->cfg); }
 
@@ -222,6 +232,8 @@ extern "C" int hostsim_encode(void *p, const void *pcm, int bits, int n_frames, 
                 const i32 nb = back_body(b, f, tile, lane, T, LocalBytes{frame}, dst);
                 for (int i = 0; i < nb; i++) dst[i] = frame[i];
             }
+            for (int lane = 0; lane < 32; lane++) fec_body(b, f, tile, lane); // k_fec
+
         }
     return 0;
 }

@@ -19,16 +19,18 @@ def lib():
     L.hostsim_new.restype = C.c_void_p
     L.hostsim_free.argtypes = [C.c_void_p]
     L.hostsim_set_bitrate.argtypes = [C.c_void_p, C.c_int]
+    L.hostsim_set_ep.argtypes = [C.c_void_p, C.c_int, C.c_int]
     L.hostsim_frame_len.argtypes = [C.c_void_p]
     L.hostsim_num_bytes.argtypes = [C.c_void_p]
     L.hostsim_encode.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
     return L
 
 
-def sim_encode(L, fs, dms, schedule, pcm, bits, bfi=None):
-    """schedule: list of (bitrate, n_frames) segments; pcm [S, total*N]"""
+def sim_encode(L, fs, dms, schedule, pcm, bits, bfi=None, ep=(0, 0)):
+    """schedule: list of (bitrate, n_frames) segments; pcm [S, total*N]; ep = (error protection mode, mode request)"""
     S = pcm.shape[0]
     h = C.c_void_p(L.hostsim_new(fs, dms, S))
+    assert L.hostsim_set_ep(h, ep[0], ep[1]) == 0
     outs = []
     pos = 0
     for br, nf in schedule:
@@ -46,9 +48,11 @@ def sim_encode(L, fs, dms, schedule, pcm, bits, bfi=None):
     return outs
 
 
-def oracle_encode(fs, dms, schedule, pcm, bits, bfi=None):
+def oracle_encode(fs, dms, schedule, pcm, bits, bfi=None, ep=(0, 0)):
     outs = []
     encs = [lc3ref.OracleEnc(fs, 1, dms) for _ in range(pcm.shape[0])]
+    for e in encs:
+        assert e.set_ep_mode(ep[0]) == 0 and e.set_ep_mode_request(ep[1]) == 0
     pos = 0
     for br, nf in schedule:
         seg_out = []

@@ -48,6 +48,9 @@ CASES = [
     (32000, 1, 24, "10", 64000, []),
     (48000, 1, 16, "10", 96000, ["-bandwidth", "8000"]),
     (44100, 2, 16, "10", 160000, []),
+    (48000, 1, 16, "10", 128000, ["-epmode", "4"]),     # error protection with partial concealment
+    (48000, 2, 16, "10", 96000, ["-epmode", "3"]),      # both channels in one protected slot
+    (32000, 1, 16, "10", 64000, ["-epmode", "2"]),
 ]
 
 

@@ -202,3 +202,51 @@ def test_transient_rich_signals(fs, dms, br, bits):
     for s in range(pcm.shape[0]):
         want = _oracle(fs, 1, dms, br, bits, pcm[s])
         assert np.array_equal(out[s, :, :want.shape[1]], want), f"stream {s}"
+
+
+def test_error_protection_mixed_batch():
+    """One batch call whose streams use different error-protection modes (and none), mono and stereo, jointly coded and
+    one slot per channel, with partial concealment (slots >= 80 bytes, modes 3/4): every stream equals the oracle
+    (fx/al_fec.c fec_encoder, fx/reorder_bitstream_fx.c, fx/enc_lc3.c:247-312)."""
+    import audio_codec_b200 as ac
+    fs, dms, nf = 48000, 100, 12
+    N = _frame_len(fs, dms)
+    cfgs = [(1, 128000, 0, 0), (1, 128000, 4, 0), (1, 128000, 3, 2), (1, 64000, 4, 1), (1, 48000, 2, 3), (1, 32000, 1, 0),
+            (2, 96000, 3, 0), (2, 128000, 4, 2), (2, 256000, 4, 1), (1, 240000, 3, 3), (1, 240000, 4, 0), (2, 192000, 2, 0)] * 3
+    encs, oras, pcms = [], [], []
+    for i, (ch, br, ep, epmr) in enumerate(cfgs):
+        e, o = ac.Encoder(fs, ch, dms), lc3ref.OracleEnc(fs, ch, dms)
+        assert e.set_ep_mode(ep) == o.set_ep_mode(ep) == 0
+        assert e.set_bitrate(br) == o.set_bitrate(br) == 0
+        assert e.set_ep_mode_request(epmr) == o.set_ep_mode_request(epmr) == 0
+        assert e.num_bytes == o.num_bytes
+        encs.append(e); oras.append(o)
+        pcms.append(make_streams(ch, nf * N, fs, N, 16, first_stream=i, silence_frames=2))
+    stride = 2 * nf * N * 2
+    buf = np.zeros((len(cfgs), stride // 2), dtype=np.int16)
+    for k, p in enumerate(pcms):
+        buf[k, :p.size] = p.reshape(-1)
+    ostride = nf * max(e.num_bytes for e in encs)
+    out = np.zeros((len(cfgs), ostride), dtype=np.uint8)
+    ac.enc_batch(encs, nf, buf, stride, 16, out, ostride)
+    for k, o in enumerate(oras):
+        want = o.encode(pcms[k])
+        assert np.array_equal(out[k, :want.size].reshape(want.shape), want), cfgs[k]
+
+
+def test_error_protection_switching_and_codes():
+    """lc3_enc_set_ep_mode between frames (the -epf switching of fx/codec_exe.c:351-363) and its error returns."""
+    import audio_codec_b200 as ac
+    fs, N = 32000, 320
+    e, o = ac.Encoder(fs, 1, 100, 96000), lc3ref.OracleEnc(fs, 1, 100, 96000)
+    pcm = make_streams(1, 30 * N, fs, N, 16, first_stream=4)
+    for f in range(30):
+        ep = (0, 4, 3, 1, 2, 4)[(f // 2) % 6]
+        assert e.set_ep_mode(ep) == o.set_ep_mode(ep) == 0
+        got = e.enc(pcm[:, f * N:(f + 1) * N])
+        assert np.array_equal(got, o.encode(pcm[:, f * N:(f + 1) * N])[0]), (f, ep)
+    assert e.set_ep_mode(5) == 9 and e.set_ep_mode_request(4) == 12     # LC3_EPMODE_ERROR, LC3_EPMR_ERROR
+    e2 = ac.Encoder(16000, 1, 100)
+    assert e2.set_ep_mode(3) == 0
+    assert e2.set_bitrate(16000, check=False) == 6                     # 20-byte slot is below FEC_SLOT_BYTES_MIN
+    assert e2.set_bitrate(32000) == 0 and e2.num_bytes == 40

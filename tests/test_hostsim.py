@@ -99,3 +99,18 @@ def test_bodies_equal_oracle_on_transient_rich_signals(L, fs, dms, br, bits):
     b = hs.oracle_encode(fs, dms, [(br, nf)], pcm, bits)[0]
     bad = np.argwhere((a != b).any(2))
     assert len(bad) == 0, f"first mismatch (stream, frame) = {bad[0]}"
+
+
+@pytest.mark.parametrize("fs,dms,br", [(48000, 100, 128000), (48000, 100, 64000), (16000, 100, 32000), (48000, 100, 240000),
+                                       (24000, 50, 64000), (48000, 25, 256000), (44100, 100, 128000)])
+def test_bodies_error_protection_equals_oracle(L, fs, dms, br):
+    """EP modes 1-4 (lc3_fec.cuh, the concealment-block tracking in lc3_bits.cuh) against the oracle's lc3o_fec.c."""
+    N = (48000 if fs == 44100 else fs) // 100 * dms // 100
+    nf, S = 10, 5
+    pcm = make_streams(S, nf * N, fs, N, 16, silence_frames=2, first_stream=br // 1000)
+    for ep in (1, 2, 3, 4):
+        epmr = (ep + br // 1000) % 4
+        a = hs.sim_encode(L, fs, dms, [(br, nf)], pcm, 16, ep=(ep, epmr))[0]
+        b = hs.oracle_encode(fs, dms, [(br, nf)], pcm, 16, ep=(ep, epmr))[0]
+        assert a.shape == b.shape
+        assert np.array_equal(a, b), (ep, epmr, np.where((a != b).any(axis=2)))
