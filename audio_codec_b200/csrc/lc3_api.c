@@ -321,7 +321,7 @@ static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_
          * the staged samples, so it is issued right behind the FIR on `par` and runs beside the per-stream high-pass and
          * pitch passes on `ser`; SNS then waits for both (it takes the attack flag from the pitch pass).  Otherwise (24-bit
          * input: the block exponent comes from the pitch pass; short frames: one fused front-end kernel) it is a chain. */
-        const int split = bits == 16 && N >= 160;
+        const int split = bits == 16 && N >= 160 && !getenv("LC3PLUS_B200_CHAIN"); /* the variable forces the chain: per-kernel timing (tools/kernel_ms.py) */
         static const int order_chain[N_KERNELS] = {K_STAGE, K_FIR, K_SCALAR, K_PITCH, K_FRONT, K_SNS, K_TNS, K_RATE, K_QUANT, K_BACK};
         static const int order_split[N_KERNELS] = {K_STAGE, K_FIR, K_FRONT, K_SCALAR, K_PITCH, K_SNS, K_TNS, K_RATE, K_QUANT, K_BACK};
         /* producers on the OTHER stream that kernel k must wait for (same-stream producers are ordered by the stream) */

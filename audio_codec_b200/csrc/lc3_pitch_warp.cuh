@@ -580,20 +580,79 @@ LC3_HD void fir_warp_body(const LC3K_Batch &b, int li, int f, FirShared &sh, con
         for (int i = l - rl; i < N; i += 32) sh.xs[64 + i] = (i16)raw(i);
     LC3_LANES_END
     SV<i16> r = tile_view(b.r12, frame_tile(b, f, tile), 128, tl);
+    // (see pitch_warp_body phase B for why plain arithmetic is exact.)  A lane owns outputs l, l + 32, l + 64, l + 96: the
+    // up-sampling factor (2, 4 or 8) divides 32 * off_frac, so they share one polyphase branch and every coefficient is
+    // fetched once for up to four products -- the pass is bound by shared-memory loads, not by the multiplies.
     LC3_LANES(l)
-        for (int n = l; n < len; n += 32) { // see pitch_warp_body phase B for why plain arithmetic is exact
-            const int t = n * off_frac, ii = 1 + n * off_int + t / upfac - rl, fr = t % upfac;
-            const i16 *co = &filt[fr * delay2], *in = &sh.xs[64 + ii];
-            i32 acc = 0;
-            for (int m = 0; m < delay2; m++) acc += in[m] * co[m];
-            r[n] = (i16)l_round(acc);
+        const int nq = len >> 5; // 1, 2 or 4 outputs per lane
+        const int t0 = l * off_frac, fr = t0 % upfac;
+        const i16 *co = &filt[fr * delay2];
+        const i16 *in0 = &sh.xs[64 + 1 + l * off_int + t0 / upfac - rl];
+        const int step = 32 * off_int + (32 * off_frac) / upfac; // input distance between two outputs of the lane
+        if (nq == 4) {
+            const i16 *in1 = in0 + step, *in2 = in1 + step, *in3 = in2 + step;
+            i32 a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+            for (int m = 0; m < delay2; m++) { const i32 c = co[m]; a0 += in0[m] * c; a1 += in1[m] * c; a2 += in2[m] * c; a3 += in3[m] * c; }
+            r[l] = (i16)l_round(a0); r[l + 32] = (i16)l_round(a1); r[l + 64] = (i16)l_round(a2); r[l + 96] = (i16)l_round(a3);
+        } else {
+            for (int q = 0; q < nq; q++) {
+                const i16 *in = in0 + q * step;
+                i32 acc = 0;
+                for (int m = 0; m < delay2; m++) acc += in[m] * co[m];
+                r[l + 32 * q] = (i16)l_round(acc);
+            }
         }
     LC3_LANES_END
 }
 
 // ---- the 50 Hz high-pass as its own pass (16-bit input): ONE LANE PER CHANNEL-STREAM walks the frames in order
 // through the recursion (resamp12k8_fx.c:88-104), in place on b.r12.  It is the one part of the time-domain chain
-// with no parallelism inside a stream; with a lane per stream it costs one warp instruction per 32 streams.
+// with no parallelism inside a stream; with a lane per stream it costs one warp instruction per 32 streams, and its run
+// time is the length of the dependent chain per sample.  So (i) the recursion runs on plain wrapping additions -- five
+// dependent instructions per sample instead of the saturating operators' thirteen -- with every addition's overflow
+// condition collected off the chain; a frame in which any addition overflowed (none does on ordinary signals) is run
+// again from its saved state with the saturating operators, so the result is the reference's in every case; (ii) the
+// next frame's samples are fetched while the current frame's chain runs.
+struct Hp50 { i32 n0, n1, n2, d0, d1; };
+
+// one frame with the reference's operators
+LC3_HD void hp50_frame_sat(const Hp50 &c, const i16 *in, i16 *out, int len, i32 &m0, i32 &m1)
+{
+    for (int n = 0; n < len; n++) {
+        const i32 v = in[n];
+        const i32 o = l_mac0(m0, c.n0, v);
+        const i32 t = l_mac0(mpy32x16k(o, c.d0), c.n1, v);
+        m0 = l_add(m1, l_shl_p(t, 1));
+        m1 = l_mac0(mpy32x16k(o, c.d1), c.n2, v);
+        out[n] = (i16)l_round(o);
+    }
+}
+
+// sixteen samples on wrapping additions; returns the accumulated overflow conditions in the sign bit
+LC3_HD u32 hp50_run16(const Hp50 &c, const i16 *in, i16 *out, i32 &m0_, i32 &m1_)
+{
+    u32 m0 = (u32)m0_, m1 = (u32)m1_, ovf = 0;
+#pragma unroll
+    for (int n = 0; n < 16; n++) {
+        const i32 v = in[n];
+        const u32 p0 = (u32)(c.n0 * v), p1 = (u32)(c.n1 * v), p2 = (u32)(c.n2 * v);
+        const u32 o = m0 + p0;
+        ovf |= (m0 ^ o) & (p0 ^ o);
+        const u32 x0 = (u32)mpy32x16k((i32)o, c.d0), t = x0 + p1;
+        ovf |= (x0 ^ t) & (p1 ^ t);
+        const u32 t2 = t << 1;
+        ovf |= t ^ t2;
+        const u32 a0 = m1 + t2;
+        ovf |= (m1 ^ a0) & (t2 ^ a0);
+        const u32 x1 = (u32)mpy32x16k((i32)o, c.d1), a1 = x1 + p2;
+        ovf |= (x1 ^ a1) & (p2 ^ a1);
+        m0 = a0; m1 = a1;
+        out[n] = (i16)l_round((i32)o);
+    }
+    m0_ = (i32)m0; m1_ = (i32)m1;
+    return ovf;
+}
+
 LC3_HD void scalar_body(const LC3K_Batch &b, int tile, int lane)
 {
     const int li = tile * LC3K_LANES + lane;
@@ -601,25 +660,32 @@ LC3_HD void scalar_body(const LC3K_Batch &b, int tile, int lane)
     SV<i32> st = slot_view(b.st32, b.slot[li], ST32_N);
     const int len = 32 * (b.dms / 25);
     i32 m0 = st[ST_MEM50_0], m1 = st[ST_MEM50_1];
-    const i32 n0 = rom_hp50_num[0], n1 = rom_hp50_num[1], n2 = rom_hp50_num[2], d0 = rom_hp50_den[0], d1 = rom_hp50_den[1];
+    const Hp50 c = {rom_hp50_num[0], rom_hp50_num[1], rom_hp50_num[2], rom_hp50_den[0], rom_hp50_den[1]};
+    i16 bufs[2][128], res[128];
+    {
+        SV<i16> r = tile_view(b.r12, frame_tile(b, 0, tile), 128, lane);
+#pragma unroll 16
+        for (int n = 0; n < len; n++) bufs[0][n] = r[n];
+    }
     for (int f = 0; f < b.n_frames; f++) {
+        const i16 *cur = bufs[f & 1];
+        i16 *nxt = bufs[(f + 1) & 1];
         SV<i16> r = tile_view(b.r12, frame_tile(b, f, tile), 128, lane);
-        // fetch the frame first (independent loads), then run the recursion from registers/local memory: with one
-        // warp per 32 streams this pass is latency-bound and a load inside the recursion would serialise with it
-        i16 buf[128];
-#pragma unroll 16
-        for (int n = 0; n < len; n++) buf[n] = r[n];
-#pragma unroll 4
-        for (int n = 0; n < len; n++) {
-            const i32 v = buf[n];
-            const i32 o = l_mac0(m0, n0, v);
-            const i32 t = l_mac0(mpy32x16k(o, d0), n1, v);
-            m0 = l_add(m1, l_shl_p(t, 1));
-            m1 = l_mac0(mpy32x16k(o, d1), n2, v);
-            buf[n] = (i16)l_round(o);
+        const bool more = f + 1 < b.n_frames;
+        SV<i16> rn = tile_view(b.r12, frame_tile(b, more ? f + 1 : f, tile), 128, lane);
+        const i32 s0 = m0, s1 = m1;
+        u32 ovf = 0;
+        for (int n0 = 0; n0 < len; n0 += 16) {
+            i16 pre[16];
+#pragma unroll
+            for (int j = 0; j < 16; j++) pre[j] = rn[n0 + j]; // next frame, in flight during the chain below
+            ovf |= hp50_run16(c, cur + n0, res + n0, m0, m1);
+#pragma unroll
+            for (int j = 0; j < 16; j++) nxt[n0 + j] = pre[j];
         }
+        if ((i32)ovf < 0) { m0 = s0; m1 = s1; hp50_frame_sat(c, cur, res, len, m0, m1); }
 #pragma unroll 16
-        for (int n = 0; n < len; n++) r[n] = buf[n];
+        for (int n = 0; n < len; n++) r[n] = res[n];
     }
     st[ST_MEM50_0] = m0; st[ST_MEM50_1] = m1;
 }

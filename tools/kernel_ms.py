@@ -8,6 +8,8 @@ import json
 import os
 import sys
 
+os.environ.setdefault("LC3PLUS_B200_CHAIN", "1")  # kernels of the chunk strictly one after the other
+
 import numpy as np
 import torch
 
