@@ -96,12 +96,27 @@ template <int N, int BITS> LC3_HD void mt_fold(const LC3K_Batch &b, int f, int t
         PcmView<BITS> xs = pcm_view<BITS>(b, tile, lane, f, x_exp);
         const i16 *win = &rom_win[b.W_off];
         const int memLen = b.mdct_mem_len, z = 2 * N - b.W_len;
-        for (int i = part; i < m; i += G::PARTS) { // same three expressions as mdct_frame()
-            i32 v = xs(i - memLen) * win[i] - xs(2 * m - 1 - i - memLen) * win[2 * m - 1 - i];
-            y[mt_ridx(m + i)] = v; range_add(rg, v);
-            if (i < z) v = xs(2 * m - memLen + i) * win[2 * m + i];
-            else v = xs(2 * m - memLen + i) * win[2 * m + i] + xs(4 * m - memLen - 1 - i) * win[4 * m - 1 - i];
-            y[mt_ridx(m - 1 - i)] = v; range_add(rg, v);
+        // same three expressions as mdct_frame(); five outputs pairs at a time with all their samples fetched first
+        // (twenty independent loads in flight per thread: this phase waits on global memory, not on arithmetic)
+        constexpr int U = 5;
+        static_assert((m / G::PARTS) % U == 0 && m % G::PARTS == 0, "fold unroll");
+        for (int i0 = part; i0 < m; i0 += U * G::PARTS) {
+            i32 xa[U], xb[U], xc[U], xd[U];
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                const int i = i0 + u * G::PARTS;
+                xa[u] = xs(i - memLen); xb[u] = xs(2 * m - 1 - i - memLen); xc[u] = xs(2 * m - memLen + i);
+                xd[u] = i < z ? 0 : xs(4 * m - memLen - 1 - i); // the window is zero there (la_zeroes)
+            }
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                const int i = i0 + u * G::PARTS;
+                i32 v = xa[u] * win[i] - xb[u] * win[2 * m - 1 - i];
+                y[mt_ridx(m + i)] = v; range_add(rg, v);
+                v = xc[u] * win[2 * m + i];
+                if (i >= z) v += xd[u] * win[4 * m - 1 - i];
+                y[mt_ridx(m - 1 - i)] = v; range_add(rg, v);
+            }
         }
     } else {
         for (int i = part; i < N; i += G::PARTS) y[mt_ridx(i)] = 0;

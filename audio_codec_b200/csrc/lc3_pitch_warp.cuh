@@ -628,12 +628,13 @@ LC3_HD void hp50_frame_sat(const Hp50 &c, const i16 *in, i16 *out, int len, i32 
     }
 }
 
-// sixteen samples on wrapping additions; returns the accumulated overflow conditions in the sign bit
-LC3_HD u32 hp50_run16(const Hp50 &c, const i16 *in, i16 *out, i32 &m0_, i32 &m1_)
+// HP50_BLOCK samples on wrapping additions; returns the accumulated overflow conditions in the sign bit
+constexpr int HP50_BLOCK = 32; // long enough for the chain of one block to cover the latency of the next frame's loads
+LC3_HD u32 hp50_run(const Hp50 &c, const i16 *in, i16 *out, i32 &m0_, i32 &m1_)
 {
     u32 m0 = (u32)m0_, m1 = (u32)m1_, ovf = 0;
 #pragma unroll
-    for (int n = 0; n < 16; n++) {
+    for (int n = 0; n < HP50_BLOCK; n++) {
         const i32 v = in[n];
         const u32 p0 = (u32)(c.n0 * v), p1 = (u32)(c.n1 * v), p2 = (u32)(c.n2 * v);
         const u32 o = m0 + p0;
@@ -675,13 +676,13 @@ LC3_HD void scalar_body(const LC3K_Batch &b, int tile, int lane)
         SV<i16> rn = tile_view(b.r12, frame_tile(b, more ? f + 1 : f, tile), 128, lane);
         const i32 s0 = m0, s1 = m1;
         u32 ovf = 0;
-        for (int n0 = 0; n0 < len; n0 += 16) {
-            i16 pre[16];
+        for (int n0 = 0; n0 < len; n0 += HP50_BLOCK) {
+            i16 pre[HP50_BLOCK];
 #pragma unroll
-            for (int j = 0; j < 16; j++) pre[j] = rn[n0 + j]; // next frame, in flight during the chain below
-            ovf |= hp50_run16(c, cur + n0, res + n0, m0, m1);
+            for (int j = 0; j < HP50_BLOCK; j++) pre[j] = rn[n0 + j]; // next frame, in flight during the chain below
+            ovf |= hp50_run(c, cur + n0, res + n0, m0, m1);
 #pragma unroll
-            for (int j = 0; j < 16; j++) nxt[n0 + j] = pre[j];
+            for (int j = 0; j < HP50_BLOCK; j++) nxt[n0 + j] = pre[j];
         }
         if ((i32)ovf < 0) { m0 = s0; m1 = s1; hp50_frame_sat(c, cur, res, len, m0, m1); }
 #pragma unroll 16
