@@ -31,6 +31,12 @@ template <class B> LC3_HD void put_bits(BackWriter<B> &w, i32 v, int n)
     bw_flush(w);
 }
 template <class B> LC3_HD void put_bit(BackWriter<B> &w, i32 bit) { put_bits(w, bit > 0 ? 1 : 0, 1); }
+template <class B> LC3_HD void put_bits8(BackWriter<B> &w, i32 v, int n)
+{ // n <= 8 and fewer than 8 bits pending: at most one byte leaves, no loop
+    w.acc |= ((u32)v & ((1u << n) - 1u)) << w.n;
+    w.n += n;
+    if (w.n >= 8) { w.buf.set(w.bp, (i32)(w.acc & 0xffu)); w.bp--; w.acc >>= 8; w.n -= 8; }
+}
 template <class B> LC3_HD void bw_close(BackWriter<B> &w)
 {
     if (w.n > 0) w.buf.set(w.bp, w.buf.get(w.bp) | (i32)(w.acc & 0xffu));
@@ -129,7 +135,7 @@ LC3_HD u32 add24(u32 a, u32 b, int &wrap)
     wrap = r < x;
     return r >> 8;
 }
-template <class B> LC3_HD void rc_encode(RangeCoder<B> &s, u32 cum, u32 freq, PcTrack &pc, const BackWriter<B> &w)
+template <bool PC, class B> LC3_HD void rc_encode(RangeCoder<B> &s, u32 cum, u32 freq, PcTrack &pc, const BackWriter<B> &w)
 { // fx/ari_codec.c:1408-1446
     u32 r = s.range >> 10;
     int carry;
@@ -139,7 +145,7 @@ template <class B> LC3_HD void rc_encode(RangeCoder<B> &s, u32 cum, u32 freq, Pc
     while (s.range < (1u << 16)) {
         s.range <<= 8;
         rc_shift(s);
-        if (pc.bytes > 0) pc_from_left(pc, w); // the decoder shifts a byte in for every byte shifted out here
+        if (PC && pc.bytes > 0) pc_from_left(pc, w); // the decoder shifts a byte in for every byte shifted out here
     }
 }
 template <class B> LC3_HD void put_fwd(B p, i32 bp, i32 v, int n)
@@ -194,13 +200,14 @@ LC3_HD i32 res_bit(const u32 *res, int i) { return (i32)((res[i >> 5] >> (i & 31
 // their tuples look like; only the short "fetch the next tuple" block is predicated.  The forward (range coder) and
 // backward (bits) streams are independent, so only the order inside each stream has to match the reference, and it does:
 // per tuple, bit planes in rising level, then the signs.
-// n_pc > 0 (partial concealment, see PcTrack): returns the first byte of the concealment block, else -1.
-template <class B, class XQ>
+// n_pc > 0 (partial concealment, see PcTrack): returns the first byte of the concealment block, else -1.  PC = false
+// compiles the tracking out (the caller picks it when no lane of the warp needs it).
+template <bool PC, class B, class XQ>
 LC3_HD i32 ari_encode(B bytes, BackWriter<B> &w, i32 nbbits, XQ xq, int nt, i32 rateFlag, const TnsOut &tns, i32 lastnz,
                       const u32 *res, i32 nres, i32 lsbMode, int lpc_weighting, const AriTabs &T, u32 *lsbs, i32 n_pc)
 {
-    PcTrack pc = {(n_pc + 1) >> 1, 0, -1};
-    if (pc.bytes > 0) for (int i = 0; i < 3; i++) pc_from_left(pc, w); // ac_dec_init_fx, fx/ari_codec.c:1559-1580
+    PcTrack pc = {PC ? (n_pc + 1) >> 1 : 0, 0, -1};
+    if (PC && pc.bytes > 0) for (int i = 0; i < 3; i++) pc_from_left(pc, w); // ac_dec_init_fx, fx/ari_codec.c:1559-1580
     int nlsbs = 0;
     u32 lword = 0;
     auto push_lsb = [&](i32 b) {
@@ -213,10 +220,10 @@ LC3_HD i32 ari_encode(B bytes, BackWriter<B> &w, i32 nbbits, XQ xq, int nt, i32 
     for (int n = 0; n < tns.nfilt; n++) {
         if (tns.order[n] <= 0) continue;
         const int o = tns.order[n] - 1;
-        rc_encode(s, (u32)rom_tns_order_cumfreq[lpc_weighting * 8 + o], (u32)rom_tns_order_freq[lpc_weighting * 8 + o], pc, w);
+        rc_encode<PC>(s, (u32)rom_tns_order_cumfreq[lpc_weighting * 8 + o], (u32)rom_tns_order_freq[lpc_weighting * 8 + o], pc, w);
         for (int k = 0; k < tns.order[n]; k++) {
             const int ix = k * 17 + tns.idx[8 * n + k];
-            rc_encode(s, (u32)rom_tns_coef_cumfreq[ix], (u32)rom_tns_coef_freq[ix], pc, w);
+            rc_encode<PC>(s, (u32)rom_tns_coef_cumfreq[ix], (u32)rom_tns_coef_freq[ix], pc, w);
         }
     }
 
@@ -248,30 +255,28 @@ LC3_HD i32 ari_encode(B bytes, BackWriter<B> &w, i32 nbbits, XQ xq, int nt, i32 
         {
             const int row = T.lut[ctx + rom_ari_esc_nb[l < 3 ? l : 3]] * 17 + (last ? msb : 16);
             const u32 cf = T.cf[row];
-            rc_encode(s, cf & 0xffffu, cf >> 16, pc, w);
+            rc_encode<PC>(s, cf & 0xffffu, cf >> 16, pc, w);
         }
-        if (!last) { // bit plane l of both magnitudes
-            const i32 ta = (a1 >> l) & 1, tb = (b1 >> l) & 1;
-            if (lsbMode != 0 && l == 0) { // lowest plane diverted to lsbs[]; a value that is +-1 takes its sign along
-                const i32 am = a1 >> 1, bm = b1 >> 1;
-                push_lsb(ta);
-                if (am == 0 && ta > 0) push_lsb(a < 0 ? 1 : 0);
-                push_lsb(tb);
-                if (bm == 0 && tb > 0) push_lsb(b < 0 ? 1 : 0);
-            } else {
-                if (pc.bytes > 0) pc_from_right(pc, w, 2);
-                put_bits(w, ta | (tb << 1), 2);
-            }
-            l++;
-        } else { // signs of the values whose sign has not gone with a diverted LSB
-            const bool div = lsbMode != 0 && lev > 0;
-            const i32 sa = (div ? (a1 >> 1) : a1) != 0, sb = (div ? (b1 >> 1) : b1) != 0;
-            const i32 na_ = (a >> 15) & 1, nb_ = (b >> 15) & 1;
-            if (pc.bytes > 0) pc_from_right(pc, w, sa + sb);
-            put_bits(w, sa ? (na_ | (nb_ << 1)) : nb_, sa + sb);
-            k += 2;
-            l = 0;
+        // side bits of this iteration, without branching on `last`: bit plane l of both magnitudes after an escape, the
+        // signs after the MSB symbol (of the values whose sign has not gone with a diverted LSB)
+        const i32 ta = (a1 >> l) & 1, tb = (b1 >> l) & 1;
+        const bool div0 = lsbMode != 0 && l == 0 && !last;
+        if (div0) { // lowest plane diverted to lsbs[]; a value that is +-1 takes its sign along
+            const i32 am = a1 >> 1, bm = b1 >> 1;
+            push_lsb(ta);
+            if (am == 0 && ta > 0) push_lsb(a < 0 ? 1 : 0);
+            push_lsb(tb);
+            if (bm == 0 && tb > 0) push_lsb(b < 0 ? 1 : 0);
         }
+        const bool dv = lsbMode != 0 && lev > 0;
+        const i32 sa = (dv ? (a1 >> 1) : a1) != 0, sb = (dv ? (b1 >> 1) : b1) != 0;
+        const i32 na_ = (a >> 15) & 1, nb_ = (b >> 15) & 1;
+        const i32 v = last ? (sa ? (na_ | (nb_ << 1)) : nb_) : (ta | (tb << 1));
+        const int cnt = last ? sa + sb : (div0 ? 0 : 2);
+        if (PC && pc.bytes > 0) pc_from_right(pc, w, cnt);
+        put_bits8(w, v, cnt);
+        k += last ? 2 : 0;
+        l = last ? 0 : l + 1;
     }
     if (nlsbs & 31) lsbs[nlsbs >> 5] = lword;
 
@@ -287,8 +292,8 @@ LC3_HD i32 ari_encode(B bytes, BackWriter<B> &w, i32 nbbits, XQ xq, int nt, i32 
     for (int i = 0; i < m; i += 8) { // eight at a time
         const int cnt = imin(8, m - i);
         const u32 v = src[i >> 5] >> (i & 31); // i is a multiple of 8: the group never straddles two words
-        if (pc.bytes > 0) pc_from_right(pc, w, cnt);
-        put_bits(w, (i32)(v & 0xffu), cnt);
+        if (PC && pc.bytes > 0) pc_from_right(pc, w, cnt);
+        put_bits8(w, (i32)(v & 0xffu), cnt);
     }
     const i32 b_left = pc.bytes <= 0 ? -1 : (pc.b_left >= 0 ? pc.b_left : w.bp - pc.bytes); // fx/ari_codec.c:1133-1141
     bw_close(w);

@@ -174,8 +174,15 @@ LC3_HD i32 back_body(const LC3K_Batch &b, int f, int tile, int lane, const AriTa
     const i32 rateFlag = s_sub(total_bits, s_add(160, s_imult(b.fs_idx, 160))) > 0 ? 2 << 8 : 0;
     // partial concealment only with error protection per channel (fx/enc_lc3.c:247-259)
     const i32 n_pc = (cfg[CFG_EP] != 0 && (cfg[CFG_EP] >> 8) == 0 && cfg[CFG_N_PCCW] > 0) ? cfg[CFG_N_PC] : 0;
-    const i32 b_left = ari_encode(bytes, w, total_bits, xq, b.yLen, rateFlag, tns, q.lastnz, res, nres, q.lsbMode, lpc_weighting, T,
-                                  lsbs, n_pc);
+#if defined(__CUDA_ARCH__)
+    const bool any_pc = __any_sync(__activemask(), n_pc > 0);
+#else
+    const bool any_pc = n_pc > 0;
+#endif
+    const i32 b_left = any_pc ? ari_encode<true>(bytes, w, total_bits, xq, b.yLen, rateFlag, tns, q.lastnz, res, nres, q.lsbMode,
+                                                 lpc_weighting, T, lsbs, n_pc)
+                              : ari_encode<false>(bytes, w, total_bits, xq, b.yLen, rateFlag, tns, q.lastnz, res, nres, q.lsbMode,
+                                                  lpc_weighting, T, lsbs, 0);
     if (n_pc > 0) reorder_payload(bytes, n_pc, b_left);
 
     dst = b.out + b.out_off[li] + (size_t)(b.frame0 + f) * b.out_stride[li];
