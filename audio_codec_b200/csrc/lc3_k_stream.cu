@@ -54,13 +54,17 @@ template <class T> __global__ void __launch_bounds__(256) k_stage(LC3K_Batch b)
 // per-stream passes: one warp per channel-stream.  14 warps per block, 2 blocks per SM: 28 x 148 = 4144 streams are
 // resident at once (the 4096-stream workload runs in one wave), and the warps of a block share instruction fetches.
 #define PITCH_WARPS 14
+#ifndef PITCH_FRAME_SYNC
+#define PITCH_FRAME_SYNC 1
+#endif
 template <int BITS, bool PRE> __global__ void __launch_bounds__(32 * PITCH_WARPS, 2) k_pitch(LC3K_Batch b)
 {
     extern __shared__ __align__(16) unsigned char pitch_smem[];
     PitchShared *sh = reinterpret_cast<PitchShared *>(pitch_smem);
     const int w = threadIdx.x >> 5;
     LC3_DBG_ENTER(0, (int)blockIdx.x * PITCH_WARPS + w);
-    pitch_warp_body<BITS, PRE>(b, blockIdx.x * PITCH_WARPS + w, sh[w]);
+    const int live = min(PITCH_WARPS, b.n_lanes - (int)blockIdx.x * PITCH_WARPS); // warps of this block that own a stream
+    pitch_warp_body<BITS, PRE>(b, blockIdx.x * PITCH_WARPS + w, sh[w], PITCH_FRAME_SYNC ? 32 * live : 0);
     LC3_DBG_LEAVE();
 }
 
@@ -80,17 +84,22 @@ __global__ void __launch_bounds__(128) k_fir(LC3K_Batch b)
 // scalar recursions (high-pass, attack detector): one lane per channel-stream
 __global__ void __launch_bounds__(32) k_scalar(LC3K_Batch b) { scalar_body(b, blockIdx.x, threadIdx.x); }
 
-__global__ void __launch_bounds__(128, 7) k_rate(LC3K_Batch b)
+// rate loop: one warp per channel-stream, like k_pitch; the block's warps meet before every frame (shared instruction fetches)
+#ifndef RATE_WARPS
+#define RATE_WARPS 14
+#endif
+__global__ void __launch_bounds__(32 * RATE_WARPS, 896 / (32 * RATE_WARPS)) k_rate(LC3K_Batch b)
 {
-    __shared__ RateShared sh[4];
+    __shared__ RateShared sh[RATE_WARPS];
     __shared__ u8 lut[4096];
     __shared__ uint16_t bits[1088];
-    for (int i = threadIdx.x; i < 4096; i += 128) lut[i] = (u8)rom_ari_lookup[i];
-    for (int i = threadIdx.x; i < 1088; i += 128) bits[i] = rom_ari_bits[i];
+    for (int i = threadIdx.x; i < 4096; i += 32 * RATE_WARPS) lut[i] = (u8)rom_ari_lookup[i];
+    for (int i = threadIdx.x; i < 1088; i += 32 * RATE_WARPS) bits[i] = rom_ari_bits[i];
     __syncthreads();
     const int w = threadIdx.x >> 5;
-    LC3_DBG_ENTER(1, (int)blockIdx.x * 4 + w);
-    rate_warp_body(b, blockIdx.x * 4 + w, sh[w], lut, bits);
+    LC3_DBG_ENTER(1, (int)blockIdx.x * RATE_WARPS + w);
+    const int live = min(RATE_WARPS, b.n_lanes - (int)blockIdx.x * RATE_WARPS);
+    rate_warp_body(b, blockIdx.x * RATE_WARPS + w, sh[w], lut, bits, 32 * live);
     LC3_DBG_LEAVE();
 }
 LC3_DBG_READER(stream)
@@ -156,6 +165,6 @@ extern "C" int lc3k_launch_pitch(const LC3K_Batch *b, void *stream)
 }
 extern "C" int lc3k_launch_rate(const LC3K_Batch *b, void *stream)
 {
-    k_rate<<<(b->n_lanes + 3) / 4, 128, 0, (cudaStream_t)stream>>>(*b);
+    k_rate<<<(b->n_lanes + RATE_WARPS - 1) / RATE_WARPS, 32 * RATE_WARPS, 0, (cudaStream_t)stream>>>(*b);
     return done();
 }

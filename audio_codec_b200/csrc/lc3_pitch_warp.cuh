@@ -45,7 +45,14 @@ template <class T> struct RawPcm {
 // run in their own passes (fir_warp_body, scalar_body below) and b.r12 holds the high-passed 12.8 kHz samples;
 // this body then does the pitch analysis only.  PRE = false: everything in one pass (24-bit input, whose block
 // exponent depends on the filter state and therefore cannot be split).
-template <int BITS, bool PRE> LC3_HD void pitch_warp_body(const LC3K_Batch &b, int li, PitchShared &sh)
+// sync_threads > 0 (kernel only): the block's active warps meet at a barrier before every frame, so that they walk the
+// (instruction-cache sized) body together and share its fetches.
+#if defined(__CUDA_ARCH__)
+#define LC3_PITCH_SYNC() do { if (sync_threads > 0) asm volatile("bar.sync 1, %0;" ::"r"(sync_threads) : "memory"); } while (0)
+#else
+#define LC3_PITCH_SYNC() do { } while (0)
+#endif
+template <int BITS, bool PRE> LC3_HD void pitch_warp_body(const LC3K_Batch &b, int li, PitchShared &sh, int sync_threads = 0)
 {
     typedef typename std::conditional<BITS == 16, i16, i32>::type T;
     if (li >= b.n_lanes) return;
@@ -88,6 +95,7 @@ template <int BITS, bool PRE> LC3_HD void pitch_warp_body(const LC3K_Batch &b, i
     raw.hist = tile_view((const T *)b.pcm_t, (size_t)tile, (size_t)(b.n_frames + 1) * N, tl);
 
     for (int f = 0; f < b.n_frames; f++) {
+        LC3_PITCH_SYNC();
         raw.cur = (const T *)b.pcm + b.pcm_off[li] + (size_t)(b.frame0 + f) * N;
         raw.first = f == 0;
 

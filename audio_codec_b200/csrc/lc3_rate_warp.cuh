@@ -20,7 +20,9 @@ struct RateShared {
     u8 tv[LC3K_MAX_N / 2 + 2];   // magnitude class of each tuple, offset by 2 (tv[0] = tv[1] = 0)
 };
 
-LC3_HD void rate_warp_body(const LC3K_Batch &b, int li, RateShared &sh, const u8 *ari_lut, const uint16_t *ari_bitstab)
+// sync_threads > 0 (kernel only): the block's active warps meet at a barrier before every frame (see pitch_warp_body)
+LC3_HD void rate_warp_body(const LC3K_Batch &b, int li, RateShared &sh, const u8 *ari_lut, const uint16_t *ari_bitstab,
+                           int sync_threads = 0)
 {
     if (li >= b.n_lanes) return;
     const int tile = li >> 5, tl = li & 31;
@@ -33,6 +35,9 @@ LC3_HD void rate_warp_body(const LC3K_Batch &b, int li, RateShared &sh, const u8
     const i32 rateFlag = s_sub(total_bits, s_add(160, s_imult(b.fs_idx, 160))) > 0 ? 2 << 8 : 0;
 
     for (int f = 0; f < b.n_frames; f++) {
+#if defined(__CUDA_ARCH__)
+        if (sync_threads > 0) asm volatile("bar.sync 1, %0;" ::"r"(sync_threads) : "memory");
+#endif
         const size_t ft = frame_tile(b, f, tile);
         SV<const i32> fo = tile_view((const i32 *)b.fout, ft, FO_N, tl);
         SV<const i32> po = tile_view((const i32 *)b.pout, ft, PO_N, tl);
