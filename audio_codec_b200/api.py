@@ -175,10 +175,23 @@ def _addr(x):
     return x.ctypes.data if isinstance(x, np.ndarray) else int(x)
 
 
+class EncoderArray:
+    """The `LC3_Enc *const *encoders` argument of lc3plus_enc_batch, built once for a fixed set of encoders (a C caller
+    keeps such an array anyway; building it from a Python list costs about 0.1 us per encoder per call)."""
+
+    def __init__(self, encoders):
+        self.encoders = list(encoders)  # keeps the Encoder objects (and their handle blocks) alive
+        self.arr = (C.c_void_p * len(self.encoders))(*[e.h.value for e in self.encoders])
+
+    def __len__(self):
+        return len(self.encoders)
+
+
 def enc_batch(encoders, n_frames, pcm, stream_stride_bytes, bits, out, out_stream_stride_bytes, num_bytes=None):
-    """lc3plus_enc_batch.  pcm/out: numpy arrays or device addresses.  num_bytes: optional int32 array [S*n_frames]."""
+    """lc3plus_enc_batch.  encoders: list of Encoder or an EncoderArray.  pcm/out: numpy arrays or device addresses.
+    num_bytes: optional int32 array [S*n_frames]."""
     L = load_library()
-    arr = (C.c_void_p * len(encoders))(*[e.h.value for e in encoders])
+    arr = encoders.arr if isinstance(encoders, EncoderArray) else (C.c_void_p * len(encoders))(*[e.h.value for e in encoders])
     nb = num_bytes.ctypes.data if num_bytes is not None else None
     r = L.lc3plus_enc_batch(arr, len(encoders), n_frames, _addr(pcm), stream_stride_bytes, bits, _addr(out),
                             out_stream_stride_bytes, nb)

@@ -48,6 +48,10 @@ typedef struct {
         cudaEvent_t state_ev[N_KERNELS], hop_ev[N_KERNELS + 2], done_ev;
     } pipe[N_PIPES];
     cudaEvent_t start_ev, end_ev;
+    /* host-pointer calls: the chunks' input copies queue on one stream and their output copies on another, so that the
+     * input of chunk c+1 streams in while chunk c computes, whatever the pipes' own streams are busy with */
+    cudaStream_t h2d, d2h;
+    cudaEvent_t d2h_ev;
     /* staging for host-pointer calls */
     size_t in_cap, out_cap, bfi_cap; void *d_in, *d_out, *d_bfi; uint8_t *h_bfi;
     int chunk_frames;
@@ -126,6 +130,9 @@ static int ctx_init(void)
     }
     CU(cudaEventCreate(&g.start_ev));
     CU(cudaEventCreate(&g.end_ev));
+    CU(cudaStreamCreateWithFlags(&g.h2d, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&g.d2h, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&g.d2h_ev, cudaEventDisableTiming));
     g.dirty_lo = 1 << 30; g.dirty_hi = -1;
     g.chunk_frames = 1 << 17;
     if (pool_grow(4096)) return 1;
@@ -216,6 +223,18 @@ static int lanes_reserve(size_t n)
     return 0;
 }
 
+/* Frames of chunk c when `rem` frames are left and a full chunk is fc frames.  With host input (ramp) the first two chunks
+ * are a quarter and a half chunk, so that the kernels start after a short first copy instead of a full chunk's. */
+static int chunk_size(int c, int rem, int fc, int ramp)
+{
+    int sz;
+    if (ramp && c == 0) sz = fc / 4;
+    else if (ramp && c == 1) sz = fc / 2;
+    else { int k = (rem + fc - 1) / fc; sz = (rem + k - 1) / k; }
+    if (sz < 1) sz = 1;
+    return sz < rem ? sz : rem;
+}
+
 /* one bucket: encoders that share (fs_idx, dms).  idx[] lists their positions in encs[]. */
 typedef struct { const void *h_pcm; void *h_out; } ChunkCopy; /* host buffers to copy chunk by chunk (NULL: not needed) */
 
@@ -279,8 +298,9 @@ static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_
     int fc = g.chunk_frames / (b.n_tiles * 32);
     if (fc < 1) fc = 1;
     if (fc > n_frames) fc = n_frames;
-    const int n_chunks = (n_frames + fc - 1) / fc;
-    fc = (n_frames + n_chunks - 1) / n_chunks;
+    const int ramp = cp && cp->h_pcm && n_frames > fc;
+    int n_chunks = 0;
+    for (int rem = n_frames; rem > 0; n_chunks++) rem -= chunk_size(n_chunks, rem, fc, ramp);
     const int n_pipes = n_chunks < N_PIPES ? n_chunks : N_PIPES;
     const size_t ftl = (size_t)fc * b.n_tiles * 32;
     const size_t need[N_WORK] = {(size_t)b.n_tiles * 32 * (size_t)(fc + 1) * N * sb, ftl * PO_N * 4, ftl * N * 4, ftl * FO_N * 4,
@@ -301,22 +321,27 @@ static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_
     /* everything queued on the main stream so far (state reset, configuration, lane tables, whole-buffer input copy)
      * is ordered before the first chunk of every pipe */
     CU(cudaEventRecord(g.start_ev, g.stream));
-    for (int f0 = 0, c = 0; f0 < n_frames; f0 += fc, c++) {
+    for (int f0 = 0, c = 0, cf; f0 < n_frames; f0 += cf, c++) {
+        cf = chunk_size(c, n_frames - f0, fc, ramp);
         const int p = c % N_PIPES;
         const cudaStream_t par = g.pipe[p].par, ser = g.pipe[p].ser;
         void *const *w = g.pipe[p].work;
         if (c < N_PIPES) { CU(cudaStreamWaitEvent(par, g.start_ev, 0)); CU(cudaStreamWaitEvent(ser, g.start_ev, 0)); }
         else CU(cudaStreamWaitEvent(ser, g.pipe[p].done_ev, 0)); /* chunk c - N_PIPES is done with these work buffers */
         b.frame0 = f0;
-        b.n_frames = n_frames - f0 < fc ? n_frames - f0 : fc;
+        b.n_frames = cf;
         b.pcm_t = w[0]; b.pout = (int32_t *)w[1]; b.spec = (int32_t *)w[2]; b.fout = (int32_t *)w[3];
         b.en4 = (int32_t *)w[4]; b.rout = (int32_t *)w[5]; b.r12 = (int16_t *)w[6]; b.xq = (int16_t *)w[7]; b.ben = (int32_t *)w[8];
-        if (cp && cp->h_pcm) /* this chunk's columns of every stream's PCM rows, one rectangle per channel */
+        const int copy_in = cp && cp->h_pcm;
+        if (copy_in) { /* this chunk's columns of every stream's PCM rows, one rectangle per channel */
+            if (c == 0) CU(cudaStreamWaitEvent(g.h2d, g.start_ev, 0));
             for (int ch = 0; ch < c0->channels; ch++) {
                 const size_t off = ((size_t)ch * n_frames + f0) * N * sb;
                 CU(cudaMemcpy2DAsync((char *)d_pcm + off, stride, (const char *)cp->h_pcm + off, stride, (size_t)b.n_frames * N * sb,
-                                     (size_t)n, cudaMemcpyHostToDevice, par));
+                                     (size_t)n, cudaMemcpyHostToDevice, g.h2d));
             }
+            CU(cudaEventRecord(g.pipe[p].hop_ev[N_KERNELS], g.h2d));
+        }
         /* The chunk's kernels form a small graph over the two streams.  16-bit input, long frames: the tile MDCT needs only
          * the staged samples, so it is issued right behind the FIR on `par` and runs beside the per-stream high-pass and
          * pitch passes on `ser`; SNS then waits for both (it takes the attack flag from the pitch pass).  Otherwise (24-bit
@@ -337,12 +362,9 @@ static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_
             if (bits != 16 && (k == K_FIR || k == K_SCALAR)) continue; /* fused into K_PITCH for 24-bit input */
             if (N < 160 && (k == K_SNS || k == K_TNS)) continue;        /* fused into K_FRONT for the short frames */
             const cudaStream_t st = k_stateful[k] ? ser : par;
-            if (!first) { /* the input copy above went to `par`: the first kernel (K_STAGE on `ser`) waits for it */
+            if (!first) { /* the first kernel (K_STAGE) waits for the chunk's input copy */
                 first = st;
-                if (st != par) {
-                    CU(cudaEventRecord(g.pipe[p].hop_ev[N_KERNELS], par));
-                    CU(cudaStreamWaitEvent(st, g.pipe[p].hop_ev[N_KERNELS], 0));
-                }
+                if (copy_in) CU(cudaStreamWaitEvent(st, g.pipe[p].hop_ev[N_KERNELS], 0));
             }
             const int *dep = split ? dep_split[k] : dep_chain[k];
             for (int j = 0; j < 2; j++)
@@ -357,15 +379,17 @@ static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_
         }
         /* K_BACK ran on `par`; error protection, if any lane asks for it, codes the finished payloads in place */
         if (any_ep) { CU((cudaError_t)lc3k_launch_fec(&b, par)); g.launches++; }
+        CU(cudaEventRecord(g.pipe[p].done_ev, par));
         if (cp && cp->h_out) {
             const size_t nb = (size_t)lc3cfg_num_bytes(c0), off = (size_t)f0 * nb;
+            CU(cudaStreamWaitEvent(g.d2h, g.pipe[p].done_ev, 0));
             CU(cudaMemcpy2DAsync((char *)cp->h_out + off, ostride, d_out + off, ostride, (size_t)b.n_frames * nb, (size_t)n,
-                                 cudaMemcpyDeviceToHost, par));
+                                 cudaMemcpyDeviceToHost, g.d2h));
         }
-        CU(cudaEventRecord(g.pipe[p].done_ev, par));
         g.launches += (bits == 16 ? 8 : 6) + (N >= 160 ? 2 : 0); /* frame lengths >= 160: the front end is three kernels (tile MDCT, SNS, TNS) */
     }
     for (int p = 0; p < n_pipes; p++) CU(cudaStreamWaitEvent(g.stream, g.pipe[p].done_ev, 0));
+    if (cp && cp->h_out) { CU(cudaEventRecord(g.d2h_ev, g.d2h)); CU(cudaStreamWaitEvent(g.stream, g.d2h_ev, 0)); }
     CU(cudaEventRecord(g.end_ev, g.stream));
     CU(cudaStreamSynchronize(g.stream)); /* lane tables are reused by the next bucket */
     if (g.prof_on) {

@@ -190,7 +190,7 @@ def main():
     pcm = make_streams_fast(S, F * N, FS, N)                 # every rank: its own shard of S streams
     if rank:
         pcm = np.roll(pcm, 131 * rank, axis=1)
-    encs = [ac.Encoder(FS, 1, DMS, BITRATE) for _ in range(S)]
+    encs = ac.EncoderArray([ac.Encoder(FS, 1, DMS, BITRATE) for _ in range(S)])  # the C call's `encoders` array, built once
     if args.chunk:
         ac.set_chunk_frames(args.chunk)
     d_pcm = torch.from_numpy(pcm).cuda()
