@@ -222,6 +222,22 @@ def main():
     frames_total = float(S) * F * args.steps * world
     value = frames_total / dev_s
 
+    # per-kernel times with every kernel ALONE on the device (the chunk's kernels strictly one after the other, one chunk per
+    # step): in the timed region above kernels of neighbouring chunks share the SMs, so their event brackets overlap
+    os.environ["LC3PLUS_B200_CHAIN"] = "1"
+    ac.set_chunk_frames(S * F)
+    step_dev()
+    torch.cuda.synchronize()
+    ac.profile_enable(True)
+    for _ in range(3):
+        step_dev()
+    torch.cuda.synchronize()
+    alone = ac.profile_read()
+    ac.profile_enable(False)
+    del os.environ["LC3PLUS_B200_CHAIN"]
+    ac.set_chunk_frames(args.chunk if args.chunk else 1 << 17)
+    barrier()
+
     # end to end: pinned host PCM in, pinned host bitstreams out, same call
     e2e = None
     if not args.no_e2e:
@@ -251,11 +267,11 @@ def main():
     except Exception:
         pass
     hbm_peak, peak_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json)") if "hbm_gbs" in peaks else (6650.0, "fallback")
-    kern = {k: prof[k] for k in ("stage", "fir", "scalar", "pitch", "mdct", "sns", "tns", "rate", "quant", "back")}
+    KS = ("stage", "fir", "scalar", "pitch", "mdct", "sns", "tns", "rate", "quant", "back")
+    kern = {k: alone[k] / alone["calls"] for k in KS}          # ms per step (S*F channel-frames), kernel alone
     top = max(kern, key=kern.get)
-    n_launch = prof["chunks"]
-    avg_ms = kern[top] / n_launch
-    frames_per_launch = S * F * args.steps / n_launch
+    avg_ms = kern[top]                                          # one launch of the dominant kernel covers the whole step here
+    frames_per_launch = S * F
     achieved = ALGO_BYTES_PER_FRAME * frames_per_launch / (avg_ms * 1e-3) / 1e9
     traffic = None
     try:
@@ -276,7 +292,11 @@ def main():
     roofline = {"bound": "hbm", "kernel": f"k_{top}", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                 "frac": achieved / hbm_peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_frame": ALGO_BYTES_PER_FRAME, "avg_launch_ms": avg_ms,
+                "timing": "CUDA events on the launching stream, each kernel alone on the device (3 untimed-region steps, one "
+                          "launch of each kernel per step of %d channel-frames); peak is the burst figure" % (S * F),
+                "kernel_ms_alone": {k: round(v, 4) for k, v in kern.items()},
                 "kernel_ms_share": {k: v / sum(kern.values()) for k, v in kern.items()},
+                "kernel_ms_overlapped_in_timed_region": {k: round(prof[k] / args.steps, 4) for k in KS},
                 "int_alu": {"note": "the path is integer-issue bound, not HBM bound (SURVEY.md 8d): reference weighted ops/frame x frames/s "
                                     "over the integer issue peak", "peak_source": int_src,
                             "weighted_ops_per_frame": WOPS_PER_FRAME, "achieved_wops_per_s": value / world * WOPS_PER_FRAME,
