@@ -279,7 +279,7 @@ template <int BITS, bool PRE> LC3_HD void pitch_warp_body(const LC3K_Batch &b, i
                 const i32 s0 = warp_sum(sh.red.a), s1 = warp_sum(sh.red.b) + 1, s2 = warp_sum(sh.red.c) + 1;
                 const i32 t0 = warp_sum(sh.red.d), t1 = warp_sum(sh.xc) + 1;
                 LC3_LANES(l)
-                    if (l < ncand) sh.red.a[l] = l == 0 ? normcorr_q15(s0, s1, s2, 0, 0) : normcorr_q15(t0, t1, s2, 0, 0);
+                    if (l < ncand) sh.red.a[l] = normcorr_q15(l == 0 ? s0 : t0, l == 0 ? s1 : t1, s2, 0, 0); // one copy of the code for both lanes
                 LC3_LANES_END
                 nc[0] = sh.red.a[0];
                 if (ncand == 2) nc[1] = sh.red.a[1];
