@@ -431,13 +431,11 @@ template <int BITS, bool PRE> LC3_HD void pitch_warp_body(const LC3K_Batch &b, i
                 LC3_LANES(l) // filtered current / predicted frame and their correlation: lane = sample
                     i64 a0 = 0, a1 = 0, a2 = 0;
                     for (int n = l; n < acflen; n += 32) {
-                        i32 s = l_mult(xp[n + 1], f00);
-                        s = l_mac(s, xp[n], f01);
-                        const i32 c = s_mac_r(s, xp[n - 1], f02);
-                        s = l_mult(xp[n - p_int + 1], fp0);
-                        s = l_mac(s, xp[n - p_int], fp1);
-                        s = l_mac(s, xp[n - p_int - 1], fp2);
-                        const i32 p = s_mac_r(s, xp[n - p_int - 2], fp3);
+                        // |xp| <= 2^12 after the block scaling above and sum |taps| <= 32875 (tests/test_rom_bounds.py): the
+                        // reference's L_mult / L_mac / round chain stays below 2^29 and is plain arithmetic
+                        const i32 c = (2 * (xp[n + 1] * f00 + xp[n] * f01 + xp[n - 1] * f02) + 0x8000) >> 16;
+                        const i32 p = (2 * (xp[n - p_int + 1] * fp0 + xp[n - p_int] * fp1 + xp[n - p_int - 1] * fp2 +
+                                            xp[n - p_int - 2] * fp3) + 0x8000) >> 16;
                         a0 += c * p; a1 += p * p; a2 += c * c;
                     }
                     sh.red.q[l] = a0; sh.red.q2[l] = a1; sh.red.q3[l] = a2;

@@ -23,6 +23,14 @@ def test_resampler_taps_cannot_overflow_32_bits():
             assert sum(abs(c) for c in co) * 32768 < 2 ** 31
 
 
+def test_ltpf_interpolation_taps_cannot_overflow_on_block_scaled_input():
+    """lc3_pitch_warp.cuh phase G: the 3-/4-tap filtered current and predicted frames are computed with plain arithmetic.
+    The LTPF buffers are block-scaled to three bits of headroom (|x| <= 2^12), so 2 * sum |taps| * 2^12 + 2^15 < 2^31."""
+    f = _tab("rom_ltpf_inter_filt")
+    for ph in range(4):
+        assert 2 * sum(abs(c) for c in f[ph * 12:(ph + 1) * 12]) * 4096 + 0x8000 < 2 ** 31
+
+
 def test_product_and_oracle_rom_identical():
     a = open(os.path.join(ROOT, "audio_codec_b200", "csrc", "rom_tables.inc")).read()
     b = open(os.path.join(ROOT, "oracle", "rom_tables.inc")).read()
