@@ -492,35 +492,38 @@ template <int BITS, bool PRE> LC3_HD void pitch_warp_body(const LC3K_Batch &b, i
             const int dec = b.fs == 32000 ? 2 : 3;
             const i32 ds = s_sub(dec - 1, s_sub(ns, in_scaling));
             const i32 fm0 = as.filter_mem[0], fm1 = as.filter_mem[1];
+            // ns <= headroom(input) + in_scaling - 2 and ns <= headroom(filter_mem) + scaling - 2, so a left shift (ds < 0) is
+            // by at most headroom - dec - 1 bits and every shifted sample is within +-2^(14 - dec): the two or three
+            // shr/add of the reference cannot saturate and |dd| <= 2^13 throughout (the rescaled memory included)
+            const i32 lsh = 1 << imax(-ds, 0), rsh = imin(imax(ds, 0), 15);
             LC3_LANES(l) // decimate to 16 kHz: lane = output sample
                 if (l == 0) { sh.dd[0] = (i16)fm0; sh.dd[1] = (i16)fm1; }
                 for (int i = l; i < 160; i += 32) {
                     const i16 *in = &sh.xs[64 + dec * i];
-                    i32 d;
-                    if (dec == 2) d = s_add(s_shr(in[0], ds), s_shr(in[1], ds));
-                    else d = s_add(s_shr(in[0], ds), s_add(s_shr(in[1], ds), s_shr(in[2], ds)));
+                    i32 d = ((in[0] * lsh) >> rsh) + ((in[1] * lsh) >> rsh);
+                    if (dec == 3) d += (in[2] * lsh) >> rsh;
                     sh.dd[2 + i] = (i16)d;
                 }
             LC3_LANES_END
-            LC3_LANES(l) // 3-tap high-pass on the unfiltered neighbours, energies of the four 40-sample blocks
-                i64 e[4] = {0, 0, 0, 0};
-                for (int i = l; i < 160; i += 32) {
-                    i32 t = l_mult(sh.dd[2 + i], 12288);
-                    t = l_msu(t, sh.dd[1 + i], 16384);
-                    t = l_mac(t, sh.dd[i], 4096);
-                    const i32 fv = hi16(t);
-                    const i64 sq = l_mult(fv, fv);
-                    const int blk = i / 40;
+            // 3-tap high-pass on the unfiltered neighbours, energies of the four 40-sample blocks.  |dd| <= 2^13: the
+            // L_mult / L_msu / L_mac chain stays within 2^29, a squared output within 2^27; a lane adds at most two of them
+            // to a block (samples l, l + 32, ..: block i / 40 of pass `it` is one of two known at compile time)
+            LC3_LANES(l)
+                i32 e[4] = {0, 0, 0, 0};
 #pragma unroll
-                    for (int j = 0; j < 4; j++) if (blk == j) e[j] += sq;
+                for (int it = 0; it < 5; it++) {
+                    const int i = l + 32 * it;
+                    const i32 t = 2 * (12288 * sh.dd[2 + i] - 16384 * sh.dd[1 + i] + 4096 * sh.dd[i]);
+                    const i32 fv = t >> 16, sq = 2 * fv * fv;
+#pragma unroll
+                    for (int j = 0; j < 4; j++)
+                        if (j >= (32 * it) / 40 && j <= (32 * it + 31) / 40) e[j] += i / 40 == j ? sq : 0;
                 }
-                sh.red.q[l] = e[0]; sh.red.q2[l] = e[1]; sh.red.q3[l] = e[2];
-                sh.red.a[l] = (i32)(e[3] >> 32); sh.red.b[l] = (i32)(e[3] & 0xffffffff);
+                sh.red.a[l] = e[0]; sh.red.b[l] = e[1]; sh.red.c[l] = e[2]; sh.red.d[l] = e[3];
             LC3_LANES_END
             i32 be[4];
-            be[0] = clamp64(warp_sum64(sh.red.q)); be[1] = clamp64(warp_sum64(sh.red.q2)); be[2] = clamp64(warp_sum64(sh.red.q3));
-            LC3_LANES(l) sh.red.q[l] = ((i64)sh.red.a[l] << 32) | (u32)sh.red.b[l]; LC3_LANES_END
-            be[3] = clamp64(warp_sum64(sh.red.q));
+            be[0] = clamp64(warp_sum_wide(sh.red.a)); be[1] = clamp64(warp_sum_wide(sh.red.b));
+            be[2] = clamp64(warp_sum_wide(sh.red.c)); be[3] = clamp64(warp_sum_wide(sh.red.d));
             as.filter_mem[0] = sh.dd[2 + 158];
             as.filter_mem[1] = sh.dd[2 + 159];
             i32 detected = as.position >= 2, pos = -1, acc = as.acc_energy;

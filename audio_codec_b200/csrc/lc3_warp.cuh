@@ -25,19 +25,29 @@ namespace lc3k {
 LC3_HD i32 warp_max(const i32 *red) { return __reduce_max_sync(0xffffffffu, red[threadIdx.x & 31]); }
 LC3_HD i32 warp_min(const i32 *red) { return __reduce_min_sync(0xffffffffu, red[threadIdx.x & 31]); }
 LC3_HD i32 warp_sum(const i32 *red) { return __reduce_add_sync(0xffffffffu, red[threadIdx.x & 31]); }
+// 64-bit reductions from the 32-bit warp-reduce instruction (one REDUX each instead of five shuffle/add rounds):
+// a sum as three partial sums of 16 + 16 + 32 bits (32 terms below 2^16 cannot carry out of 32 bits; the top part wraps
+// like the 64-bit sum does), a maximum as the maximum of the high words and then of the low words among its holders
 LC3_HD i64 warp_sum64(const i64 *red)
 {
-    i64 v = red[threadIdx.x & 31];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
+    const i64 v = red[threadIdx.x & 31];
+    const u32 lo = __reduce_add_sync(0xffffffffu, (u32)v & 0xffffu);
+    const u32 mid = __reduce_add_sync(0xffffffffu, (u32)(v >> 16) & 0xffffu);
+    const i32 hi = __reduce_add_sync(0xffffffffu, (i32)(v >> 32));
+    return (i64)(((uint64_t)(u32)hi << 32) + ((uint64_t)mid << 16) + lo);
+}
+LC3_HD i64 warp_sum_wide(const i32 *red) // 64-bit sum of non-negative 32-bit terms
+{
+    const u32 v = (u32)red[threadIdx.x & 31];
+    return (i64)(((uint64_t)__reduce_add_sync(0xffffffffu, v >> 16) << 16) + __reduce_add_sync(0xffffffffu, v & 0xffffu));
 }
 LC3_HD i64 warp_max64(const i64 *red)
 {
-    i64 v = red[threadIdx.x & 31];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) { i64 t = __shfl_xor_sync(0xffffffffu, v, o); v = t > v ? t : v; }
-    return v;
+    const i64 v = red[threadIdx.x & 31];
+    const i32 h = (i32)(v >> 32);
+    const i32 mh = __reduce_max_sync(0xffffffffu, h);
+    const u32 ml = __reduce_max_sync(0xffffffffu, h == mh ? (u32)v : 0u);
+    return (i64)(((uint64_t)(u32)mh << 32) | ml);
 }
 #else
 #define LC3_LANES(l) for (int l = 0; l < 32; l++) {
@@ -51,6 +61,7 @@ LC3_HD i32 warp_max(const i32 *red) { i32 v = red[0]; for (int i = 1; i < 32; i+
 LC3_HD i32 warp_min(const i32 *red) { i32 v = red[0]; for (int i = 1; i < 32; i++) v = red[i] < v ? red[i] : v; return v; }
 LC3_HD i32 warp_sum(const i32 *red) { i32 v = 0; for (int i = 0; i < 32; i++) v += red[i]; return v; }
 LC3_HD i64 warp_sum64(const i64 *red) { i64 v = 0; for (int i = 0; i < 32; i++) v += red[i]; return v; }
+LC3_HD i64 warp_sum_wide(const i32 *red) { i64 v = 0; for (int i = 0; i < 32; i++) v += red[i]; return v; }
 LC3_HD i64 warp_max64(const i64 *red) { i64 v = red[0]; for (int i = 1; i < 32; i++) v = red[i] > v ? red[i] : v; return v; }
 #endif
 
