@@ -2,6 +2,7 @@
 """Aggregate an ncu report's per-SASS-instruction counters by CUDA source line and by pipeline stage.
 
     tools/ncu_lines.py <report.ncu-rep> <kernel regex> <mangled name substring> [top N]
+    LINES=243,244 tools/ncu_lines.py ...   lists the SASS (executed count, stall samples) of those body lines instead
 
 `ncu --page source --csv` lists SASS instructions in address order with "Instructions Executed" and stall
 samples; `nvdisasm -gi -c` on the cubin extracted from liblc3plus_b200.so lists the same instructions with
@@ -88,6 +89,12 @@ def main():
                 return ch[i - 1] if i > 0 else fr
         return ch[0]
 
+    if os.environ.get("LINES"):  # dump the SASS (with executed counts) whose call site in the body is one of these lines
+        want = {int(v) for v in os.environ["LINES"].split(",")}
+        for k in range(n):
+            if stage_of(chains[k])[1] in want:
+                print(f"{k:6d} {sass[k][1]:12d} {sass[k][2]:6d}  L{stage_of(chains[k])[1]:<4d} {sass[k][0]}")
+        return
     tot_i = sum(s[1] for s in sass[:n])
     tot_s = sum(s[2] for s in sass[:n])
     print(f"total warp instructions {tot_i}, stall samples {tot_s}, SASS instructions {n}")
