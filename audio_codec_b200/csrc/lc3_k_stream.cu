@@ -73,12 +73,15 @@ __global__ void __launch_bounds__(128) k_fir(LC3K_Batch b)
 {
     __shared__ FirShared sh[4];
     __shared__ i16 filt[240];
+    __shared__ u32 filtp[120];
     for (int i = threadIdx.x; i < 240; i += 128) filt[i] = rom_resamp_filt[b.fs_idx * 240 + i];
+    if (threadIdx.x < 120)
+        filtp[threadIdx.x] = fir_pack_taps(rom_resamp_filt[b.fs_idx * 240 + 2 * threadIdx.x], rom_resamp_filt[b.fs_idx * 240 + 2 * threadIdx.x + 1]);
     __syncthreads();
     const int w = threadIdx.x >> 5;
     const long long item = (long long)blockIdx.x * 4 + w;
     if (item >= (long long)b.n_frames * b.n_lanes) return;
-    fir_warp_body(b, (int)(item % b.n_lanes), (int)(item / b.n_lanes), sh[w], filt);
+    fir_warp_body(b, (int)(item % b.n_lanes), (int)(item / b.n_lanes), sh[w], filt, filtp);
 }
 
 // scalar recursions (high-pass, attack detector): one lane per channel-stream

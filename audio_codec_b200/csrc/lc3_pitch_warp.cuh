@@ -572,9 +572,45 @@ template <int BITS, bool PRE> LC3_HD void pitch_warp_body(const LC3K_Batch &b, i
 }
 
 // ---- resampler FIR as its own frame-parallel pass (16-bit input): one warp per (channel-stream, frame)
-struct FirShared { i16 xs[64 + LC3K_MAX_N]; };
+struct FirShared {
+    alignas(4) i16 xs[64 + LC3K_MAX_N];  // xs[64 + i] = sample i of the frame
+    alignas(4) i16 xs2[64 + LC3K_MAX_N]; // the same one sample earlier (xs2[k] = xs[k + 1]): an aligned pair for odd offsets
+};
 
-LC3_HD void fir_warp_body(const LC3K_Batch &b, int li, int f, FirShared &sh, const i16 *filt /* this rate's 240 taps */)
+// Two taps as one word for the two-way dot product instruction (dp2a: two 16-bit samples times two BYTES): a tap is
+// split into its unsigned low byte and its signed high byte, c = 256 * ch + cl; bytes 0,1 = cl of the two taps, 2,3 = ch.
+LC3_HD u32 fir_pack_taps(i32 c0, i32 c1)
+{
+    return (u32)(c0 & 255) | ((u32)(c1 & 255) << 8) | ((u32)((c0 >> 8) & 255) << 16) | ((u32)((c1 >> 8) & 255) << 24);
+}
+LC3_HD u32 ld_u32(const i16 *p)
+{
+#if defined(__CUDA_ARCH__)
+    return *reinterpret_cast<const u32 *>(p);
+#else
+    u32 v; memcpy(&v, p, 4); return v;
+#endif
+}
+// acc + x.lo * (unsigned byte 0 of c) + x.hi * (unsigned byte 1 of c);  acc + x.lo * (signed byte 2) + x.hi * (signed byte 3)
+LC3_HD i32 dp2a_lo_u8(u32 x, u32 c, i32 acc)
+{
+#if defined(__CUDA_ARCH__)
+    i32 r; asm("dp2a.lo.s32.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(x), "r"(c), "r"(acc)); return r;
+#else
+    return (i32)((u32)acc + (u32)((i32)(i16)(x & 0xffff) * (i32)(c & 255)) + (u32)(((i32)x >> 16) * (i32)((c >> 8) & 255)));
+#endif
+}
+LC3_HD i32 dp2a_hi_s8(u32 x, u32 c, i32 acc)
+{
+#if defined(__CUDA_ARCH__)
+    i32 r; asm("dp2a.hi.s32.s32 %0, %1, %2, %3;" : "=r"(r) : "r"(x), "r"(c), "r"(acc)); return r;
+#else
+    return (i32)((u32)acc + (u32)((i32)(i16)(x & 0xffff) * (i32)(int8_t)((c >> 16) & 255)) + (u32)(((i32)x >> 16) * ((i32)c >> 24)));
+#endif
+}
+
+LC3_HD void fir_warp_body(const LC3K_Batch &b, int li, int f, FirShared &sh, const i16 *filt /* this rate's 240 taps */,
+                          const u32 *filtp /* the same, fir_pack_taps of taps 2p, 2p + 1 */)
 {
     if (li >= b.n_lanes) return;
     const int tile = li >> 5, tl = li & 31, N = b.N, rl = b.r12k8_mem_in_len, len = 32 * (b.dms / 25);
@@ -586,7 +622,7 @@ LC3_HD void fir_warp_body(const LC3K_Batch &b, int li, int f, FirShared &sh, con
     raw.cur = (const i16 *)b.pcm + b.pcm_off[li] + (size_t)(b.frame0 + f) * N;
     raw.first = f == 0;
     LC3_LANES(l)
-        for (int i = l - rl; i < N; i += 32) sh.xs[64 + i] = (i16)raw(i);
+        for (int i = l - rl; i < N; i += 32) { const i16 v = (i16)raw(i); sh.xs[64 + i] = v; sh.xs2[63 + i] = v; }
     LC3_LANES_END
     SV<i16> r = tile_view(b.r12, frame_tile(b, f, tile), 128, tl);
     // (see pitch_warp_body phase B for why plain arithmetic is exact.)  A lane owns outputs l, l + 32, l + 64, l + 96: the
@@ -599,9 +635,23 @@ LC3_HD void fir_warp_body(const LC3K_Batch &b, int li, int f, FirShared &sh, con
         const i16 *in0 = &sh.xs[64 + 1 + l * off_int + t0 / upfac - rl];
         const int step = 32 * off_int + (32 * off_frac) / upfac; // input distance between two outputs of the lane
         if (nq == 4) {
-            const i16 *in1 = in0 + step, *in2 = in1 + step, *in3 = in2 + step;
-            i32 a0 = 0, a1 = 0, a2 = 0, a3 = 0;
-            for (int m = 0; m < delay2; m++) { const i32 c = co[m]; a0 += in0[m] * c; a1 += in1[m] * c; a2 += in2[m] * c; a3 += in3[m] * c; }
+            // Two taps and two samples per instruction: the number of taps per branch, the branch's offset in the table and
+            // `step` are even at every rate, so the pairs are aligned words (of xs or of its one-sample-shifted copy).
+            // The low-byte and high-byte sums are exact (60 taps * 2^15 * 2^8 < 2^31) and 256 * hi + lo is the plain sum.
+            const int e0 = (int)(in0 - sh.xs), sw = step >> 1, np = delay2 >> 1;
+            const i16 *p0 = (e0 & 1) ? &sh.xs2[e0 - 1] : &sh.xs[e0];
+            const u32 *cp = &filtp[(fr * delay2) >> 1];
+            i32 l0 = 0, l1 = 0, l2 = 0, l3 = 0, h0 = 0, h1 = 0, h2 = 0, h3 = 0;
+            for (int m = 0; m < np; m++) {
+                const u32 c = cp[m];
+                const u32 x0 = ld_u32(p0 + 2 * m), x1 = ld_u32(p0 + 2 * (m + sw)), x2 = ld_u32(p0 + 2 * (m + 2 * sw)), x3 = ld_u32(p0 + 2 * (m + 3 * sw));
+                l0 = dp2a_lo_u8(x0, c, l0); h0 = dp2a_hi_s8(x0, c, h0);
+                l1 = dp2a_lo_u8(x1, c, l1); h1 = dp2a_hi_s8(x1, c, h1);
+                l2 = dp2a_lo_u8(x2, c, l2); h2 = dp2a_hi_s8(x2, c, h2);
+                l3 = dp2a_lo_u8(x3, c, l3); h3 = dp2a_hi_s8(x3, c, h3);
+            }
+            const i32 a0 = (i32)(((u32)h0 << 8) + (u32)l0), a1 = (i32)(((u32)h1 << 8) + (u32)l1);
+            const i32 a2 = (i32)(((u32)h2 << 8) + (u32)l2), a3 = (i32)(((u32)h3 << 8) + (u32)l3);
             r[l] = (i16)l_round(a0); r[l + 32] = (i16)l_round(a1); r[l + 64] = (i16)l_round(a2); r[l + 96] = (i16)l_round(a3);
         } else {
             for (int q = 0; q < nq; q++) {

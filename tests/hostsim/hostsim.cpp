@@ -193,8 +193,10 @@ extern "C" int hostsim_encode(void *p, const void *pcm, int bits, int n_frames, 
         b.r12 = r12.data();
         if (bits == 16) { // three passes as the kernels run them
             static FirShared fsh;
+            uint32_t filtp[120];
+            for (int i = 0; i < 120; i++) filtp[i] = fir_pack_taps(rom_resamp_filt[b.fs_idx * 240 + 2 * i], rom_resamp_filt[b.fs_idx * 240 + 2 * i + 1]);
             for (int f = 0; f < n_frames; f++)
-                for (int li = 0; li < b.n_lanes; li++) fir_warp_body(b, li, f, fsh, &rom_resamp_filt[b.fs_idx * 240]);
+                for (int li = 0; li < b.n_lanes; li++) fir_warp_body(b, li, f, fsh, &rom_resamp_filt[b.fs_idx * 240], filtp);
             for (int tile = 0; tile < b.n_tiles; tile++)
                 for (int lane = 0; lane < 32; lane++) scalar_body(b, tile, lane);
             for (int li = 0; li < b.n_lanes; li++) pitch_warp_body<16, true>(b, li, psh);
