@@ -69,19 +69,27 @@ template <int BITS, bool PRE> __global__ void __launch_bounds__(32 * PITCH_WARPS
 }
 
 // resampler FIR, frame-parallel: one warp per (channel-stream, frame)
-__global__ void __launch_bounds__(128) k_fir(LC3K_Batch b)
+// A block's warps each take FIR_ITEMS (stream, frame) pairs, so the tap tables (read lane by lane from constant
+// memory, which serialises) are set up once per FIR_WARPS * FIR_ITEMS frames.
+#define FIR_WARPS 8
+#define FIR_ITEMS 4
+__global__ void __launch_bounds__(32 * FIR_WARPS) k_fir(LC3K_Batch b)
 {
-    __shared__ FirShared sh[4];
+    __shared__ FirShared sh[FIR_WARPS];
     __shared__ i16 filt[240];
     __shared__ u32 filtp[120];
-    for (int i = threadIdx.x; i < 240; i += 128) filt[i] = rom_resamp_filt[b.fs_idx * 240 + i];
-    if (threadIdx.x < 120)
-        filtp[threadIdx.x] = fir_pack_taps(rom_resamp_filt[b.fs_idx * 240 + 2 * threadIdx.x], rom_resamp_filt[b.fs_idx * 240 + 2 * threadIdx.x + 1]);
+    for (int i = threadIdx.x; i < 240; i += 32 * FIR_WARPS) filt[i] = rom_resamp_filt[b.fs_idx * 240 + i];
+    __syncthreads();
+    if (threadIdx.x < 120) filtp[threadIdx.x] = fir_pack_taps(filt[2 * threadIdx.x], filt[2 * threadIdx.x + 1]);
     __syncthreads();
     const int w = threadIdx.x >> 5;
-    const long long item = (long long)blockIdx.x * 4 + w;
-    if (item >= (long long)b.n_frames * b.n_lanes) return;
-    fir_warp_body(b, (int)(item % b.n_lanes), (int)(item / b.n_lanes), sh[w], filt, filtp);
+    const long long n_items = (long long)b.n_frames * b.n_lanes;
+    for (int k = 0; k < FIR_ITEMS; k++) {
+        const long long item = ((long long)blockIdx.x * FIR_ITEMS + k) * FIR_WARPS + w;
+        if (item >= n_items) return;
+        fir_warp_body(b, (int)(item % b.n_lanes), (int)(item / b.n_lanes), sh[w], filt, filtp);
+        __syncwarp();
+    }
 }
 
 // scalar recursions (high-pass, attack detector): one lane per channel-stream
@@ -142,7 +150,7 @@ extern "C" int lc3k_launch_fir(const LC3K_Batch *b, void *stream)
 {
     if (b->bits != 16) return 0;
     const long long items = (long long)b->n_frames * b->n_lanes;
-    k_fir<<<(unsigned)((items + 3) / 4), 128, 0, (cudaStream_t)stream>>>(*b);
+    k_fir<<<(unsigned)((items + FIR_WARPS * FIR_ITEMS - 1) / (FIR_WARPS * FIR_ITEMS)), 32 * FIR_WARPS, 0, (cudaStream_t)stream>>>(*b);
     return done();
 }
 extern "C" int lc3k_launch_scalar(const LC3K_Batch *b, void *stream)

@@ -622,7 +622,9 @@ LC3_HD void fir_warp_body(const LC3K_Batch &b, int li, int f, FirShared &sh, con
     raw.cur = (const i16 *)b.pcm + b.pcm_off[li] + (size_t)(b.frame0 + f) * N;
     raw.first = f == 0;
     LC3_LANES(l)
-        for (int i = l - rl; i < N; i += 32) { const i16 v = (i16)raw(i); sh.xs[64 + i] = v; sh.xs2[63 + i] = v; }
+        int i = l - rl;
+        for (; i < 0; i += 32) { const i16 v = (i16)raw(i); sh.xs[64 + i] = v; sh.xs2[63 + i] = v; } // previous frame: history or PCM
+        for (; i < N; i += 32) { const i16 v = raw.cur[i]; sh.xs[64 + i] = v; sh.xs2[63 + i] = v; }
     LC3_LANES_END
     SV<i16> r = tile_view(b.r12, frame_tile(b, f, tile), 128, tl);
     // (see pitch_warp_body phase B for why plain arithmetic is exact.)  A lane owns outputs l, l + 32, l + 64, l + 96: the
