@@ -246,14 +246,15 @@ LC3_HD i32 ari_encode(B bytes, BackWriter<B> &w, i32 nbbits, XQ xq, int nt, i32 
             const i32 mx = imax(a1, b1);
             ctx = c + rateFlag;
             if (k > nt_half) ctx += 1 << 8;
-            lev = mx < 4 ? 0 : (mx < 8 ? 1 : 13 - s_norm(mx));
-            msb = (a1 >> lev) + ((b1 >> lev) << 2);
-            const i32 t = mx == 0 ? 1 : (lev == 0 ? a1 + b1 + 1 : (lev == 1 ? 2 * ((a1 >> 1) + (b1 >> 1)) + 1 : 12 + imin(lev, 3)));
+            lev = imax(0, 13 - s_norm(mx | 1)); // 0 below 4, 1 below 8, 13 - norm_s(mx) from there
+            const i32 am = a1 >> lev, bm = b1 >> lev;
+            msb = am + (bm << 2);
+            const i32 t = lev < 2 ? ((am + bm) << lev) + 1 : 12 + imin(lev, 3); // 1 | a1 + b1 + 1 | 2 (a1 / 2 + b1 / 2) + 1 | 12 + ..
             c = ((c & 0xf) << 4) + t;
         }
         const bool last = l == lev; // this iteration codes the MSB symbol, the earlier ones an escape each
         {
-            const int row = T.lut[ctx + rom_ari_esc_nb[l < 3 ? l : 3]] * 17 + (last ? msb : 16);
+            const int row = T.lut[ctx + (imin(l, 3) << 10)] * 17 + (last ? msb : 16); // rom_ari_esc_nb[q] = 1024 q
             const u32 cf = T.cf[row];
             rc_encode<PC>(s, cf & 0xffffu, cf >> 16, pc, w);
         }

@@ -131,11 +131,9 @@ LC3_HD void rate_warp_body(const LC3K_Batch &b, int li, RateShared &sh, const u8
                 const i32 a1 = s_abs((i16)quant_bin(d[k], inv, s)), b1 = s_abs((i16)quant_bin(d[k + 1], inv, s)), mx = imax(a1, b1);
                 LC3_PL(ab, m, l) = a1 | (b1 << 16);
                 // magnitude class of the tuple (the value the reference folds into the next two contexts)
-                i32 t;
-                if (mx == 0) t = 1;
-                else if (mx < 4) t = a1 + b1 + 1;
-                else if (mx < 8) t = 2 * ((a1 >> 1) + (b1 >> 1)) + 1;
-                else t = 12 + imin(13 - s_norm(mx), 3);
+                // (1 | a1 + b1 + 1 | 2 * (a1 / 2 + b1 / 2) + 1 | 12 + min(lev, 3) for mx = 0 | < 4 | < 8 | above, with lev = 0, 0, 1, >= 2)
+                const i32 lev = imax(0, 13 - s_norm(mx | 1));
+                const i32 t = lev < 2 ? (((a1 >> lev) + (b1 >> lev)) << lev) + 1 : 12 + imin(lev, 3);
                 sh.tv[2 + (k >> 1)] = (u8)t;
                 if (mx != 0 && k >= 2) last = k + 2; // find_last_nz_pair: the pair below bin 2 is not looked at
             }
@@ -153,21 +151,16 @@ LC3_HD void rate_warp_body(const LC3K_Batch &b, int li, RateShared &sh, const u8
                 i32 t = ((i32)sh.tv[j] << 4) + sh.tv[j + 1] + rateFlag; // tv[j] = class of tuple j-2, tv[j+1] = of j-1
                 if (k > nt_half) t += 1 << 8;
                 const i32 a1 = LC3_PL(ab, m, l) & 0xffff, b1 = LC3_PL(ab, m, l) >> 16, mx = imax(a1, b1);
-                if (mx == 0) { nb += ari_bits(ari_lut, ari_bitstab, t, 0); continue; }
-                i32 lev, am, bm;
-                if (mx < 4) {
-                    lev = 0; am = a1; bm = b1;
-                } else if (mx < 8) {
-                    lev = 1; am = a1 >> 1; bm = b1 >> 1;
-                    nb += ari_bits(ari_lut, ari_bitstab, t, 16) + (2 << 11);
-                } else {
-                    lev = 13 - s_norm(mx);
-                    for (int q = 0; q < lev; q++) nb += ari_bits(ari_lut, ari_bitstab, t + rom_ari_esc_nb[q < 3 ? q : 3], 16);
-                    nb += lev << 12;
-                    am = a1 >> lev; bm = b1 >> lev;
-                }
-                nb += ari_bits(ari_lut, ari_bitstab, t + (lev ? rom_ari_esc_nb[lev < 3 ? lev : 3] : 0), am + (bm << 2));
-                nb += ((a1 != 0) + (b1 != 0)) << 11;
+                // One straight path for every magnitude class (the lanes of a warp hold all of them at once): `lev` escape
+                // symbols (row t + 1024 * min(q, 3), symbol 16) and lev LSB pairs, the MSB symbol, the signs.
+                // 13 - norm_s(mx) for mx >= 4, 0 below (an all-zero tuple codes symbol 0 of its own row).
+                const i32 lev = imax(0, 13 - s_norm(mx | 1));
+                nb += (lev << 12) + (((a1 != 0) + (b1 != 0)) << 11);
+                if (lev > 0) nb += ari_bits(ari_lut, ari_bitstab, t, 16);
+                if (lev > 1) nb += ari_bits(ari_lut, ari_bitstab, t + 1024, 16);
+                if (lev > 2) nb += ari_bits(ari_lut, ari_bitstab, t + 2048, 16);
+                if (lev > 3) nb += (lev - 3) * ari_bits(ari_lut, ari_bitstab, t + 3072, 16);
+                nb += ari_bits(ari_lut, ari_bitstab, t + (imin(lev, 3) << 10), (a1 >> lev) + ((b1 >> lev) << 2));
             }
             sh.red.a[l] = nb;
         LC3_LANES_END

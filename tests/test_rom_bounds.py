@@ -31,6 +31,11 @@ def test_ltpf_interpolation_taps_cannot_overflow_on_block_scaled_input():
         assert 2 * sum(abs(c) for c in f[ph * 12:(ph + 1) * 12]) * 4096 + 0x8000 < 2 ** 31
 
 
+def test_escape_rows_are_multiples_of_1024():
+    """lc3_bits.cuh ari_encode and lc3_rate_warp.cuh write the escape row offset as min(q, 3) << 10."""
+    assert list(_tab("rom_ari_esc_nb")) == [0, 1024, 2048, 3072]
+
+
 def test_product_and_oracle_rom_identical():
     a = open(os.path.join(ROOT, "audio_codec_b200", "csrc", "rom_tables.inc")).read()
     b = open(os.path.join(ROOT, "oracle", "rom_tables.inc")).read()
