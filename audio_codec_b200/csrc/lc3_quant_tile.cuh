@@ -74,29 +74,17 @@ LC3_HD void qt_quantise(const LC3K_Batch &b, int f, int tile, int t, QuantShared
 // bit cost (Q11) of tuple (a1, b1) in context t, and what it adds to the diverted LSB plane (mode 1)
 LC3_HD i32 qt_tuple_bits(i32 t, i32 a1, i32 b1, i32 mode, const u8 *lut, const uint16_t *bitstab, i32 &lsb)
 {
+    // one straight path for every magnitude class, as in rate_warp_body: lev = 0 below 4, 1 below 8, 13 - norm_s(mx) above
     const i32 mx = imax(a1, b1);
-    lsb = 0;
-    if (mx == 0) return ari_bits(lut, bitstab, t, 0);
-    i32 nb = 0, lev, am, bm;
-    if (mx < 4) {
-        lev = 0; am = a1; bm = b1;
-    } else if (mx < 8) {
-        lev = 1; am = a1 >> 1; bm = b1 >> 1;
-        nb += ari_bits(lut, bitstab, t, 16);
-        if (mode <= 0) nb += 2 << 11;
-    } else {
-        lev = 13 - s_norm(mx);
-        for (int l = 0; l < lev; l++) nb += ari_bits(lut, bitstab, t + rom_ari_esc_nb[l < 3 ? l : 3], 16);
-        nb += (mode <= 0 ? lev : lev - 1) << 12;
-        am = a1 >> lev; bm = b1 >> lev;
-    }
-    nb += ari_bits(lut, bitstab, t + (lev ? rom_ari_esc_nb[lev < 3 ? lev : 3] : 0), am + (bm << 2));
-    if (mode > 0 && lev > 0) { // sign bits only for values that survive dropping the LSB
-        nb += (((a1 >> 1) != 0) + ((b1 >> 1) != 0)) << 11;
-        lsb = 2 + (a1 == 1) + (b1 == 1);
-    } else {
-        nb += ((a1 != 0) + (b1 != 0)) << 11;
-    }
+    const i32 lev = imax(0, 13 - s_norm(mx | 1));
+    const i32 dv = (mode > 0 && lev > 0) ? 1 : 0; // the lowest plane is diverted: its bits are counted apart, signs of +-1 go with it
+    i32 nb = ((lev - dv) << 12) + ((((a1 >> dv) != 0) + ((b1 >> dv) != 0)) << 11);
+    lsb = dv ? 2 + (a1 == 1) + (b1 == 1) : 0;
+    if (lev > 0) nb += ari_bits(lut, bitstab, t, 16);
+    if (lev > 1) nb += ari_bits(lut, bitstab, t + 1024, 16);
+    if (lev > 2) nb += ari_bits(lut, bitstab, t + 2048, 16);
+    if (lev > 3) nb += (lev - 3) * ari_bits(lut, bitstab, t + 3072, 16);
+    nb += ari_bits(lut, bitstab, t + (imin(lev, 3) << 10), (a1 >> lev) + ((b1 >> lev) << 2));
     return nb;
 }
 
@@ -117,11 +105,8 @@ LC3_HD void qt_analyse(QuantFrame &q, i16 *xq, int nt, QuantWarp &w, const u8 *l
     LC3_LANES(l) // magnitude class of every tuple (what the reference folds into the next two contexts)
         for (int k = 2 * l; k < lastnz; k += 64) {
             const i32 a1 = s_abs(xq[k]), b1 = s_abs(xq[k + 1]), mx = imax(a1, b1);
-            i32 t;
-            if (mx == 0) t = 1;
-            else if (mx < 4) t = a1 + b1 + 1;
-            else if (mx < 8) t = 2 * ((a1 >> 1) + (b1 >> 1)) + 1;
-            else t = 12 + imin(13 - s_norm(mx), 3);
+            const i32 lev = imax(0, 13 - s_norm(mx | 1));
+            const i32 t = lev < 2 ? (((a1 >> lev) + (b1 >> lev)) << lev) + 1 : 12 + imin(lev, 3);
             w.tv[2 + (k >> 1)] = (u8)t;
         }
     LC3_LANES_END

@@ -310,6 +310,16 @@ LC3_HD i32 noise_factor(i32 x_e, A x, XQ xq, i32 gg, i32 gg_e, int bw, int dms, 
     // group, fetched up front (independent loads); bins from N - width on see zeros ahead of them, as in the reference
     for (int k0 = start; k0 < N; k0 += 8) {
         i32 q[8], xv[8];
+        if (k0 + 8 + width <= N) { // a whole group inside the band: no bounds to check (nz and isum stay far below 2^15 / 2^31)
+#pragma unroll
+            for (int j = 0; j < 8; j++) { q[j] = xq[k0 + j + width]; xv[j] = x[k0 + j]; }
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                nz = q[j] != 0 ? -2 * width - 1 : nz + 1;
+                if (nz >= 0) { c++; sum = l_add(sum, l_abs(xv[j])); isum += k0 + j; }
+            }
+            continue;
+        }
 #pragma unroll
         for (int j = 0; j < 8; j++) {
             const int kk = k0 + j;
@@ -320,8 +330,8 @@ LC3_HD i32 noise_factor(i32 x_e, A x, XQ xq, i32 gg, i32 gg_e, int bw, int dms, 
         for (int j = 0; j < 8; j++) {
             const int kk = k0 + j;
             if (kk >= N) break;
-            nz = q[j] != 0 ? -2 * width - 1 : s_add(nz, 1);
-            if (nz >= 0) { c++; sum = l_add(sum, l_abs(xv[j])); isum = l_add(isum, kk); }
+            nz = q[j] != 0 ? -2 * width - 1 : nz + 1;
+            if (nz >= 0) { c++; sum = l_add(sum, l_abs(xv[j])); isum += kk; }
         }
     }
     i32 fac = 0;
