@@ -1,5 +1,6 @@
 // sm_100a kernels of the batched LC3plus encoder, part: bandwidth detector + SNS of the tile path (lc3_body_frame.cuh,
 // sns_body): one lane per channel-frame, band energies in, SNS gains and indices out -- no spectrum access.
+#define LC3_SAT16_PTX 1
 #include <cuda_runtime.h>
 #include "lc3_body_frame.cuh"
 

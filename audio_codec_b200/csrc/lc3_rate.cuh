@@ -37,15 +37,16 @@ template <class A, class E> LC3_HD i32 gain_energies(A x, i32 x_e, int lg, E en)
             const i32 v0 = w[4 * h], v1 = w[4 * h + 1], v2 = w[4 * h + 2], v3 = w[4 * h + 3];
             i32 m = l_max(l_max(l_abs(v0), l_abs(v1)), l_max(l_abs(v2), l_abs(v3)));
             x_max = l_max(x_max, m);
-            i32 s = m != 0 ? l_norm(m) : 31;
-            s = s - 2;
+            const i32 nrm = m != 0 ? l_norm(m) : 31;
+            i32 s = nrm - 2;
             // the shift leaves 2 bits of headroom, the rounded values are below 2^13 and 1 + 4 * 2 * t^2 < 2^29:
-            // none of the reference's saturating operators (L_shl, round_fx, L_mac) can saturate here
+            // none of the reference's saturating operators (L_shl, round_fx, L_mac) can saturate here.  A shift by
+            // nrm - 2 (which is negative for the largest values) is the exact shift by nrm followed by >> 2.
             i32 e = 1, t;
-            t = (l_shl_ns(v0, s) + 0x8000) >> 16; e += 2 * t * t;
-            t = (l_shl_ns(v1, s) + 0x8000) >> 16; e += 2 * t * t;
-            t = (l_shl_ns(v2, s) + 0x8000) >> 16; e += 2 * t * t;
-            t = (l_shl_ns(v3, s) + 0x8000) >> 16; e += 2 * t * t;
+            t = (((i32)((u32)v0 << nrm) >> 2) + 0x8000) >> 16; e += 2 * t * t;
+            t = (((i32)((u32)v1 << nrm) >> 2) + 0x8000) >> 16; e += 2 * t * t;
+            t = (((i32)((u32)v2 << nrm) >> 2) + 0x8000) >> 16; e += 2 * t * t;
+            t = (((i32)((u32)v3 << nrm) >> 2) + 0x8000) >> 16; e += 2 * t * t;
             s = s_shl(s_sub(x_e, s), 1);
             if (e == 1 && s < 0) s = 0;
             t = l_add(m_log2(e), l_shl_p(s, 25) );

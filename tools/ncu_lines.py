@@ -92,7 +92,7 @@ def main():
     if os.environ.get("LINES"):  # dump the SASS (with executed counts) whose call site in the body is one of these lines
         want = {int(v) for v in os.environ["LINES"].split(",")}
         for k in range(n):
-            if stage_of(chains[k])[1] in want:
+            if stage_of(chains[k])[1] in want or (os.environ.get("LINES_FILE") and any(fr[0] == os.environ["LINES_FILE"] and fr[1] in want for fr in chains[k])):
                 print(f"{k:6d} {sass[k][1]:12d} {sass[k][2]:6d}  L{stage_of(chains[k])[1]:<4d} {sass[k][0]}")
         return
     tot_i = sum(s[1] for s in sass[:n])
