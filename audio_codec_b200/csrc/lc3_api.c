@@ -54,7 +54,8 @@ typedef struct {
     cudaEvent_t d2h_ev;
     /* staging for host-pointer calls */
     size_t in_cap, out_cap, bfi_cap; void *d_in, *d_out, *d_bfi; uint8_t *h_bfi;
-    int chunk_frames;
+    int chunk_frames;      /* channel-frames per chunk, input resident on the device */
+    int chunk_frames_host; /* same, input in host memory: shorter chunks, the copies fill and drain the pipeline faster */
     long long launches;
     /* optional per-kernel timing with CUDA events on the launching stream */
     int prof_on; cudaEvent_t *ev; int n_ev; double prof_ms[N_KERNELS + 3];
@@ -134,7 +135,9 @@ static int ctx_init(void)
     CU(cudaStreamCreateWithFlags(&g.d2h, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&g.d2h_ev, cudaEventDisableTiming));
     g.dirty_lo = 1 << 30; g.dirty_hi = -1;
-    g.chunk_frames = 1 << 17;
+    g.chunk_frames = 5 << 15;
+    g.chunk_frames_host = 1 << 16;
+    { const char *e = getenv("LC3PLUS_B200_HOST_CHUNK"); if (e && atoi(e) >= 32) g.chunk_frames_host = atoi(e); } /* tuning aid */
     if (pool_grow(4096)) return 1;
     g.failed = 0;
     g.ready = 1;
@@ -295,7 +298,7 @@ static int run_bucket(struct LC3_Enc *const *encs, const int *idx, int n, int n_
     }
 
     /* frames per chunk: about g.chunk_frames channel-frames each, balanced over the chunks */
-    int fc = g.chunk_frames / (b.n_tiles * 32);
+    int fc = ((cp && cp->h_pcm) ? g.chunk_frames_host : g.chunk_frames) / (b.n_tiles * 32);
     if (fc < 1) fc = 1;
     if (fc > n_frames) fc = n_frames;
     const int ramp = cp && cp->h_pcm && n_frames > fc;
@@ -649,7 +652,7 @@ long long lc3plus_kernel_launches(void) { return g.launches; }
 void lc3plus_profile_enable(int on) { g.prof_on = on; memset(g.prof_ms, 0, sizeof(g.prof_ms)); }
 void lc3plus_profile_read(double *ms) { memcpy(ms, g.prof_ms, sizeof(g.prof_ms)); }
 const char *lc3plus_last_error(void) { return g.err; }
-void lc3plus_set_chunk_frames(int channel_frames) { if (channel_frames >= 32) { ctx_init(); g.chunk_frames = channel_frames; } }
+void lc3plus_set_chunk_frames(int channel_frames) { if (channel_frames >= 32) { ctx_init(); g.chunk_frames = g.chunk_frames_host = channel_frames; } }
 
 /* `lc3plus_` spellings */
 LC3_Error lc3plus_enc_init(LC3_Enc *e, int fs, int ch) { return lc3_enc_init(e, fs, ch); }

@@ -112,8 +112,9 @@ void lc3plus_profile_enable(int on);
 void lc3plus_profile_read(double *ms);
 /* NEW: last CUDA error string seen by the library ("" if none). */
 const char *lc3plus_last_error(void);
-/* NEW: upper bound on channel-frames processed per internal chunk (default 131072); up to three chunks are in
- * flight at once, each on its own CUDA stream with its own work buffers. */
+/* NEW: upper bound on channel-frames processed per internal chunk (defaults: 163840 when the PCM is already on the
+ * device, 65536 when it is copied from host memory chunk by chunk); up to three chunks are in flight at once, each on
+ * its own CUDA streams with its own work buffers. */
 void lc3plus_set_chunk_frames(int channel_frames);
 
 /* ---- Bitstream containers of the reference command-line tool.  Host-only helpers: they
