@@ -44,8 +44,10 @@ template <class A> LC3_HD i32 band_one(i32 &en, A d, int band, const i16 *bo, co
     }
     // wider bands
     const int start = bo[band], stop = imin(bo[band + 1], g.maxbin);
-    i32 s1 = 15;
-    for (int k = start; k < stop; k++) s1 = hr15(d[k], s1);
+    // minimum norm_l over the band's non-zero bins = norm_l of the OR of their magnitudes (v, or ~v when negative)
+    u32 mag = 0;
+    for (int k = start; k < stop; k++) { const i32 v = d[k]; mag |= (u32)(v ^ (v >> 31)); }
+    const i32 s1 = hr15((i32)mag, 15);
     int w = bo[band + 1] - bo[band];
     w = w < 0 ? 0 : (w > 31 ? 31 : w);
     const i32 s2 = s_sub(s1, rom_bands_nrg_scale[w]);
