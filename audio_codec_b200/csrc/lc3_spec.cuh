@@ -52,8 +52,9 @@ template <class A> LC3_HD i32 band_one(i32 &en, A d, int band, const i16 *bo, co
     w = w < 0 ? 0 : (w > 31 ? 31 : w);
     const i32 s2 = s_sub(s1, rom_bands_nrg_scale[w]);
     i64 a64 = 0; // non-negative terms: the saturating L_mac0 chain equals the clamped exact sum
+    const int sl = s2 > 0 ? s2 : 0, sr = 16 + (s2 < 0 ? imin(-s2, 15) : 0); // the shift by s2 split once for the band, and the high half
     for (int i = start; i < stop; i++) {
-        const i32 t = hi16(l_shl_ns(d[i], s2));
+        const i32 t = (i32)((u32)d[i] << sl) >> sr;
         a64 += (i64)t * t;
     }
     i32 a = a64 > LC3_I32_MAX ? LC3_I32_MAX : (i32)a64;
