@@ -49,6 +49,8 @@ def load_library():
             getattr(L, n).argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.lc3plus_enc_batch.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p,
                                         C.c_size_t, C.c_void_p]
+        L.lc3plus_enc_fresh_noalloc.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t,
+                                                C.c_void_p, C.c_size_t, C.c_void_p]
         L.lc3plus_kernel_launches.restype = C.c_longlong
         L.lc3plus_last_error.restype = C.c_char_p
         L.lc3plus_set_chunk_frames.argtypes = [C.c_int]
@@ -197,6 +199,15 @@ def enc_batch(encoders, n_frames, pcm, stream_stride_bytes, bits, out, out_strea
                             out_stream_stride_bytes, nb)
     if r:
         raise LC3Error(r, "lc3plus_enc_batch")
+
+
+def enc_fresh_noalloc(samplerate, frame_dms, bitrate, bits, n_streams, n_frames, d_pcm, stream_stride_bytes, d_out,
+                      out_stream_stride_bytes, cuda_stream=None):
+    """lc3plus_enc_fresh_noalloc: fresh mono streams, device pointers only, nothing allocated, nothing synchronised."""
+    r = load_library().lc3plus_enc_fresh_noalloc(samplerate, frame_dms, bitrate, bits, n_streams, n_frames, int(d_pcm),
+                                                 stream_stride_bytes, int(d_out), out_stream_stride_bytes, cuda_stream)
+    if r:
+        raise LC3Error(r, "lc3plus_enc_fresh_noalloc")
 
 
 # ---- bitstream containers of the reference tool (include/lc3plus_b200.h, SURVEY.md 8-f1); host only

@@ -652,6 +652,7 @@ long long lc3plus_kernel_launches(void) { return g.launches; }
 void lc3plus_profile_enable(int on) { g.prof_on = on; memset(g.prof_ms, 0, sizeof(g.prof_ms)); }
 void lc3plus_profile_read(double *ms) { memcpy(ms, g.prof_ms, sizeof(g.prof_ms)); }
 const char *lc3plus_last_error(void) { return g.err; }
+void lc3b_set_error(const char *msg) { snprintf(g.err, sizeof(g.err), "%s", msg); } /* for lc3_k_noalloc.cu */
 void lc3plus_set_chunk_frames(int channel_frames) { if (channel_frames >= 32) { ctx_init(); g.chunk_frames = g.chunk_frames_host = channel_frames; } }
 
 /* `lc3plus_` spellings */

@@ -99,6 +99,25 @@ LC3_Error lc3plus_enc_batch(LC3_Enc *const *encoders, int n_streams, int n_frame
                             size_t stream_stride_bytes, int bitdepth, void *out, size_t out_stream_stride_bytes,
                             int *num_bytes);
 
+/* NEW -- no counterpart in the reference; added for callers that may not allocate
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * Encodes the first n_frames frames of n_streams FRESH mono streams (every stream starts from the power-on state of
+ * lc3_enc_init; nothing is carried to the next call) that share one configuration, byte for byte what lc3_enc_init +
+ * lc3_enc_set_frame_dms + lc3_enc_set_bitrate + n_frames x lc3_enc16/24 give.  The call allocates NOTHING (no cudaMalloc,
+ * cudaFree, pinned or library allocation) and does no host<->device copy or synchronisation: it queues one memset and the
+ * chain's kernels on `cuda_stream` (a cudaStream_t; NULL = the default stream) and returns; synchronise that stream before
+ * reading `out`.  All scratch -- stream state, lane tables, the kernels' work buffers -- lives in one static 7 MiB device
+ * array that every GPU loading the library holds until exit.  Limits: n_streams <= LC3PLUS_NOALLOC_MAX_STREAMS and
+ * (n_streams rounded up to a multiple of 32) * n_frames <= LC3PLUS_NOALLOC_MAX_CHANNEL_FRAMES, else LC3_ERROR with the
+ * reason in lc3plus_last_error().  pcm and out MUST be device pointers, laid out as for lc3plus_enc_batch (mono).
+ * Every call on a GPU shares the array, which keeps the previous call's contents (the state part is cleared at the start
+ * of each call): calls that overlap on the GPU -- different streams, or threads -- race; serialise them. */
+#define LC3PLUS_NOALLOC_MAX_STREAMS 64
+#define LC3PLUS_NOALLOC_MAX_CHANNEL_FRAMES 1024
+LC3_Error lc3plus_enc_fresh_noalloc(int samplerate, int frame_dms, int bitrate, int bitdepth, int n_streams, int n_frames,
+                                    const void *pcm, size_t stream_stride_bytes, void *out, size_t out_stream_stride_bytes,
+                                    void *cuda_stream);
+
 /* NEW: returns the device state of an encoder to the library's pool. */
 void lc3plus_enc_release(LC3_Enc *encoder);
 /* NEW: number of kernels launched by this process so far (for benchmarks' gpu_launches). */
