@@ -653,7 +653,15 @@ void lc3plus_profile_enable(int on) { g.prof_on = on; memset(g.prof_ms, 0, sizeo
 void lc3plus_profile_read(double *ms) { memcpy(ms, g.prof_ms, sizeof(g.prof_ms)); }
 const char *lc3plus_last_error(void) { return g.err; }
 void lc3b_set_error(const char *msg) { snprintf(g.err, sizeof(g.err), "%s", msg); } /* for lc3_k_noalloc.cu */
-void lc3plus_set_chunk_frames(int channel_frames) { if (channel_frames >= 32) { ctx_init(); g.chunk_frames = g.chunk_frames_host = channel_frames; } }
+void lc3plus_set_chunk_frames(int channel_frames)
+{ /* >= 32: both chunk sizes; 0: back to the defaults */
+    pthread_mutex_lock(&g_lock);
+    if (!ctx_init()) {
+        if (channel_frames >= 32) g.chunk_frames = g.chunk_frames_host = channel_frames;
+        else if (channel_frames == 0) { g.chunk_frames = 5 << 15; g.chunk_frames_host = 1 << 16; }
+    }
+    pthread_mutex_unlock(&g_lock);
+}
 
 /* `lc3plus_` spellings */
 LC3_Error lc3plus_enc_init(LC3_Enc *e, int fs, int ch) { return lc3_enc_init(e, fs, ch); }

@@ -93,6 +93,30 @@ def run_refbench(pcm_block, n_streams, n_frames, threads, repeat):
     return float(o[2]), float(o[1])
 
 
+VERIFY_STREAMS = (0, 7, 31, 32, 63, 64, 1000, 2047, 4094, 4095)   # 7 and 63 open with 50 frames of digital silence
+
+
+def verify_against_reference(pcm, out, frames, repeat, what):
+    """Byte-compare some streams of `out` [S, frames, NBYTES] (the bitstreams of the `repeat`-th pass over `pcm`, state carried
+    from pass to pass) with the unmodified reference encoder run over the same passes (oracle/_ref/refbench ... out.bin).
+    Returns (streams, frames) verified; a mismatch ends the benchmark with a non-zero exit code."""
+    if refbench_path() is None:
+        return 0, 0
+    idx = sorted({s for s in VERIFY_STREAMS if s < pcm.shape[0]})
+    block = np.ascontiguousarray(pcm[idx, :frames * N])
+    with tempfile.TemporaryDirectory(dir="/tmp") as d:
+        block.tofile(os.path.join(d, "pcm.raw"))
+        subprocess.run([refbench_path(), os.path.join(d, "pcm.raw"), str(FS), str(DMS), str(BITRATE), str(len(idx)), str(frames),
+                        str(min(len(idx), os.cpu_count() or 1)), os.path.join(d, "out.bin"), str(repeat)], capture_output=True, check=True)
+        want = np.fromfile(os.path.join(d, "out.bin"), dtype=np.uint8).reshape(len(idx), frames, NBYTES)
+    got = np.asarray(out)[idx]
+    if not np.array_equal(got, want):
+        bad = [(idx[i], int(np.argmax((got[i] != want[i]).any(axis=1)))) for i in range(len(idx)) if not np.array_equal(got[i], want[i])]
+        print(f"bench.py: {what}: output differs from the reference encoder at (stream, first frame) {bad[:8]}", file=sys.stderr)
+        sys.exit(3)
+    return len(idx), len(idx) * frames
+
+
 def cpu_reference_rate(pcm, frames, target_s):
     """Bounded sample of the workload on all host cores: calibrate, then one run of about target_s seconds."""
     cores = os.cpu_count() or 1
@@ -216,6 +240,8 @@ def main():
     prof = ac.profile_read()
     ac.profile_enable(False)
     launches = ac.kernel_launches() - l0
+    last_out = d_out.cpu().numpy() if rank == 0 else None     # bitstreams of the last timed step, checked after the timing legs
+    passes = args.warmup + args.steps                          # every step encodes the same PCM again, state carried
     barrier()
     dev_s = max_over_ranks(prof["span"] / 1e3)
     wall_s = max_over_ranks(wall)
@@ -232,10 +258,11 @@ def main():
     for _ in range(3):
         step_dev()
     torch.cuda.synchronize()
+    passes += 4
     alone = ac.profile_read()
     ac.profile_enable(False)
     del os.environ["LC3PLUS_B200_CHAIN"]
-    ac.set_chunk_frames(args.chunk if args.chunk else 1 << 17)
+    ac.set_chunk_frames(args.chunk if args.chunk else 0)   # 0: the library's defaults
     barrier()
 
     # end to end: pinned host PCM in, pinned host bitstreams out, same call
@@ -251,6 +278,7 @@ def main():
             ac.enc_batch(encs, F, h_pcm.data_ptr(), F * N * 2, 16, h_out.data_ptr(), F * NBYTES)
         torch.cuda.synchronize()
         e2e_s = max_over_ranks(time.perf_counter() - t0)
+        passes += 1 + ksteps
         barrier()
         e2e = {"value": float(S) * F * ksteps * world / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": S * F * N * 2,
                "d2h_bytes_per_step": S * F * NBYTES, "steps": ksteps,
@@ -260,6 +288,15 @@ def main():
         if dist is not None:
             dist.destroy_process_group()
         return
+
+    # the timed bytes are the reference encoder's bytes: device-resident leg (last timed step) and end-to-end leg (last step)
+    v_streams, v_frames = verify_against_reference(pcm, last_out, F, args.warmup + args.steps, "device-resident leg")
+    verified = {"verified_streams": v_streams, "verified_frames": v_frames,
+                "verified_against": "unmodified ETSI reference encoder (oracle/_ref/refbench) over the same %d passes of the PCM, "
+                                    "streams %s of rank 0" % (args.warmup + args.steps, list(VERIFY_STREAMS))}
+    if e2e is not None:
+        e_streams, e_frames = verify_against_reference(pcm, h_out.numpy(), F, passes, "end-to-end leg")
+        e2e["verified_streams"], e2e["verified_frames"] = e_streams, e_frames
 
     peaks = {}
     try:
@@ -308,6 +345,7 @@ def main():
                        "l2": "per-step input 393 MB > 126 MB L2 (no flush needed)"},
             "realtime_channels": value / 100.0, "wall_ms_per_step": 1e3 * wall_s / args.steps,
             "e2e": e2e, "gpu_launches": int(launches), "clocks": sm_clock, "roofline": roofline}
+    line.update(verified)
     if world == 1 and not args.no_cpu_baseline and refbench_path() is not None:
         rate, cores, sample = cpu_reference_rate(pcm, F, 12.0)
         line["cpu_baseline"] = {"value": rate, "unit": "frames/s", "cores": cores, "kind": "reference", "sample": sample}
