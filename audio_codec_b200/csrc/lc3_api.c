@@ -22,6 +22,7 @@ struct LC3_Enc { /* lives in the caller's block; device state is referenced by s
     int slot[2];
     int dirty;          /* configuration words not yet mirrored to the device pool */
     int batch_mark;     /* scratch for duplicate detection inside one batch call */
+    int last_bits;      /* bit depth of the frames encoded so far (0: none yet): one encoder, one bit depth */
     LC3Cfg cfg;
 };
 
@@ -37,6 +38,7 @@ typedef struct {
     int dirty_lo, dirty_hi;        /* tile range of cfg_host not yet uploaded */
     int *free_list, n_free, next_fresh;
     int32_t *reset_list; int n_reset, cap_reset;
+    int32_t *areset_list; int n_areset, cap_areset; /* slots whose attack-detector state set_bitrate cleared (fx/setup_enc_lc3.c:266-275) */
     /* per-call lane tables: host (pinned) and device */
     size_t lanes_cap;
     int32_t *h_slot, *d_slot, *h_ostride, *d_ostride;
@@ -201,6 +203,14 @@ static int flush_pending(void)
         CU((cudaError_t)lc3k_launch_reset(g.st32, g.st16, g.hist16, g.hist32, (const int32_t *)g.d_bfi, g.n_reset, g.stream));
         g.launches++;
         g.n_reset = 0;
+    }
+    if (g.n_areset) { /* after the power-on reset: a slot may be in both lists */
+        if (ensure((void **)&g.d_bfi, &g.bfi_cap, (size_t)g.n_areset * 4, 0)) return 1;
+        CU(cudaMemcpyAsync(g.d_bfi, g.areset_list, (size_t)g.n_areset * 4, cudaMemcpyHostToDevice, g.stream));
+        CU(cudaStreamSynchronize(g.stream)); /* areset_list is pageable */
+        CU((cudaError_t)lc3k_launch_attack_reset(g.st32, (const int32_t *)g.d_bfi, g.n_areset, g.stream));
+        g.launches++;
+        g.n_areset = 0;
     }
     if (g.dirty_hi >= g.dirty_lo) {
         size_t off = (size_t)g.dirty_lo * CFG_N * 32, n = (size_t)(g.dirty_hi - g.dirty_lo + 1) * CFG_N * 32;
@@ -425,6 +435,12 @@ static LC3_Error run_batch(struct LC3_Enc *const *encs, int n_streams, int n_fra
         if (!encs[i]) return LC3_NULL_ERROR;
         if (encs[i]->magic != LC3B_MAGIC) return LC3_ERROR;
         if (!encs[i]->cfg.br_set) return LC3_BITRATE_UNSET_ERROR;
+        if (encs[i]->last_bits && encs[i]->last_bits != bits) {
+            /* the reference carries the MDCT overlap across an lc3_enc16 <-> lc3_enc24 switch (fx/enc_lc3.c:35-83); here the two
+             * input widths keep their history in different pools, so the switch is refused rather than coded differently */
+            snprintf(g.err, sizeof(g.err), "encoder %d: bit depth changed from %d to %d (one encoder, one bit depth: re-initialise it)", i, encs[i]->last_bits, bits);
+            return LC3_ERROR;
+        }
     }
     pthread_mutex_lock(&g_lock);
     LC3_Error ret = LC3_ERROR;
@@ -494,6 +510,7 @@ static LC3_Error run_batch(struct LC3_Enc *const *encs, int n_streams, int n_fra
         }
     }
     if (cu_fail(cudaStreamSynchronize(g.stream), "sync")) goto done;
+    for (int i = 0; i < n_streams; i++) encs[i]->last_bits = bits;
     if (num_bytes)
         for (int i = 0; i < n_streams; i++) {
             int nb = lc3cfg_num_bytes(&encs[i]->cfg);
@@ -575,7 +592,24 @@ LC3_Error lc3_enc_set_bitrate(LC3_Enc *encoder, int bitrate)
     if (encoder == NULL) return LC3_NULL_ERROR;
     if (encoder->magic != LC3B_MAGIC) return LC3_ERROR;
     int r = lc3cfg_set_bitrate(&encoder->cfg, bitrate);
-    if (r == 0) encoder->dirty = 1;
+    if (r == 0) {
+        encoder->dirty = 1;
+        /* the reference clears the attack detector's state right here whenever the new bitrate switches it off, frames in
+         * between or not (fx/setup_enc_lc3.c:266-275): queue the slot for a clear before the next batch */
+        pthread_mutex_lock(&g_lock);
+        for (int ch = 0; ch < encoder->cfg.channels; ch++) {
+            if (!encoder->cfg.attack_reset[ch]) continue;
+            encoder->cfg.attack_reset[ch] = 0;
+            if (g.n_areset == g.cap_areset) {
+                int nc = g.cap_areset ? g.cap_areset * 2 : 1024;
+                int32_t *a = (int32_t *)realloc(g.areset_list, (size_t)nc * 4);
+                if (!a) { pthread_mutex_unlock(&g_lock); return LC3_ERROR; }
+                g.areset_list = a; g.cap_areset = nc;
+            }
+            g.areset_list[g.n_areset++] = encoder->slot[ch];
+        }
+        pthread_mutex_unlock(&g_lock);
+    }
     return (LC3_Error)r;
 }
 LC3_Error lc3_enc_set_frame_dms(LC3_Enc *encoder, int frame_ms)

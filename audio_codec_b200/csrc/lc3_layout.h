@@ -111,6 +111,8 @@ int lc3k_launch_back(const LC3K_Batch *b, void *stream);
 int lc3k_launch_fec(const LC3K_Batch *b, void *stream);     /* error protection of the finished payloads, in place in the output (only when a lane has CFG_EP) */
 /* set the listed state slots to their power-on values (fx/setup_enc_lc3.c:38-66) */
 int lc3k_launch_reset(int32_t *st32, int16_t *st16, int16_t *hist16, int32_t *hist32, const int32_t *slots, int n, void *stream);
+/* clear the attack detector's state words of the listed slots (fx/setup_enc_lc3.c:266-275) */
+int lc3k_launch_attack_reset(int32_t *st32, const int32_t *slots, int n, void *stream);
 #ifdef __cplusplus
 }
 #endif

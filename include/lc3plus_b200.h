@@ -11,6 +11,8 @@
  *     the per-channel signal state lives in device memory owned by the library.  Call lc3plus_enc_release
  *     when an encoder is no longer needed (the reference has no such call because it owns no memory).
  *   - `scratch` is accepted and ignored.
+ *   - One encoder, one bit depth: after lc3_enc16 frames, lc3_enc24 on the same encoder (or the reverse) returns LC3_ERROR
+ *     instead of carrying the MDCT overlap across the switch as the reference does (fx/enc_lc3.c:35-83); re-initialise it.
  *   - There is no CPU fallback: every encode call needs a CUDA device and returns LC3_ERROR if the
  *     device path fails.
  *   - Error protection (lc3_enc_set_ep_mode, modes 1-4, and lc3_enc_set_ep_mode_request) is implemented on the
