@@ -47,8 +47,11 @@ def load_library():
             getattr(L, n).argtypes = [C.c_void_p]
         for n in ("lc3_enc16", "lc3_enc24"):
             getattr(L, n).argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
-        L.lc3plus_enc_batch.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p,
-                                        C.c_size_t, C.c_void_p]
+        for n in ("lc3plus_enc_batch", "lc3plus_enc_batch_async"):
+            getattr(L, n).argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p,
+                                      C.c_size_t, C.c_void_p]
+        L.lc3plus_set_device.argtypes = [C.c_int]
+        L.lc3plus_enc_get_device.argtypes = [C.c_void_p]
         L.lc3plus_enc_fresh_noalloc.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t,
                                                 C.c_void_p, C.c_size_t, C.c_void_p]
         L.lc3plus_kernel_launches.restype = C.c_longlong
@@ -75,8 +78,23 @@ def kernel_launches():
     return int(load_library().lc3plus_kernel_launches())
 
 
-def profile_enable(on=True):
-    load_library().lc3plus_profile_enable(1 if on else 0)
+def profile_enable(level=2):
+    """0/False off, 1 device span only (asynchronous calls stay asynchronous), 2/True per-kernel events as well"""
+    load_library().lc3plus_profile_enable(2 if level is True else int(level))
+
+
+def set_device(device):
+    """lc3plus_set_device: encoders created by this thread from now on live on `device` (-1: the current CUDA device)."""
+    r = load_library().lc3plus_set_device(int(device))
+    if r:
+        raise LC3Error(r, "lc3plus_set_device")
+
+
+def sync():
+    """lc3plus_sync: wait for every batch queued with enc_batch(..., wait=False)."""
+    r = load_library().lc3plus_sync()
+    if r:
+        raise LC3Error(r, "lc3plus_sync")
 
 
 def profile_read():
@@ -104,6 +122,7 @@ class Encoder:
         if r:
             raise LC3Error(r, "lc3_enc_init")
         self._live = True
+        self._scratch = C.create_string_buffer(16)   # must not be NULL (fx/lc3.c:250); never used by this library
         r = L.lc3_enc_set_frame_dms(self.h, frame_dms)
         if r:
             raise LC3Error(r, "lc3_enc_set_frame_dms")
@@ -153,6 +172,10 @@ class Encoder:
         return load_library().lc3_enc_get_real_bitrate(self.h)
 
     @property
+    def device(self):
+        return load_library().lc3plus_enc_get_device(self.h)
+
+    @property
     def delay(self):
         return load_library().lc3_enc_get_delay(self.h)
 
@@ -167,7 +190,7 @@ class Encoder:
             ptrs[c] = frame[c].ctypes.data
         out = np.zeros(870, dtype=np.uint8)
         n = C.c_int(-1 if lost else 0)
-        r = (L.lc3_enc16 if bits == 16 else L.lc3_enc24)(self.h, ptrs, out.ctypes.data, C.byref(n), None)
+        r = (L.lc3_enc16 if bits == 16 else L.lc3_enc24)(self.h, ptrs, out.ctypes.data, C.byref(n), self._scratch)
         if r:
             raise LC3Error(r, "lc3_enc")
         return out[:n.value].copy()
@@ -189,14 +212,14 @@ class EncoderArray:
         return len(self.encoders)
 
 
-def enc_batch(encoders, n_frames, pcm, stream_stride_bytes, bits, out, out_stream_stride_bytes, num_bytes=None):
-    """lc3plus_enc_batch.  encoders: list of Encoder or an EncoderArray.  pcm/out: numpy arrays or device addresses.
-    num_bytes: optional int32 array [S*n_frames]."""
+def enc_batch(encoders, n_frames, pcm, stream_stride_bytes, bits, out, out_stream_stride_bytes, num_bytes=None, wait=True):
+    """lc3plus_enc_batch (wait=False: lc3plus_enc_batch_async, results valid after sync()).  encoders: list of Encoder or an
+    EncoderArray.  pcm/out: numpy arrays or device addresses.  num_bytes: optional int32 array [S*n_frames]."""
     L = load_library()
     arr = encoders.arr if isinstance(encoders, EncoderArray) else (C.c_void_p * len(encoders))(*[e.h.value for e in encoders])
     nb = num_bytes.ctypes.data if num_bytes is not None else None
-    r = L.lc3plus_enc_batch(arr, len(encoders), n_frames, _addr(pcm), stream_stride_bytes, bits, _addr(out),
-                            out_stream_stride_bytes, nb)
+    r = (L.lc3plus_enc_batch if wait else L.lc3plus_enc_batch_async)(arr, len(encoders), n_frames, _addr(pcm), stream_stride_bytes, bits,
+                                                                     _addr(out), out_stream_stride_bytes, nb)
     if r:
         raise LC3Error(r, "lc3plus_enc_batch")
 

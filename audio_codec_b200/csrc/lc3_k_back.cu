@@ -96,7 +96,8 @@ static int done() { return (int)cudaGetLastError(); }
 
 extern "C" int lc3k_launch_quant(const LC3K_Batch *b, void *stream)
 {
-    static bool attr_set = false;
+    static bool attr_dev[64] = {false}; // the attribute is per device
+    int attr_d = 0; cudaGetDevice(&attr_d); bool &attr_set = attr_dev[attr_d & 63];
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(k_quant, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(QuantSmem));
         if (e != cudaSuccess) return (int)e;
@@ -113,7 +114,8 @@ extern "C" int lc3k_launch_fec(const LC3K_Batch *b, void *stream)
 }
 extern "C" int lc3k_launch_back(const LC3K_Batch *b, void *stream)
 {
-    static bool attr_set = false;
+    static bool attr_dev[64] = {false}; // the attribute is per device
+    int attr_d = 0; cudaGetDevice(&attr_d); bool &attr_set = attr_dev[attr_d & 63];
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(k_back, cudaFuncAttributeMaxDynamicSharedMemorySize, BACK_SMEM_MAX);
         if (e != cudaSuccess) return (int)e;

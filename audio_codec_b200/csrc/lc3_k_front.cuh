@@ -82,7 +82,8 @@ template <int N> static int front_launch(const LC3K_Batch *b, cudaStream_t s)
 // (tns_launch below) follow as their own launches, each one lane per channel-frame
 template <int N> static int front_launch_tiled(const LC3K_Batch *b, cudaStream_t s)
 {
-    static bool attr_set = false;
+    static bool attr_dev[64] = {false}; // the attribute is per device
+    int attr_d = 0; cudaGetDevice(&attr_d); bool &attr_set = attr_dev[attr_d & 63];
     const size_t smem = MdctTile<N>::smem_bytes;
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(k_mdct<N, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -176,7 +176,8 @@ extern "C" int lc3k_launch_scalar(const LC3K_Batch *b, void *stream)
 }
 extern "C" int lc3k_launch_pitch(const LC3K_Batch *b, void *stream)
 {
-    static bool attr_set = false;
+    static bool attr_dev[64] = {false}; // the attribute is per device
+    int attr_d = 0; cudaGetDevice(&attr_d); bool &attr_set = attr_dev[attr_d & 63];
     const size_t smem = PITCH_WARPS * sizeof(PitchShared);
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(k_pitch<16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -10,7 +10,7 @@
  *   - The encoder block the caller allocates (lc3_enc_get_size bytes) holds configuration and a handle;
  *     the per-channel signal state lives in device memory owned by the library.  Call lc3plus_enc_release
  *     when an encoder is no longer needed (the reference has no such call because it owns no memory).
- *   - `scratch` is accepted and ignored.
+ *   - `scratch` must not be NULL (the reference returns LC3_NULL_ERROR, fx/lc3.c:250, and so does this library); it is not used.
  *   - One encoder, one bit depth: after lc3_enc16 frames, lc3_enc24 on the same encoder (or the reverse) returns LC3_ERROR
  *     instead of carrying the MDCT overlap across the switch as the reference does (fx/enc_lc3.c:35-83); re-initialise it.
  *   - There is no CPU fallback: every encode call needs a CUDA device and returns LC3_ERROR if the
@@ -101,6 +101,24 @@ LC3_Error lc3plus_enc_batch(LC3_Enc *const *encoders, int n_streams, int n_frame
                             size_t stream_stride_bytes, int bitdepth, void *out, size_t out_stream_stride_bytes,
                             int *num_bytes);
 
+/* NEW: the same call without the wait at its end.  It returns when the batch is queued; `out` and `num_bytes` are valid after
+ * lc3plus_sync().  The caller's `pcm` (if in host memory) must stay untouched until then.  Consecutive calls on one device
+ * form one continuing pipeline -- the next call's copies and first kernels overlap the previous call's last ones -- and at
+ * most two calls per device are in flight: a third waits for the first to finish. */
+LC3_Error lc3plus_enc_batch_async(LC3_Enc *const *encoders, int n_streams, int n_frames, const void *pcm,
+                                  size_t stream_stride_bytes, int bitdepth, void *out, size_t out_stream_stride_bytes,
+                                  int *num_bytes);
+/* NEW: waits for everything queued by lc3plus_enc_batch_async on every device; LC3_ERROR if any of it failed. */
+LC3_Error lc3plus_sync(void);
+/* NEW ("one thread/stream-of-work per device"): selects the CUDA device on which the encoders that THIS
+ * THREAD initialises from now on keep their state (-1: back to the default, the thread's current CUDA device).  The library
+ * keeps one context per device.  lc3plus_enc_batch accepts encoders of several devices in one call when pcm and out are host
+ * buffers: each device's share is queued by its own host thread and the call joins them.  With device buffers, make one
+ * call per device (lc3plus_enc_batch_async lets one host thread keep several devices busy). */
+LC3_Error lc3plus_set_device(int device);
+/* NEW: the device an encoder lives on (-1 for an invalid handle). */
+int lc3plus_enc_get_device(const LC3_Enc *encoder);
+
 /* NEW -- no counterpart in the reference; added for callers that may not allocate
  * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
  * Encodes the first n_frames frames of n_streams FRESH mono streams (every stream starts from the power-on state of
@@ -120,7 +138,9 @@ LC3_Error lc3plus_enc_fresh_noalloc(int samplerate, int frame_dms, int bitrate, 
                                     const void *pcm, size_t stream_stride_bytes, void *out, size_t out_stream_stride_bytes,
                                     void *cuda_stream);
 
-/* NEW: returns the device state of an encoder to the library's pool. */
+/* NEW: returns the device state of an encoder to the library's pool.  Optional: the library remembers which state belongs
+ * to which encoder block by the block's address, so initialising a block again (or a new block at an address that was freed
+ * without this call) hands the old state back first. */
 void lc3plus_enc_release(LC3_Enc *encoder);
 /* NEW: number of kernels launched by this process so far (for benchmarks' gpu_launches). */
 long long lc3plus_kernel_launches(void);
@@ -129,7 +149,7 @@ long long lc3plus_kernel_launches(void);
  * quant, back kernel ms (each bracketed by events
  * on the stream it was launched on; chunks overlap, so these can sum to more than the span), start-of-first-chunk to
  * end-of-last-chunk span ms, calls, chunks}; enable() also clears the accumulators. */
-void lc3plus_profile_enable(int on);
+void lc3plus_profile_enable(int level); /* 0 off; 1 device span only (calls stay asynchronous); 2 per-kernel events too */
 void lc3plus_profile_read(double *ms);
 /* NEW: last CUDA error string seen by the library ("" if none). */
 const char *lc3plus_last_error(void);
