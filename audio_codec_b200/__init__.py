@@ -6,4 +6,4 @@ API (ctypes) used by the tests and bench.py; there is no Python or CPU encode pa
 """
 from .api import (LC3Error, Encoder, EncoderArray, enc_batch, kernel_launches, last_error, load_library, library_path,  # noqa: F401
                   profile_enable, profile_read, set_chunk_frames, container_header, container_frames,
-                  write_bitstream_file, read_switching_file, enc_fresh_noalloc, set_device, sync)
+                  write_bitstream_file, read_switching_file, enc_fresh_noalloc, set_device, sync, profile_read_device, set_bitrate_many)

@@ -51,6 +51,8 @@ def load_library():
             getattr(L, n).argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p,
                                       C.c_size_t, C.c_void_p]
         L.lc3plus_set_device.argtypes = [C.c_int]
+        L.lc3plus_profile_read_device.argtypes = [C.c_int, C.c_void_p]
+        L.lc3plus_enc_set_bitrate_many.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         L.lc3plus_enc_get_device.argtypes = [C.c_void_p]
         L.lc3plus_enc_fresh_noalloc.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t,
                                                 C.c_void_p, C.c_size_t, C.c_void_p]
@@ -102,6 +104,20 @@ def profile_read():
     ms = (C.c_double * 13)()
     load_library().lc3plus_profile_read(ms)
     return dict(zip(("stage", "fir", "scalar", "pitch", "mdct", "sns", "tns", "rate", "quant", "back", "span", "calls", "chunks"), list(ms)))
+
+
+def profile_read_device(device):
+    ms = (C.c_double * 13)()
+    load_library().lc3plus_profile_read_device(int(device), ms)
+    return dict(zip(("stage", "fir", "scalar", "pitch", "mdct", "sns", "tns", "rate", "quant", "back", "span", "calls", "chunks"), list(ms)))
+
+
+def set_bitrate_many(encoders, bitrates):
+    """lc3plus_enc_set_bitrate_many: encoders is an EncoderArray, bitrates an int32 array of the same length."""
+    b = np.ascontiguousarray(bitrates, dtype=np.int32)
+    r = load_library().lc3plus_enc_set_bitrate_many(encoders.arr, len(encoders), b.ctypes.data)
+    if r:
+        raise LC3Error(r, "lc3plus_enc_set_bitrate_many")
 
 
 def set_chunk_frames(n):

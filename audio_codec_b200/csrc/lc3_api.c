@@ -957,6 +957,22 @@ void lc3plus_profile_read(double *ms)
     for (int d = 0; d < LC3B_MAX_DEV; d++)
         if (g_ctx[d]) for (int k = 0; k < N_KERNELS + 3; k++) ms[k] += g_ctx[d]->prof_ms[k];
 }
+void lc3plus_profile_read_device(int device, double *ms)
+{
+    lc3plus_sync();
+    memset(ms, 0, sizeof(double) * (N_KERNELS + 3));
+    if (device >= 0 && device < LC3B_MAX_DEV && g_ctx[device]) memcpy(ms, g_ctx[device]->prof_ms, sizeof(double) * (N_KERNELS + 3));
+}
+LC3_Error lc3plus_enc_set_bitrate_many(LC3_Enc *const *encoders, int n, const int *bitrates)
+{ /* lc3_enc_set_bitrate on each encoder (fx/codec_exe.c:340-349 does this per frame from its switching file) */
+    if (!encoders || !bitrates) return LC3_NULL_ERROR;
+    LC3_Error first = LC3_OK;
+    for (int i = 0; i < n; i++) {
+        const LC3_Error r = lc3_enc_set_bitrate(encoders[i], bitrates[i]);
+        if (r != LC3_OK && first == LC3_OK) first = r;
+    }
+    return first;
+}
 const char *lc3plus_last_error(void) { return g_err; }
 void lc3b_set_error(const char *msg) { snprintf(g_err, sizeof(g_err), "%s", msg); } /* for lc3_k_noalloc.cu */
 void lc3plus_set_chunk_frames(int channel_frames)

@@ -150,7 +150,11 @@ long long lc3plus_kernel_launches(void);
  * on the stream it was launched on; chunks overlap, so these can sum to more than the span), start-of-first-chunk to
  * end-of-last-chunk span ms, calls, chunks}; enable() also clears the accumulators. */
 void lc3plus_profile_enable(int level); /* 0 off; 1 device span only (calls stay asynchronous); 2 per-kernel events too */
-void lc3plus_profile_read(double *ms);
+void lc3plus_profile_read(double *ms);                        /* summed over the devices in use */
+void lc3plus_profile_read_device(int device, double *ms);    /* one device's share */
+/* NEW: lc3_enc_set_bitrate(encoders[i], bitrates[i]) for i < n in one call (mid-stream switching of many streams between two
+ * batches, as fx/codec_exe.c:340-349 does per frame from its switching file); returns the first error, applies the rest. */
+LC3_Error lc3plus_enc_set_bitrate_many(LC3_Enc *const *encoders, int n, const int *bitrates);
 /* NEW: last CUDA error string seen by the library ("" if none). */
 const char *lc3plus_last_error(void);
 /* NEW: upper bound on channel-frames processed per internal chunk (defaults: 163840 when the PCM is already on the
