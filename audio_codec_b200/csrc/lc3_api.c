@@ -408,6 +408,7 @@ static int run_bucket(Ctx *g, int key, struct LC3_Enc *const *encs, const int *i
     memset(&b, 0, sizeof(b));
     lc3cfg_fill_batch(c0, &b);
     b.bits = bits;
+    b.stage_full = !(bits == 16 && N >= 160);
     b.n_lanes = (int)n_lanes;
     b.n_tiles = (int)((n_lanes + 31) / 32);
     b.max_bytes = max_bytes;

@@ -34,20 +34,36 @@ template <int N, int BITS> __global__ void __launch_bounds__(256, 2) k_mdct(LC3K
 {
     typedef MdctTile<N> G;
     extern __shared__ __align__(16) i32 mt_smem[];
-    i32 *X = mt_smem, *mx = X + 32 * G::S, *mn = mx + G::PARTS * 32, *smx = mn + G::PARTS * 32;
+    unsigned long long *bar = reinterpret_cast<unsigned long long *>(mt_smem); // 16 bytes reserved in front of X
+    i32 *X = mt_smem + 4, *mx = X + 32 * G::S, *mn = mx + G::PARTS * 32, *smx = mn + G::PARTS * 32;
     i32 *ben = smx + G::PARTS * 32, *bexp = ben + 32 * G::BROW;
-    i16 *s_tw = (i16 *)(bexp + 32 * G::BROW), *s_sn = s_tw + G::TW_LEN, *s_W = s_sn + G::SN_LEN;
+    i16 *s_tw = (i16 *)(bexp + 32 * G::BROW), *s_sn = s_tw + G::TW_LEN, *s_W = s_sn + G::SN_LEN, *s_win = s_W + G::W_LEN;
     const int f = blockIdx.x / b.n_tiles, tile = blockIdx.x % b.n_tiles, t = threadIdx.x, w = t >> 5, l = t & 31;
+    const bool rows = BITS == 16 && !b.stage_full; // PCM rows straight from the caller's buffer (bulk asynchronous copies)
+    if (rows) mt_stage_rows<N>(b, f, tile, t, X, bar);
     {
         const MtTabs R = mt_rom_tabs<N>();
         for (int i = t; i < G::TW_LEN; i += G::THREADS) s_tw[i] = R.tw[i];
         for (int i = t; i < G::SN_LEN; i += G::THREADS) s_sn[i] = R.sn[i];
         for (int i = t; i < G::W_LEN; i += G::THREADS) s_W[i] = R.W[i];
+        if (rows) for (int i = t; i < b.W_len; i += G::THREADS) s_win[i] = rom_win[b.W_off + i];
     }
     const MtTabs T = {s_tw, s_sn, s_W};
     LC3_DBG_ENTER(1, w == 0 ? (int)blockIdx.x : LC3_DBG_ROWS); // one row per tile, written by its first warp
-    mt_fold<N, BITS>(b, f, tile, t, X, mx, mn);
-    __syncthreads();
+    if (rows) {
+        mt_wait_rows(bar);
+        __syncthreads(); // the tables, too
+#pragma unroll 1
+        for (int j = 0; j < 4; j++) {
+            const int r = w + 8 * j;
+            mt_fill_row<N>(b, f, tile, r, mt_row_is_bulk<N>(b, f, tile, r), X);
+            mt_fold_row<N>(b, r, tile * LC3K_LANES + r < b.n_lanes, X, mx, mn, s_win);
+        }
+        __syncwarp();
+    } else {
+        mt_fold<N, BITS>(b, f, tile, t, X, mx, mn);
+        __syncthreads();
+    }
 #pragma unroll 1
     for (int j = 0; j < 4; j++) mt_pre<N>(X, mx, mn, w + 8 * j, l, T);
     __syncwarp();

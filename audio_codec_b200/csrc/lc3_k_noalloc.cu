@@ -96,6 +96,7 @@ extern "C" LC3_Error lc3plus_enc_fresh_noalloc(int samplerate, int frame_dms, in
     LC3K_Batch b;
     memset(&b, 0, sizeof(b));
     lc3cfg_fill_batch(&c, &b);
+    b.stage_full = !(bitdepth == 16 && c.N >= 160);
     b.bits = bitdepth; b.n_lanes = n_streams; b.n_tiles = n_tiles; b.n_frames = n_frames; b.frame0 = 0;
     b.max_bytes = c.ch[0][CFG_TARGET_BYTES];
     // state region first (zeroed as one block)

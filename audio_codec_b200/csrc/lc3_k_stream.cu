@@ -32,6 +32,7 @@ template <class T> __global__ void __launch_bounds__(256) k_stage(LC3K_Batch b)
             for (int i = ty; i < N; i += 8) { dst[(size_t)i * 32 + tx] = h[i]; h[i] = last[i]; }
         }
     }
+    if (!b.stage_full) return; // history only: every later frame is read from the caller's PCM where it lies
     const int c_end = min(total, (int)(blockIdx.y + 1) * STAGE_SEG);
     for (int c0 = blockIdx.y * STAGE_SEG; c0 < c_end; c0 += 32) {
 #pragma unroll
@@ -154,7 +155,7 @@ extern "C" int lc3k_launch_reset(int32_t *st32, int16_t *st16, int16_t *hist16, 
 }
 extern "C" int lc3k_launch_stage(const LC3K_Batch *b, void *stream)
 {
-    const dim3 grid(b->n_tiles, (b->n_frames * b->N + STAGE_SEG - 1) / STAGE_SEG);
+    const dim3 grid(b->n_tiles, b->stage_full ? (b->n_frames * b->N + STAGE_SEG - 1) / STAGE_SEG : 1);
     if (b->bits == 16) k_stage<int16_t><<<grid, 256, 0, (cudaStream_t)stream>>>(*b);
     else k_stage<int32_t><<<grid, 256, 0, (cudaStream_t)stream>>>(*b);
     return done();

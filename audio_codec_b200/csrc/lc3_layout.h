@@ -68,6 +68,8 @@ typedef struct {
     int n_lanes, n_tiles, n_frames;
     int max_bytes;            /* largest CFG_TARGET_BYTES of the bucket's lanes (sizes k_back's shared-memory frame buffers) */
     int frame0;               /* index of this chunk's first frame within the caller's batch */
+    int stage_full;           /* 1: k_stage copies the chunk's PCM into pcm_t (24-bit input, frames shorter than 160 samples);
+                                 0: history frame only -- the tile MDCT pulls its PCM rows from the caller's buffer with bulk copies */
     /* state pool */
     const int32_t *slot;      /* [n_lanes] */
     const int32_t *cfg;       /* pool, CFG_N words per slot */

@@ -21,6 +21,7 @@
 #include "lc3_mdct.cuh"
 #include "lc3_stages.cuh"
 #include "lc3_spec.cuh"
+#include "lc3_warp.cuh"
 
 namespace lc3k {
 
@@ -40,7 +41,8 @@ template <int N> struct MdctTile {
     // per-band energies of the tile before alignment: mantissa and exponent [32 frames][BROW], row stride odd
     static constexpr int BROW = 65;
     static constexpr size_t smem_words = 32 * S + 3 * PARTS * 32 + 2 * 32 * BROW;
-    static constexpr size_t smem_bytes = smem_words * sizeof(i32) + (size_t)(TW_LEN + SN_LEN + W_LEN) * sizeof(i16);
+    static constexpr int WIN_LEN = 2 * N; // low-delay window (2N - la_zeroes entries), for the row-wise fold: lane-varying indices
+    static constexpr size_t smem_bytes = 16 /* mbarrier of the row staging */ + smem_words * sizeof(i32) + (size_t)(TW_LEN + SN_LEN + W_LEN + WIN_LEN) * sizeof(i16);
     static_assert(N == 160 || N == 240 || N == 320 || N == 480, "8-column FFT lengths only");
 };
 
@@ -123,6 +125,134 @@ template <int N, int BITS> LC3_HD void mt_fold(const LC3K_Batch &b, int f, int t
     }
     mx[part * 32 + lane] = rg.mx; mn[part * 32 + lane] = rg.mn;
 }
+
+// ---- fold, 16-bit input, rows pulled from the caller's PCM: WARP = frame.  The 2N samples the fold of a frame needs
+// (previous frame | current frame) are contiguous in the caller's [stream][sample] buffer, so they are brought into the
+// frame's own row of X by ONE bulk asynchronous copy per row (cp.async.bulk + mbarrier, issued by mt_stage_rows in the
+// kernel; 16-byte aligned rows only, others and the chunk's first frame -- whose previous frame is the staged history -- are
+// filled in by the warp).  The fold then runs in place: every lane gathers the samples of its outputs into registers, the
+// warp synchronises, the outputs overwrite the row.  This replaces the transposed copy of the whole PCM (k_stage) and the
+// fold's strided global loads.
+template <int N> struct MtRowIn { // where row r's staged samples sit: in[N + s] = sample s relative to the frame's start, s in [-N, N)
+    LC3_HDM static i16 *at(i32 *X, int r) { return reinterpret_cast<i16 *>(X + r * MdctTile<N>::S) + ((r & 1) ? 4 : 0); } // 16-byte aligned
+};
+
+template <int N> LC3_HD void mt_fold_row(const LC3K_Batch &b, int r, bool valid, i32 *X, i32 *mx, i32 *mn, const i16 *win /* &rom_win[b.W_off], in shared memory in the kernel */)
+{
+    typedef MdctTile<N> G;
+    constexpr int m = N / 2, K = (m + 31) / 32;
+    i32 *y = X + r * G::S;
+    const i16 *in = MtRowIn<N>::at(X, r) + N;
+    const int memLen = b.mdct_mem_len, z = 2 * N - b.W_len;
+    LC3_PERLANE(i32, v1, K);
+    LC3_PERLANE(i32, v2, K);
+    LC3_LANES(l)
+#pragma unroll
+        for (int k = 0; k < K; k++) {
+            const int i = l + 32 * k;
+            i32 a = 0, c = 0;
+            if (valid && i < m) { // same three expressions as mdct_frame() / mt_fold()
+                a = in[i - memLen] * win[i] - in[2 * m - 1 - i - memLen] * win[2 * m - 1 - i];
+                c = in[2 * m - memLen + i] * win[2 * m + i];
+                if (i >= z) c += in[4 * m - memLen - 1 - i] * win[4 * m - 1 - i]; // the window is zero below z (la_zeroes)
+            }
+            LC3_PL(v1, k, l) = a; LC3_PL(v2, k, l) = c;
+        }
+    LC3_LANES_END
+    LC3_LANES(l)
+        Range rg; range_init(rg);
+#pragma unroll
+        for (int k = 0; k < K; k++) {
+            const int i = l + 32 * k;
+            if (i < m) {
+                y[mt_ridx(m + i)] = LC3_PL(v1, k, l); y[mt_ridx(m - 1 - i)] = LC3_PL(v2, k, l);
+                range_add(rg, LC3_PL(v1, k, l)); range_add(rg, LC3_PL(v2, k, l));
+            }
+        }
+        // reduced over the warp below: the slots of row r in the per-part arrays all receive the row's range
+        LC3_PL(v1, 0, l) = rg.mx; LC3_PL(v2, 0, l) = rg.mn;
+    LC3_LANES_END
+    {
+#if defined(__CUDA_ARCH__)
+        const i32 rmx = __reduce_max_sync(0xffffffffu, v1[0]), rmn = __reduce_min_sync(0xffffffffu, v2[0]);
+        const int l = (int)(threadIdx.x & 31);
+        if (l < G::PARTS) { mx[l * 32 + r] = rmx; mn[l * 32 + r] = rmn; }
+        __syncwarp();
+#else
+        i32 rmx = v1[0][0], rmn = v2[0][0];
+        for (int l = 1; l < 32; l++) { rmx = imax(rmx, v1[0][l]); rmn = imin(rmn, v2[0][l]); }
+        for (int p = 0; p < G::PARTS; p++) { mx[p * 32 + r] = rmx; mn[p * 32 + r] = rmn; }
+#endif
+    }
+}
+
+// what the bulk copy did not bring into row r: the previous frame of the chunk's first frame (staged history, tile-interleaved
+// prefix of pcm_t), and whole rows whose address in the caller's buffer is not 16-byte aligned.  Warp-cooperative.
+template <int N> LC3_HD void mt_fill_row(const LC3K_Batch &b, int f, int tile, int r, bool bulk_done, i32 *X)
+{
+    const int li = tile * LC3K_LANES + r;
+    if (li >= b.n_lanes) return;
+    i16 *in = MtRowIn<N>::at(X, r);
+    const i16 *cur = (const i16 *)b.pcm + b.pcm_off[li] + (size_t)(b.frame0 + f) * N; // sample 0 of the frame
+    SV<const i16> hist = tile_view((const i16 *)b.pcm_t, (size_t)tile, (size_t)(b.n_frames + 1) * N, r);
+    LC3_LANES(l)
+        if (f == 0) for (int s = l; s < N; s += 32) in[s] = hist[s];
+        else if (!bulk_done) for (int s = l; s < N; s += 32) in[s] = cur[s - N];
+        if (!bulk_done) for (int s = l; s < N; s += 32) in[N + s] = cur[s];
+    LC3_LANES_END
+}
+
+// true when row r of (tile, f) was brought in by the bulk copy (mt_stage_rows applies the same test)
+template <int N> LC3_HD bool mt_row_is_bulk(const LC3K_Batch &b, int f, int tile, int r)
+{
+    const int li = tile * LC3K_LANES + r;
+    if (li >= b.n_lanes) return false;
+    const i16 *cur = (const i16 *)b.pcm + b.pcm_off[li] + (size_t)(b.frame0 + f) * N;
+    return (reinterpret_cast<uintptr_t>(f == 0 ? cur : cur - N) & 15) == 0;
+}
+
+#if defined(__CUDACC__)
+__device__ __forceinline__ u32 mt_smem_addr(const void *p) { return (u32)__cvta_generic_to_shared(p); }
+// Thread t < 32 of the block issues the bulk copy of row t and returns whether it did; every thread then waits on `bar`.
+template <int N> __device__ __forceinline__ bool mt_stage_rows(const LC3K_Batch &b, int f, int tile, int t, i32 *X, unsigned long long *bar)
+{
+    bool issued = false;
+    if (t == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mt_smem_addr(bar)) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (t < 32) {
+        const int li = tile * LC3K_LANES + t;
+        const i16 *src = nullptr;
+        u32 bytes = 0;
+        i16 *dst = MtRowIn<N>::at(X, t);
+        if (li < b.n_lanes) {
+            const i16 *cur = (const i16 *)b.pcm + b.pcm_off[li] + (size_t)(b.frame0 + f) * N;
+            if (f == 0) { src = cur; bytes = 2 * N; dst += N; }      // the previous frame comes from the staged history
+            else { src = cur - N; bytes = 4 * N; }
+            if ((reinterpret_cast<unsigned long long>(src) & 15) != 0) bytes = 0; // mt_fill_row loads such rows
+        }
+        const u32 total = __reduce_add_sync(0xffffffffu, bytes);
+        if (t == 0) asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mt_smem_addr(bar)), "r"(total) : "memory");
+        __syncwarp();
+        if (bytes) {
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(mt_smem_addr(dst)), "l"(src), "r"(bytes), "r"(mt_smem_addr(bar)) : "memory");
+            issued = true;
+        }
+    }
+    return issued;
+}
+__device__ __forceinline__ void mt_wait_rows(unsigned long long *bar)
+{
+    u32 ok;
+    do {
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }"
+                     : "=r"(ok) : "r"(mt_smem_addr(bar)) : "memory");
+    } while (!ok);
+}
+#endif
 
 // ---- block shift + pre-twiddle of frame fr: lane l takes pairs l, l+32, ...
 template <int N> LC3_HD void mt_pre(i32 *X, const i32 *mx, const i32 *mn, int fr, int l, const MtTabs &T)

@@ -37,6 +37,17 @@ template <int N, int BITS> static void run_mdct_tile(const LC3K_Batch &b, int f,
     static std::vector<i32> sm(G::smem_bytes / sizeof(i32));
     i32 *X = sm.data(), *mx = X + 32 * G::S, *mn = mx + G::PARTS * 32;
     const MtTabs T = mt_rom_tabs<N>();
+    if (BITS == 16 && !b.stage_full) { // rows from the caller's PCM (the kernel's bulk copies are a memcpy here)
+        for (int r = 0; r < 32; r++) {
+            const int li = tile * 32 + r;
+            if (li < b.n_lanes && f > 0) {
+                const i16 *cur = (const i16 *)b.pcm + b.pcm_off[li] + (size_t)(b.frame0 + f) * N;
+                memcpy(MtRowIn<N>::at(X, r), cur - N, 4 * N);
+            }
+            mt_fill_row<N>(b, f, tile, r, f > 0, X);
+            mt_fold_row<N>(b, r, li < b.n_lanes, X, mx, mn, &rom_win[b.W_off]);
+        }
+    } else
     for (int t = 0; t < G::THREADS; t++) mt_fold<N, BITS>(b, f, tile, t, X, mx, mn);
     for (int t = 0; t < G::THREADS; t++) { const int w = t >> 5, l = t & 31; for (int j = 0; j < 4; j++) mt_pre<N>(X, mx, mn, w + 8 * j, l, T); }
     for (int t = 0; t < G::THREADS; t++) { const int w = t >> 5, l = t & 31; mt_leaf<N>(X, w + 8 * (l >> 3), l & 7); }
@@ -136,6 +147,7 @@ extern "C" int hostsim_encode(void *p, const void *pcm, int bits, int n_frames, 
     lc3cfg_fill_batch(&s->cfg, &b);
     const int N = b.N, nb = lc3cfg_num_bytes(&s->cfg);
     b.bits = bits;
+    b.stage_full = !(bits == 16 && N >= 160);
     b.n_lanes = s->n_streams; b.n_tiles = (s->n_streams + 31) / 32; b.n_frames = n_frames;
     b.slot = s->slot.data(); b.cfg = s->cfgw.data(); b.st32 = s->st32.data(); b.st16 = s->st16.data();
     b.hist16 = s->hist16.data(); b.hist32 = s->hist32.data();
@@ -162,8 +174,8 @@ extern "C" int hostsim_encode(void *p, const void *pcm, int bits, int n_frames, 
             SV<i16> h = slot_view(b.hist16, slot, LC3K_MAX_N);
             const int16_t *src = (const int16_t *)pcm + (size_t)li * n_frames * N;
             for (int i = 0; i < N; i++) t[i] = h[i];
-            for (int i = 0; i < n_frames * N; i++) t[N + i] = src[i];
-            for (int i = 0; i < N; i++) h[i] = t[n_frames * N + i];
+            if (b.stage_full) for (int i = 0; i < n_frames * N; i++) t[N + i] = src[i];
+            for (int i = 0; i < N; i++) h[i] = src[(n_frames - 1) * N + i];
         } else {
             SV<i32> t = tile_view((i32 *)b.pcm_t, tile, per_tile, lane);
             SV<i32> h = slot_view(b.hist32, slot, LC3K_MAX_N);
