@@ -7,7 +7,6 @@
 extern "C" {
 #include "lc3_config.h"
 }
-#include "lc3_body_serial.cuh"
 #include "lc3_body_frame.cuh"
 #include "lc3_pitch_warp.cuh"
 #include "lc3_rate_warp.cuh"
@@ -190,17 +189,11 @@ extern "C" int hostsim_encode(void *p, const void *pcm, int bits, int n_frames, 
     AriTabs T = {(const u8 *)rom_ari_lookup, ari_cf};
     static PitchShared psh;
     static RateShared rsh;
-    const bool lane_serial = getenv("HOSTSIM_LANE_SERIAL") != 0; // older one-lane-per-stream bodies, kept for debugging
     b.pcm = pcm;
     std::vector<int64_t> pcm_off(s->n_streams);
     for (int i = 0; i < s->n_streams; i++) pcm_off[i] = (int64_t)i * n_frames * N;
     b.pcm_off = pcm_off.data();
-    if (lane_serial) {
-        for (int tile = 0; tile < b.n_tiles; tile++)
-            for (int lane = 0; lane < 32; lane++) {
-                if (bits == 16) pitch_body<16>(b, tile, lane); else pitch_body<24>(b, tile, lane);
-            }
-    } else {
+    {
         std::vector<int16_t> r12(ftl * 128);
         b.r12 = r12.data();
         if (bits == 16) { // three passes as the kernels run them
@@ -218,19 +211,10 @@ extern "C" int hostsim_encode(void *p, const void *pcm, int bits, int n_frames, 
     }
     for (int f = 0; f < n_frames; f++)
         for (int tile = 0; tile < b.n_tiles; tile++) {
-            if (lane_serial) { // the original lane-per-frame MDCT for every frame length
-                for (int lane = 0; lane < 32; lane++) {
-                    if (bits == 16) run_front<16>(b, f, tile, lane); else run_front<24>(b, f, tile, lane);
-                }
-            } else if (bits == 16) run_front_tile<16>(b, f, tile);
+            if (bits == 16) run_front_tile<16>(b, f, tile);
             else run_front_tile<24>(b, f, tile);
         }
-    if (lane_serial) {
-        for (int tile = 0; tile < b.n_tiles; tile++)
-            for (int lane = 0; lane < 32; lane++) rate_body(b, tile, lane, (const u8 *)rom_ari_lookup, rom_ari_bits);
-    } else {
-        for (int li = 0; li < b.n_lanes; li++) rate_warp_body(b, li, rsh, (const u8 *)rom_ari_lookup, rom_ari_bits);
-    }
+    for (int li = 0; li < b.n_lanes; li++) rate_warp_body(b, li, rsh, (const u8 *)rom_ari_lookup, rom_ari_bits);
     for (int f = 0; f < n_frames; f++)
         for (int tile = 0; tile < b.n_tiles; tile++) {
             // the tile quantiser (k_quant in lc3_k_back.cu), phase by phase
