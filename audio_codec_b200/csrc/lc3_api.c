@@ -17,7 +17,9 @@
 
 #define LC3B_MAGIC 0x4c433362u
 #define LC3B_MAX_DEV 16
+#ifndef N_PIPES
 #define N_PIPES 3
+#endif
 #define N_WORK 9
 #define N_BUCKETS 15
 enum { K_STAGE = 0, K_FIR, K_SCALAR, K_PITCH, K_FRONT, K_SNS, K_TNS, K_RATE, K_QUANT, K_BACK, N_KERNELS };
@@ -84,7 +86,7 @@ static pthread_mutex_t g_lock = PTHREAD_MUTEX_INITIALIZER; /* context creation, 
 static char g_err[256];
 static __thread int tl_device = -1;
 static int g_prof = 0;
-static int g_chunk_dev = 5 << 15, g_chunk_host = 1 << 16; /* channel-frames per chunk: input on the device | in host memory */
+static int g_chunk_dev = 5 << 15, g_chunk_host = 25 << 13; /* channel-frames per chunk: input on the device | in host memory */
 static unsigned g_call_id = 0;
 
 static int cu_fail(cudaError_t e, const char *what)
@@ -979,7 +981,7 @@ void lc3b_set_error(const char *msg) { snprintf(g_err, sizeof(g_err), "%s", msg)
 void lc3plus_set_chunk_frames(int channel_frames)
 { /* >= 32: both chunk sizes; 0: back to the defaults */
     if (channel_frames >= 32) g_chunk_dev = g_chunk_host = channel_frames;
-    else if (channel_frames == 0) { g_chunk_dev = 5 << 15; g_chunk_host = 1 << 16; }
+    else if (channel_frames == 0) { g_chunk_dev = 5 << 15; g_chunk_host = 25 << 13; }
     { const char *e = getenv("LC3PLUS_B200_HOST_CHUNK"); if (channel_frames == 0 && e && atoi(e) >= 32) g_chunk_host = atoi(e); } /* tuning aid */
 }
 
