@@ -57,22 +57,25 @@ template <class XS> LC3_HD void resamp12k8(XS xs, int mem_in_len, PitchState &st
     for (int k = 0; k < 24; k++) st.r12k8_mem_out[k] = out[len + k];
 }
 
-// <a,b>/sqrt(<a,a><b,b>) in Q15 (fx/olpa_fx.c:126-155, fx/ltpf_coder_fx.c:108-141)
+// <a,b>/sqrt(<a,a><b,b>) in Q15 (fx/olpa_fx.c:126-155, fx/ltpf_coder_fx.c:108-141).
+// sum1 and sum2 are energies plus one (>= 1): their norm is a leading-zero count, the normalising shifts cannot saturate, and
+// the fractional products have a positive factor, so the -1 x -1 case of Mpy_32_32 cannot occur; the exponents are sums of a
+// few values below 64.  tests/hostsim/primcheck.cpp compares this with the operator-by-operator form.
 LC3_HD i32 normcorr_q15(i32 sum0, i32 sum1, i32 sum2, int sum1_prenorm, i32 sc1_in)
 {
-    i32 sc1 = sc1_in, sc2;
-    if (!sum1_prenorm) { sc1 = l_norm(sum1); sum1 = l_shl(sum1, sc1); }
-    sc2 = l_norm(sum2);
-    sum2 = l_shl(sum2, sc2);
-    i32 prod = mpy32x32(sum1, sum2);
-    i32 sh = l_norm(prod);
-    prod = l_shl(prod, sh);
-    i32 pe = s_sub(62, s_add(s_add(sc1, sc2), sh));
-    i32 inv = m_isqrt32(prod, &pe);
-    i32 sc0 = l_norm(sum0);
-    sum0 = l_shl(sum0, sc0);
-    prod = mpy32x32(sum0, inv);
-    pe = s_add(s_sub(31, sc0), pe);
+    i32 sc1 = sc1_in;
+    if (!sum1_prenorm) { sc1 = clz32((u32)sum1) - 1; sum1 = (i32)((u32)sum1 << sc1); }
+    const i32 sc2 = clz32((u32)sum2) - 1;
+    sum2 = (i32)((u32)sum2 << sc2);
+    i32 prod = (i32)(((i64)sum1 * sum2) >> 31); // both factors in [2^30, 2^31): the product is in [2^29, 2^31)
+    const i32 sh = clz32((u32)prod) - 1;
+    prod = (i32)((u32)prod << sh);
+    i32 pe = 62 - (sc1 + sc2 + sh);
+    const i32 inv = m_isqrt32(prod, &pe);       // > 0
+    const i32 sc0 = l_norm(sum0);
+    sum0 = (i32)((u32)sum0 << sc0);
+    prod = (i32)(((i64)sum0 * inv) >> 31);
+    pe = (31 - sc0) + pe;
     if (prod == 0 || s_sub(l_norm(prod), pe) >= 0) return s_max(0, l_round(l_shl(prod, pe)));
     return 32767;
 }

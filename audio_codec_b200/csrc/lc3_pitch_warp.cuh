@@ -28,7 +28,7 @@ struct PitchShared {
     i16 olpa[2][4 + 130 + 64 + 2]; // 6.4 kHz history + new samples, ping-pong; 4 samples of pad in front (phase E reads 2 of them)
     i16 ltpf[2][4 + 264 + 128 + 4]; // 12.8 kHz history + new samples, ping-pong; 4 samples of pad in front (lag windows read 3)
     i16 ac[32];                   // LTPF normalised correlations
-    i32 xc[128];                  // LTPF cross-correlation partial sums [lane][4 lags]
+    i32 xc[224];                  // OLPA autocorrelation partial sums [7 lags][lane], then LTPF cross-correlation partial sums [lane][4 lags]
     i16 dd[2 + 160 + 2];          // attack detector: decimated signal, two samples of history first
 };
 
@@ -40,6 +40,31 @@ template <class T> struct RawPcm {
     int N, first;
     LC3_HDM i32 operator()(int i) const { return (i < 0 && first) ? (i32)hist[N + i] : (i32)cur[i]; }
 };
+
+// OLPA autocorrelation, lags 17..114 (olpa_fx.c:101-122): lane = (group of 7 consecutive lags, half of the samples).
+// 14 groups x 2 halves = 28 lanes hold 7 accumulators each; a lane walks SEG samples with a seven-sample window of the lagged
+// signal sliding through registers (everything unrolled: one load per new window sample, no register rotation).  A half has
+// at most 32 products of |v| <= 2^12 operands per lag, the two halves are added afterwards: far below 2^31, any order.
+template <int SEG> LC3_HD void olpa_acf_half(const i16 *s, int l, i32 *xc /* [7][32] */)
+{
+    const int g = l >> 1, half = l & 1;
+    i32 a[7] = {0, 0, 0, 0, 0, 0, 0};
+    if (g < 14) {
+        const i16 *x = s + half * SEG;   // x[m] = s[half * SEG + m]
+        const i16 *q = x - (17 + 7 * g); // q[m - j] = the sample lag (17 + 7 g + j) behind x[m]
+        i32 w[SEG + 6];                  // w[k] = q[k - 6]
+#pragma unroll
+        for (int k = 0; k < SEG + 6; k++) w[k] = q[k - 6];
+#pragma unroll
+        for (int m = 0; m < SEG; m++) {
+            const i32 xv = x[m];
+#pragma unroll
+            for (int j = 0; j < 7; j++) a[j] += xv * w[m - j + 6];
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 7; j++) xc[j * 32 + l] = a[j];
+}
 
 // PRE = true (16-bit input only): the resampler FIR, the high-pass recursion and the attack detector have already
 // run in their own passes (fir_warp_body, scalar_body below) and b.r12 holds the high-passed 12.8 kHz samples;
@@ -228,29 +253,20 @@ template <int BITS, bool PRE> LC3_HD void pitch_warp_body(const LC3K_Batch &b, i
             // ---- E. autocorrelation, lags 17..114: lane = lag (olpa_fx.c:101-122, :157-172)
             const i16 *s = dms == 25 ? s6 - 16 : s6;
             const i32 lo = s_max(17, s_sub(olpa_pitch, 4)), hi = s_min(114, s_add(olpa_pitch, 4));
-            // Each lane takes four consecutive lags and slides a four-sample window of the lagged signal through
-            // registers: two shared-memory loads per four products.  (Lanes 0..24 cover lags 17..116; the two lags
-            // past 114 read the pad in front of the history and are dropped.)
             LC3_LANES(l)
+                if (acflen6 == 64) olpa_acf_half<32>(s, l, sh.xc);
+                else if (acflen6 == 48) olpa_acf_half<24>(s, l, sh.xc);
+                else olpa_acf_half<16>(s, l, sh.xc);
+            LC3_LANES_END
+            LC3_LANES(l) // totals of the pair's two halves; lane (g, half) weighs lags j = half, half + 2, .. of its group
                 i64 kw = LC3_I32_MIN * (i64)4294967296LL, k2 = kw;
-                const int n0 = 17 + 4 * l;
-                if (n0 <= 114) {
-                    // <= 80 products of |v| <= 2^12 operands: below 2^31, the L_mac0 chain cannot saturate
-                    i32 a0 = 0, a1 = 0, a2 = 0, a3 = 0;
-                    const i16 *q = s - n0; // q[m - j] = s[m - (n0 + j)]
-                    i32 w1 = q[-1], w2 = q[-2], w3 = q[-3];
-#pragma unroll 4
-                    for (int m = 0; m < acflen6; m++) {
-                        const i32 x = s[m], w0 = q[m];
-                        a0 += x * w0; a1 += x * w1; a2 += x * w2; a3 += x * w3;
-                        w3 = w2; w2 = w1; w1 = w0;
-                    }
-                    const i32 accs[4] = {a0, a1, a2, a3};
+                const int g = l >> 1, half = l & 1;
+                if (g < 14) {
 #pragma unroll
-                    for (int j = 0; j < 4; j++) {
-                        const int n = n0 + j;
-                        if (n > 114) break;
-                        const i32 acc = accs[j];
+                    for (int j = 0; j < 7; j++) {
+                        if ((j & 1) != half) continue;
+                        const int n = 17 + 7 * g + j;
+                        const i32 acc = sh.xc[j * 32 + l] + sh.xc[j * 32 + (l ^ 1)];
                         const i64 a = argmax_key(mpy32x16(acc, rom_olpa_weight[n - 17]), n);
                         kw = a > kw ? a : kw;
                         if (n >= lo && n <= hi) { const i64 c = argmax_key(acc, n); k2 = c > k2 ? c : k2; }

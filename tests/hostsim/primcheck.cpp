@@ -10,6 +10,7 @@
 #include "lc3_math.cuh"
 #include "lc3_fft.cuh"
 #include "lc3_rate.cuh"
+#include "lc3_pitch.cuh"
 
 using namespace lc3k;
 
@@ -33,6 +34,26 @@ static i32 log2_poly_ref(i32 f)
     }
     acc = l_mac0(acc >> 1, hi16(acc), 14506);
     return acc >> 5;
+}
+
+// operator-by-operator form of normcorr_q15 (fx/olpa_fx.c:126-155)
+static i32 normcorr_ref(i32 sum0, i32 sum1, i32 sum2, int sum1_prenorm, i32 sc1_in)
+{
+    i32 sc1 = sc1_in, sc2;
+    if (!sum1_prenorm) { sc1 = l_norm(sum1); sum1 = l_shl(sum1, sc1); }
+    sc2 = l_norm(sum2);
+    sum2 = l_shl(sum2, sc2);
+    i32 prod = mpy32x32(sum1, sum2);
+    i32 sh = l_norm(prod);
+    prod = l_shl(prod, sh);
+    i32 pe = s_sub(62, s_add(s_add(sc1, sc2), sh));
+    i32 inv = m_isqrt32(prod, &pe);
+    i32 sc0 = l_norm(sum0);
+    sum0 = l_shl(sum0, sc0);
+    prod = mpy32x32(sum0, inv);
+    pe = s_add(s_sub(31, sc0), pe);
+    if (prod == 0 || s_sub(l_norm(prod), pe) >= 0) return s_max(0, l_round(l_shl(prod, pe)));
+    return 32767;
 }
 
 static int fails = 0;
@@ -160,6 +181,26 @@ int main(int argc, char **argv)
         CHECK("rate_bounds", t_max < (1 << 26) && t_min > -(1 << 26), "t range");
         CHECK("rate_bounds", 4 * (2 * t_max) < 2147483647LL, "lane sum"); // four quadruples per lane, each t + (t - 0x460000)
         printf("ok rate_bounds en in [%d, %d]\n", lo, hi);
+    }
+    { // normcorr_q15: energies >= 1 of every magnitude, correlations of either sign, pre-normalised first energy too
+        const i32 edge[] = {1, 2, 3, 0x7fffffff, 0x40000000, 0x3fffffff, 0x10000, 0xffff, 12345};
+        const i32 edge0[] = {0, 1, -1, LC3_I32_MIN, LC3_I32_MAX, 0x40000000, -0x40000000, 77, -77};
+        for (i32 a : edge0) for (i32 b : edge) for (i32 c : edge) {
+            CHECK("normcorr_q15", normcorr_q15(a, b, c, 0, 0) == normcorr_ref(a, b, c, 0, 0), "%d %d %d", a, b, c);
+            const i32 n1 = l_norm(b);
+            CHECK("normcorr_q15", normcorr_q15(a, l_shl(b, n1), c, 1, n1) == normcorr_ref(a, l_shl(b, n1), c, 1, n1), "pre %d %d %d", a, b, c);
+        }
+        for (long it = 0; it < 20000000; it++) {
+            const int s1 = rnd() % 31, s2 = rnd() % 31, s0 = rnd() % 32;
+            const i32 b = (i32)((rnd() << 16 ^ rnd()) & 0x7fffffff) >> s1 | 1, c = (i32)((rnd() << 16 ^ rnd()) & 0x7fffffff) >> s2 | 1;
+            const i32 a = (i32)(rnd() << 16 ^ rnd()) >> s0;
+            const int pre = it & 1;
+            const i32 n1 = l_norm(b);
+            const i32 got = pre ? normcorr_q15(a, l_shl(b, n1), c, 1, n1) : normcorr_q15(a, b, c, 0, 0);
+            const i32 want = pre ? normcorr_ref(a, l_shl(b, n1), c, 1, n1) : normcorr_ref(a, b, c, 0, 0);
+            CHECK("normcorr_q15", got == want, "%d %d %d pre %d: %d vs %d", a, b, c, pre, got, want);
+        }
+        printf("ok normcorr_q15\n");
     }
     if (fails) { printf("%d mismatches\n", fails); return 1; }
     return 0;

@@ -13,5 +13,5 @@ def test_shortcuts_equal_operator_forms():
     subprocess.run(["make", "-s", "primcheck"], cwd=d, check=True)
     r = subprocess.run([os.path.join(d, "primcheck")], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:]
-    for name in ("quant_bin", "m_log2_poly", "l_round", "l_shl_plan", "fft_bound"):
+    for name in ("quant_bin", "m_log2_poly", "l_round", "l_shl_plan", "fft_bound", "normcorr_q15"):
         assert f"ok {name}" in r.stdout
