@@ -58,14 +58,14 @@ template <class T> __global__ void __launch_bounds__(256) k_stage(LC3K_Batch b)
 #ifndef PITCH_FRAME_SYNC
 #define PITCH_FRAME_SYNC 1
 #endif
-template <int BITS, bool PRE> __global__ void __launch_bounds__(32 * PITCH_WARPS, 2) k_pitch(LC3K_Batch b)
+template <int BITS, bool PRE, int DMS> __global__ void __launch_bounds__(32 * PITCH_WARPS, 2) k_pitch(LC3K_Batch b)
 {
     extern __shared__ __align__(16) unsigned char pitch_smem[];
     PitchShared *sh = reinterpret_cast<PitchShared *>(pitch_smem);
     const int w = threadIdx.x >> 5;
     LC3_DBG_ENTER(0, (int)blockIdx.x * PITCH_WARPS + w);
     const int live = min(PITCH_WARPS, b.n_lanes - (int)blockIdx.x * PITCH_WARPS); // warps of this block that own a stream
-    pitch_warp_body<BITS, PRE>(b, blockIdx.x * PITCH_WARPS + w, sh[w], PITCH_FRAME_SYNC ? 32 * live : 0);
+    pitch_warp_body<BITS, PRE, DMS>(b, blockIdx.x * PITCH_WARPS + w, sh[w], PITCH_FRAME_SYNC ? 32 * live : 0);
     LC3_DBG_LEAVE();
 }
 
@@ -175,21 +175,24 @@ extern "C" int lc3k_launch_scalar(const LC3K_Batch *b, void *stream)
     k_scalar<<<b->n_tiles, 32, 0, (cudaStream_t)stream>>>(*b);
     return done();
 }
-extern "C" int lc3k_launch_pitch(const LC3K_Batch *b, void *stream)
+template <int BITS, bool PRE, int DMS> static int pitch_launch(const LC3K_Batch *b, cudaStream_t stream)
 {
     static bool attr_dev[64] = {false}; // the attribute is per device
     int attr_d = 0; cudaGetDevice(&attr_d); bool &attr_set = attr_dev[attr_d & 63];
     const size_t smem = PITCH_WARPS * sizeof(PitchShared);
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(k_pitch<16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_pitch<24, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(k_pitch<BITS, PRE, DMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return (int)e;
         attr_set = true;
     }
-    const int blocks = (b->n_lanes + PITCH_WARPS - 1) / PITCH_WARPS;
-    if (b->bits == 16) k_pitch<16, true><<<blocks, 32 * PITCH_WARPS, smem, (cudaStream_t)stream>>>(*b);
-    else k_pitch<24, false><<<blocks, 32 * PITCH_WARPS, smem, (cudaStream_t)stream>>>(*b);
+    k_pitch<BITS, PRE, DMS><<<(b->n_lanes + PITCH_WARPS - 1) / PITCH_WARPS, 32 * PITCH_WARPS, smem, stream>>>(*b);
     return done();
+}
+extern "C" int lc3k_launch_pitch(const LC3K_Batch *b, void *stream)
+{ // one instance per input width and frame duration
+    cudaStream_t s = (cudaStream_t)stream;
+    if (b->bits == 16) return b->dms == 100 ? pitch_launch<16, true, 100>(b, s) : b->dms == 50 ? pitch_launch<16, true, 50>(b, s) : pitch_launch<16, true, 25>(b, s);
+    return b->dms == 100 ? pitch_launch<24, false, 100>(b, s) : b->dms == 50 ? pitch_launch<24, false, 50>(b, s) : pitch_launch<24, false, 25>(b, s);
 }
 extern "C" int lc3k_launch_rate(const LC3K_Batch *b, void *stream)
 {

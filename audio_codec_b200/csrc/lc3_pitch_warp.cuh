@@ -77,7 +77,9 @@ template <int SEG> LC3_HD void olpa_acf_half(const i16 *s, int l, i32 *xc /* [7]
 #else
 #define LC3_PITCH_SYNC() do { } while (0)
 #endif
-template <int BITS, bool PRE> LC3_HD void pitch_warp_body(const LC3K_Batch &b, int li, PitchShared &sh, int sync_threads = 0)
+// DMS = 25 / 50 / 100 fixes the frame duration at compile time (0: taken from the batch): every lane-strided loop of the body
+// then has a constant trip count and unrolls without the remainder bookkeeping a run-time bound needs.
+template <int BITS, bool PRE, int DMS = 0> LC3_HD void pitch_warp_body(const LC3K_Batch &b, int li, PitchShared &sh, int sync_threads = 0)
 {
     typedef typename std::conditional<BITS == 16, i16, i32>::type T;
     if (li >= b.n_lanes) return;
@@ -87,10 +89,10 @@ template <int BITS, bool PRE> LC3_HD void pitch_warp_body(const LC3K_Batch &b, i
     SV<i16> s16 = slot_view(b.st16, slot, ST16_N);
     SV<const i32> cfg = slot_view(b.cfg, slot, CFG_N);
     const i32 ltpf_enable = cfg[CFG_LTPF_ENABLE], attack_handling = cfg[CFG_ATTACK];
-    const int N = b.N, dms = b.dms, rl = b.r12k8_mem_in_len, ml = b.mdct_mem_len;
+    const int N = b.N, dms = DMS ? DMS : b.dms, rl = b.r12k8_mem_in_len, ml = b.mdct_mem_len;
     const int len = 32 * (dms / 25), len2 = len >> 1;
     const int olpa_len = dms == 25 ? 130 : 114, acflen6 = dms == 25 ? len2 + 16 : len2;
-    const int lt_len = b.ltpf_mem_in_len;
+    const int lt_len = DMS ? (DMS == 25 ? 232 + 32 : 232) : b.ltpf_mem_in_len;
     const int upfac = rom_resamp_params[b.fs_idx * 4 + 0], delay2 = 2 * rom_resamp_params[b.fs_idx * 4 + 1];
     const int off_int = rom_resamp_params[b.fs_idx * 4 + 2], off_frac = rom_resamp_params[b.fs_idx * 4 + 3];
 
