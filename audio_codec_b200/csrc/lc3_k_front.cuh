@@ -8,9 +8,19 @@ using namespace lc3k;
 // Large blocks on purpose (here and in k_tns, k_sns, k_back): these bodies are tens of thousands of instructions of
 // mostly straight-line code that every warp runs once, so the kernels are bound by instruction fetch unless the warps
 // of an SM walk through the code together and share the fetches (k_sns: "no instruction" stalls 9.7 -> 0, 1.24 -> 0.89 ms).
-#define FRONT_WARPS 16
-#define TNS_WARPS 24
-template <int N, int BITS> __global__ void __launch_bounds__(32 * FRONT_WARPS, 1) k_front(LC3K_Batch b)
+#ifndef FRONT_WARPS
+#define FRONT_WARPS 32 /* measured: 16 warps (128 registers) C3 94.6 / C4 86.4 M frames/s, 24 warps 101.2 / 93.3, 32 warps (64 registers) 104.7 / 95.6 */
+#endif
+#ifndef FRONT_BLOCKS
+#define FRONT_BLOCKS 1
+#endif
+#ifndef TNS_WARPS
+#define TNS_WARPS 32 /* measured at N = 480: 24 warps 1.11 ms, 32 warps (64 registers) 1.01, 12 x 2 blocks 1.12, 16 (128 registers) 1.35 */
+#endif
+#ifndef TNS_BLOCKS
+#define TNS_BLOCKS 1
+#endif
+template <int N, int BITS> __global__ void __launch_bounds__(32 * FRONT_WARPS, FRONT_BLOCKS) k_front(LC3K_Batch b)
 {
     const int warp = blockIdx.x * FRONT_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (warp >= b.n_frames * b.n_tiles) return;
@@ -18,7 +28,7 @@ template <int N, int BITS> __global__ void __launch_bounds__(32 * FRONT_WARPS, 1
 }
 
 // tile path, steps 2 and 3 (lc3_body_frame.cuh): one lane per channel-frame
-template <int N> __global__ void __launch_bounds__(32 * TNS_WARPS, 1) k_tns(LC3K_Batch b)
+template <int N> __global__ void __launch_bounds__(32 * TNS_WARPS, TNS_BLOCKS) k_tns(LC3K_Batch b)
 {
     const int warp = blockIdx.x * TNS_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (warp >= b.n_frames * b.n_tiles) return;

@@ -8,8 +8,13 @@ using namespace lc3k;
 
 // Large blocks on purpose: the body is ~15 000 instructions of straight-line code that every warp runs once, so the
 // kernel is bound by instruction fetch unless the warps of an SM walk through it together and share the fetches.
-#define SNS_WARPS 24
-__global__ void __launch_bounds__(32 * SNS_WARPS, 1) k_sns(LC3K_Batch b)
+#ifndef SNS_WARPS
+#define SNS_WARPS 12 /* measured: 24 x 1 block 0.73 ms, 12 x 2 blocks 0.67, 32 x 1 0.67, 16 x 1 (128 registers) 0.85, 8 x 3 0.77 */
+#endif
+#ifndef SNS_BLOCKS
+#define SNS_BLOCKS 2
+#endif
+__global__ void __launch_bounds__(32 * SNS_WARPS, SNS_BLOCKS) k_sns(LC3K_Batch b)
 {
     const int warp = blockIdx.x * SNS_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (warp >= b.n_frames * b.n_tiles) return;
