@@ -17,9 +17,9 @@
 
 #define LC3B_MAGIC 0x4c433362u
 #define LC3B_MAX_DEV 16
-#ifndef N_PIPES
-#define N_PIPES 3
-#endif
+#define N_PIPES 8      /* pipes that exist */
+#define N_PIPES_MIN 3  /* pipes in use: three chunks in flight (four measured slower on one bucket), more when a call has
+                          many small (sample rate, frame size) buckets, whose warp-per-stream kernels fill a fraction of the device */
 #define N_WORK 9
 #define N_BUCKETS 15
 enum { K_STAGE = 0, K_FIR, K_SCALAR, K_PITCH, K_FRONT, K_SNS, K_TNS, K_RATE, K_QUANT, K_BACK, N_KERNELS };
@@ -65,6 +65,7 @@ typedef struct {
         int used;               /* done_ev / state_ev have been recorded at least once */
     } pipe[N_PIPES];
     long long seq;              /* chunks queued so far (runs on across calls) */
+    int n_active, next_pipe, last_pipe; /* pipes in rotation for this call, the next one to use, the previous chunk's (-1: none) */
     cudaEvent_t call_ev;        /* this call's uploads are done */
     cudaEvent_t call_end_ev[2]; int call_end_used[2]; long long call_no;
     /* host-pointer calls: input copies queue on one stream, output copies on another */
@@ -210,6 +211,7 @@ static int ctx_create(Ctx *c, int device)
     CU(cudaStreamCreateWithFlags(&c->d2h, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&c->d2h_ev, cudaEventDisableTiming));
     c->dirty_lo = 1 << 30; c->dirty_hi = -1;
+    c->n_active = N_PIPES_MIN; c->next_pipe = 0; c->last_pipe = -1;
     return pool_grow(c, 4096);
 }
 
@@ -443,8 +445,8 @@ static int run_bucket(Ctx *g, int key, struct LC3_Enc *const *encs, const int *i
     const size_t ftl = (size_t)fc * b.n_tiles * 32;
     const size_t need[N_WORK] = {(size_t)b.n_tiles * 32 * (size_t)(fc + 1) * N * sb, ftl * PO_N * 4, ftl * N * 4, ftl * FO_N * 4,
                                  ftl * (N / 4) * 4, ftl * RO_N * 4, ftl * 128 * 2, ftl * N * 2, ftl * BEN_N * 4};
-    for (int k = 0; k < (n_chunks < N_PIPES ? n_chunks : N_PIPES); k++) {
-        const int p = (int)((g->seq + k) % N_PIPES);
+    for (int k = 0; k < (n_chunks < g->n_active ? n_chunks : g->n_active); k++) {
+        const int p = (g->next_pipe + k) % g->n_active;
         for (int i = 0; i < N_WORK; i++)
             if (g->pipe[p].work_cap[i] < need[i]) {
                 if (ctx_wait(g)) return 1; /* the buffer being replaced may be in use */
@@ -464,8 +466,10 @@ static int run_bucket(Ctx *g, int key, struct LC3_Enc *const *encs, const int *i
                                                                   lc3k_launch_front, lc3k_launch_sns, lc3k_launch_tns, lc3k_launch_rate, lc3k_launch_quant, lc3k_launch_back};
     for (int f0 = 0, c = 0, cf; f0 < n_frames; f0 += cf, c++) {
         cf = chunk_size(c, n_frames - f0, fc, ramp);
-        const long long seq = g->seq++;
-        const int p = (int)(seq % N_PIPES), pprev = (int)((seq + N_PIPES - 1) % N_PIPES);
+        g->seq++;
+        const int p = g->next_pipe % g->n_active, pprev = g->last_pipe;
+        g->next_pipe = (p + 1) % g->n_active;
+        g->last_pipe = p;
         const cudaStream_t par = g->pipe[p].par, ser = g->pipe[p].ser;
         void *const *w = g->pipe[p].work;
         /* the chunk that used these work buffers last is done with them (every kernel of this chunk follows its first one,
@@ -506,7 +510,7 @@ static int run_bucket(Ctx *g, int key, struct LC3_Enc *const *encs, const int *i
             if ((bits != 16 && (k == K_FIR || k == K_SCALAR)) /* fused into K_PITCH for 24-bit input */
                 || (N < 160 && (k == K_SNS || k == K_TNS))) { /* fused into K_FRONT for the short frames */
                 if (k_stateful[k]) { /* keep the chunk-to-chunk chain of this kernel's state events unbroken */
-                    if (g->pipe[pprev].used) CU(cudaStreamWaitEvent(st, g->pipe[pprev].state_ev[k], 0));
+                    if (pprev >= 0 && pprev != p) CU(cudaStreamWaitEvent(st, g->pipe[pprev].state_ev[k], 0));
                     CU(cudaEventRecord(g->pipe[p].state_ev[k], st));
                 }
                 continue;
@@ -520,7 +524,7 @@ static int run_bucket(Ctx *g, int key, struct LC3_Enc *const *encs, const int *i
             for (int j = 0; j < 2; j++)
                 if (dep[j] >= 0 && ran[dep[j]] && (k_stateful[dep[j]] ? ser : par) != st) CU(cudaStreamWaitEvent(st, g->pipe[p].hop_ev[dep[j]], 0));
             /* the same kernel of the chunk before (of this or an earlier call) has left the per-stream state it hands over */
-            if (k_stateful[k] && g->pipe[pprev].used && pprev != p) CU(cudaStreamWaitEvent(st, g->pipe[pprev].state_ev[k], 0));
+            if (k_stateful[k] && pprev >= 0 && pprev != p) CU(cudaStreamWaitEvent(st, g->pipe[pprev].state_ev[k], 0));
             if (kprof) CU(cudaEventRecord(g->ev[c * EPC + 2 * k], st));
             CU((cudaError_t)launch[k](&b, st));
             if (kprof) CU(cudaEventRecord(g->ev[c * EPC + 2 * k + 1], st));
@@ -587,6 +591,15 @@ static int run_on_device(DevJob *j)
         if (out_b > max_out) max_out = out_b;
     }
     CallState cs = {0, 0, 0};
+    {
+        unsigned seen = 0;
+        int nb = 0;
+        for (int i = 0; i < n; i++) {
+            const unsigned bit = 1u << (encs[idx[i]]->cfg.dms_idx * 5 + encs[idx[i]]->cfg.fs_idx);
+            if (!(seen & bit)) { seen |= bit; nb++; }
+        }
+        g->n_active = nb < N_PIPES_MIN ? N_PIPES_MIN : (nb > N_PIPES ? N_PIPES : nb);
+    }
     if (flush_pending(g, &cs.uploads)) return 1;
     cs.uploads = 0; /* flush_pending leaves nothing in flight */
 
@@ -609,6 +622,14 @@ static int run_on_device(DevJob *j)
         if (!chunked) {
             if (uniform && contiguous) {
                 CU(cudaMemcpy2DAsync(g->d_in[par2], stride, pcm, stride, max_in, rows, cudaMemcpyHostToDevice, g->up));
+            } else if (contiguous) {
+                /* rows of unequal length (mixed sample rates / frame sizes): one rectangle as wide as the longest row (a row
+                 * is `stride` bytes apart from the next, so reading past a shorter row's samples stays inside the buffer)
+                 * for all rows but the last, which is copied exactly */
+                const size_t wid = max_in < stride ? max_in : stride;
+                const size_t last_b = (size_t)encs[idx[n - 1]]->cfg.channels * n_frames * encs[idx[n - 1]]->cfg.N * sb;
+                if (rows > 1) CU(cudaMemcpy2DAsync(g->d_in[par2], stride, pcm, stride, wid, rows - 1, cudaMemcpyHostToDevice, g->up));
+                CU(cudaMemcpyAsync((char *)g->d_in[par2] + (rows - 1) * stride, pcm + (rows - 1) * stride, last_b, cudaMemcpyHostToDevice, g->up));
             } else {
                 for (int i = 0; i < n; i++) {
                     const size_t in_b = (size_t)encs[idx[i]]->cfg.channels * n_frames * encs[idx[i]]->cfg.N * sb, off = (idx[i] - row0) * stride;
@@ -647,6 +668,13 @@ static int run_on_device(DevJob *j)
     if (!rc && !out_dev && !chunked) {
         if (uniform && contiguous) {
             CU(cudaMemcpy2DAsync(out, ostride, d_out, ostride, max_out, rows, cudaMemcpyDeviceToHost, g->join));
+        } else if (contiguous) {
+            /* unequal rows: one rectangle as wide as the longest row for all rows but the last (the header says that the bytes
+             * of a row past its own frames, up to the longest row of the batch, are overwritten), the last row exactly */
+            const size_t wid = max_out < ostride ? max_out : ostride;
+            const size_t last_b = (size_t)n_frames * lc3cfg_num_bytes(&encs[idx[n - 1]]->cfg);
+            if (rows > 1) CU(cudaMemcpy2DAsync(out, ostride, d_out, ostride, wid, rows - 1, cudaMemcpyDeviceToHost, g->join));
+            CU(cudaMemcpyAsync(out + (rows - 1) * ostride, d_out + (rows - 1) * ostride, last_b, cudaMemcpyDeviceToHost, g->join));
         } else {
             for (int i = 0; i < n; i++) {
                 const size_t out_b = (size_t)n_frames * lc3cfg_num_bytes(&encs[idx[i]]->cfg), off = (idx[i] - row0) * ostride;

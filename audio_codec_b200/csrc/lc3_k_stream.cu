@@ -54,11 +54,13 @@ template <class T> __global__ void __launch_bounds__(256) k_stage(LC3K_Batch b)
 
 // per-stream passes: one warp per channel-stream.  14 warps per block, 2 blocks per SM: 28 x 148 = 4144 streams are
 // resident at once (the 4096-stream workload runs in one wave), and the warps of a block share instruction fetches.
+#ifndef PITCH_WARPS
 #define PITCH_WARPS 14
+#endif
 #ifndef PITCH_FRAME_SYNC
 #define PITCH_FRAME_SYNC 1
 #endif
-template <int BITS, bool PRE, int DMS> __global__ void __launch_bounds__(32 * PITCH_WARPS, 2) k_pitch(LC3K_Batch b)
+template <int BITS, bool PRE, int DMS> __global__ void __launch_bounds__(32 * PITCH_WARPS, 28 / PITCH_WARPS) k_pitch(LC3K_Batch b)
 {
     extern __shared__ __align__(16) unsigned char pitch_smem[];
     PitchShared *sh = reinterpret_cast<PitchShared *>(pitch_smem);

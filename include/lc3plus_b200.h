@@ -94,7 +94,9 @@ int lc3plus_enc_get_delay(const LC3_Enc *encoder);
  *   num_bytes           optional [n_streams*n_frames], stream-major.  On entry -1 marks "signal this frame as
  *                       lost" (the reference's in/out quirk, fx/lc3.c:253); on return the byte count.
  *   pcm / out may be host or device pointers (detected with cudaPointerGetAttributes); device pointers
- *   avoid the copies.  Encoders may differ in sample rate, frame size, bitrate and channel count; they are
+ *   avoid the copies.  With host buffers and streams of unequal size in one call, the bytes of an output row past its own
+ *   frames -- up to the length of the longest row of the batch, never past the row's stride -- are overwritten with
+ *   unspecified values.  Encoders may differ in sample rate, frame size, bitrate and channel count; they are
  *   bucketed internally.  An encoder may appear only once per call.
  */
 LC3_Error lc3plus_enc_batch(LC3_Enc *const *encoders, int n_streams, int n_frames, const void *pcm,
