@@ -121,13 +121,14 @@ LC3_HD void est_gain(E en, int lg4, i32 x_max, i32 x_e, i32 nbitsSQ, i32 qgain_o
 // operator-by-operator form on edge values and 10^8 random inputs.
 LC3_HD i32 quant_bin(i32 x, i32 inv_gain, i32 s)
 {
-    const u32 ax = x == LC3_I32_MIN ? (u32)LC3_I32_MAX : (u32)(x < 0 ? -x : x);
-    const uint64_t p = ((uint64_t)ax * (u32)inv_gain) >> 15;
-    const int sl = imin(imax(s, 0), 32), sr = imin(imax(-s, 0), 31);
-    uint64_t v = (p << sl) >> sr;
-    if (v > (uint64_t)LC3_I32_MAX) v = LC3_I32_MAX;
-    u32 t = (u32)v + 24576u;
-    if (t > (u32)LC3_I32_MAX) t = (u32)LC3_I32_MAX;
+    u32 ax = x < 0 ? 0u - (u32)x : (u32)x;
+    ax = ax > (u32)LC3_I32_MAX ? (u32)LC3_I32_MAX : ax;        // L_abs saturates -2^31
+    const u32 p = (u32)(((uint64_t)ax * (u32)inv_gain) >> 15);  // below 2^31 * 2^16 >> 15 = 2^32: fits 32 bits
+    const int sl = imin(imax(s, 0), 32), sr = imin(imax(-s, 0), 31); // one of the two is zero
+    const uint64_t w = (uint64_t)p << sl;
+    u32 v = (u32)w >> sr;
+    if (((u32)(w >> 32) | (v >> 31)) != 0) v = (u32)LC3_I32_MAX;  // L_shl saturated
+    const u32 t = (v < (u32)LC3_I32_MAX - 24576u ? v : (u32)LC3_I32_MAX - 24576u) + 24576u; // round_fx saturates at the top
     const i32 q = (i32)(t >> 16);
     return x < 0 ? -q : q;
 }
