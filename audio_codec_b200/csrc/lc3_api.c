@@ -38,7 +38,8 @@ struct LC3_Enc { /* lives in the caller's block; device state is referenced by s
 
 /* lane tables of one bucket, one block: slot[n] i32 | ostride[n] i32 | poff[n] i64 | ooff[n] i64.  Kept from call to call:
  * a call that finds the same table (the usual streaming case) uploads nothing. */
-typedef struct { size_t cap, n; unsigned char *h /* pinned */, *d; } Tab;
+typedef struct { size_t cap, n; unsigned char *h /* pinned */, *d[2]; int cur; } Tab; /* two device copies: a changed table goes
+   into the one no queued kernel reads (the call before the previous one has finished), like the configuration words */
 
 typedef struct {
     int device;
@@ -47,13 +48,16 @@ typedef struct {
     cudaStream_t join;             /* joins the end of every call; whole-buffer output copies */
     /* state pool, tile-interleaved (lc3_layout.h) */
     int cap;                       /* slots, multiple of 32 */
-    int32_t *cfg, *st32, *hist32;  /* device */
+    int32_t *cfg, *cfg_b, *st32, *hist32;  /* device; cfg / cfg_b: the configuration words alternate between two copies, so new
+                                      values can be uploaded while queued kernels still read the old ones */
+    int cfg_cur;                   /* 0: kernels of the current call read cfg, 1: cfg_b */
     int16_t *st16, *hist16;        /* device */
-    int32_t *cfg_host;             /* host shadow of cfg (same layout) */
+    int32_t *cfg_host;             /* pinned host shadow of the configuration words (same layout) */
+    cudaEvent_t cfg_ev; int cfg_ev_used; /* the last upload from the shadow has been read */
+    cudaEvent_t tab_ev; int tab_ev_used; /* the last lane-table upload has read its pinned source */
     int dirty_lo, dirty_hi;        /* tile range of cfg_host not yet uploaded */
     int *free_list, n_free, next_fresh;
     int32_t *reset_list; int n_reset, cap_reset;    /* slots to set to their power-on state */
-    int32_t *areset_list; int n_areset, cap_areset; /* slots whose attack-detector state set_bitrate cleared (fx/setup_enc_lc3.c:266-275) */
     void *d_list; size_t list_cap;
     Tab tab[N_BUCKETS];
     unsigned char *tab_tmp; size_t tab_tmp_cap;
@@ -162,10 +166,10 @@ static int pool_grow(Ctx *c, int need)
     while (cap < need) cap *= 2;
     if (cap == c->cap) return 0;
     if (ctx_wait(c)) return 1; /* the old arrays may be in use */
-    struct { void **p; int words, elem; } a[5] = {
-        {(void **)&c->cfg, CFG_N, 4}, {(void **)&c->st32, ST32_N, 4}, {(void **)&c->hist32, LC3K_MAX_N, 4},
+    struct { void **p; int words, elem; } a[6] = {
+        {(void **)&c->cfg, CFG_N, 4}, {(void **)&c->cfg_b, CFG_N, 4}, {(void **)&c->st32, ST32_N, 4}, {(void **)&c->hist32, LC3K_MAX_N, 4},
         {(void **)&c->st16, ST16_N, 2}, {(void **)&c->hist16, LC3K_MAX_N, 2}};
-    for (int i = 0; i < 5; i++) {
+    for (int i = 0; i < 6; i++) {
         void *n = NULL;
         CU(cudaMalloc(&n, pool_bytes(cap, a[i].words, a[i].elem)));
         CU(cudaMemsetAsync(n, 0, pool_bytes(cap, a[i].words, a[i].elem), c->up));
@@ -174,9 +178,10 @@ static int pool_grow(Ctx *c, int need)
         if (c->cap) CU(cudaFree(*a[i].p));
         *a[i].p = n;
     }
-    int32_t *nh = (int32_t *)calloc((size_t)cap * CFG_N, 4);
-    if (!nh) return 1;
-    if (c->cfg_host) { memcpy(nh, c->cfg_host, pool_bytes(c->cap, CFG_N, 4)); free(c->cfg_host); }
+    int32_t *nh = NULL;
+    CU(cudaMallocHost((void **)&nh, pool_bytes(cap, CFG_N, 4))); /* pinned: uploads from it are asynchronous */
+    memset(nh, 0, pool_bytes(cap, CFG_N, 4));
+    if (c->cfg_host) { memcpy(nh, c->cfg_host, pool_bytes(c->cap, CFG_N, 4)); cudaFreeHost(c->cfg_host); }
     c->cfg_host = nh;
     int *fl = (int *)realloc(c->free_list, (size_t)cap * sizeof(int));
     if (!fl) return 1;
@@ -204,6 +209,8 @@ static int ctx_create(Ctx *c, int device)
         CU(cudaEventCreateWithFlags(&c->pipe[p].done_ev, cudaEventDisableTiming));
     }
     CU(cudaEventCreateWithFlags(&c->call_ev, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&c->cfg_ev, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&c->tab_ev, cudaEventDisableTiming));
     CU(cudaEventCreate(&c->call_end_ev[0]));
     CU(cudaEventCreate(&c->call_end_ev[1]));
     CU(cudaEventCreate(&c->span_ev));
@@ -264,22 +271,20 @@ static int slot_alloc(Ctx *c)
 
 static void cfg_to_shadow(Ctx *c, struct LC3_Enc *e)
 {
+    if (c->cfg_ev_used) { cudaEventSynchronize(c->cfg_ev); c->cfg_ev_used = 0; } /* the last upload has read the shadow (short: uploads queue on their own stream) */
     for (int ch = 0; ch < e->cfg.channels; ch++) {
         int slot = e->slot[ch], tile = slot >> 5, lane = slot & 31;
         int32_t *w = c->cfg_host + (size_t)tile * CFG_N * 32 + lane;
+        if (e->cfg.attack_reset[ch]) {
+            /* set_bitrate switched the attack detector off since the last batch: the reference clears the detector's state right
+             * there (fx/setup_enc_lc3.c:266-275).  Here the lane's generation word moves on and the pitch pass, which owns that
+             * state, clears it when the word differs from the one it stored -- no extra kernel, nothing to wait for. */
+            e->cfg.attack_reset[ch] = 0;
+            e->cfg.ch[ch][CFG_ATT_GEN]++;
+        }
         for (int k = 0; k < CFG_N; k++) w[k * 32] = e->cfg.ch[ch][k];
         if (tile < c->dirty_lo) c->dirty_lo = tile;
         if (tile > c->dirty_hi) c->dirty_hi = tile;
-        if (e->cfg.attack_reset[ch]) { /* set_bitrate switched the attack detector off since the last batch */
-            e->cfg.attack_reset[ch] = 0;
-            if (c->n_areset == c->cap_areset) {
-                int nc = c->cap_areset ? c->cap_areset * 2 : 1024;
-                int32_t *a = (int32_t *)realloc(c->areset_list, (size_t)nc * 4);
-                if (!a) continue;
-                c->areset_list = a; c->cap_areset = nc;
-            }
-            c->areset_list[c->n_areset++] = slot;
-        }
     }
     e->dirty = 0;
 }
@@ -309,33 +314,29 @@ static int upload_list(Ctx *c, const int32_t *list, int n)
     return 0;
 }
 
-/* power-on state for freshly initialised encoders, cleared attack detectors, then the configuration words.  These change
- * what kernels already queued would read, so the device is drained first; a steady stream of calls has nothing pending here. */
+/* Power-on state for freshly initialised encoders (changes what queued kernels may read: the device is drained first; a steady
+ * stream of calls has none), then the configuration words: the whole shadow goes into the copy of the pool that no queued
+ * kernel reads (at most two calls are in flight and the one before the previous has finished), asynchronously, and this call's
+ * kernels take that copy -- a bitrate switch between two asynchronous calls costs one small upload, not a drain. */
 static int flush_pending(Ctx *c, int *uploaded)
 {
-    if (!c->n_reset && !c->n_areset && c->dirty_hi < c->dirty_lo) return 0;
-    if (ctx_wait(c)) return 1;
     if (c->n_reset) {
+        if (ctx_wait(c)) return 1;
         if (upload_list(c, c->reset_list, c->n_reset)) return 1;
         CU((cudaError_t)lc3k_launch_reset(c->st32, c->st16, c->hist16, c->hist32, (const int32_t *)c->d_list, c->n_reset, c->up));
         CU(cudaStreamSynchronize(c->up));
         c->launches++;
         c->n_reset = 0;
     }
-    if (c->n_areset) { /* after the power-on reset: a slot may be in both lists */
-        if (upload_list(c, c->areset_list, c->n_areset)) return 1;
-        CU((cudaError_t)lc3k_launch_attack_reset(c->st32, (const int32_t *)c->d_list, c->n_areset, c->up));
-        CU(cudaStreamSynchronize(c->up));
-        c->launches++;
-        c->n_areset = 0;
-    }
     if (c->dirty_hi >= c->dirty_lo) {
-        size_t off = (size_t)c->dirty_lo * CFG_N * 32, n = (size_t)(c->dirty_hi - c->dirty_lo + 1) * CFG_N * 32;
-        CU(cudaMemcpyAsync(c->cfg + off, c->cfg_host + off, n * 4, cudaMemcpyHostToDevice, c->up));
-        CU(cudaStreamSynchronize(c->up));
+        const size_t n = (size_t)((c->next_fresh + 31) / 32) * CFG_N * 32; /* every tile in use: the other copy is a call behind */
+        c->cfg_cur ^= 1;
+        CU(cudaMemcpyAsync(c->cfg_cur ? c->cfg_b : c->cfg, c->cfg_host, n * 4, cudaMemcpyHostToDevice, c->up));
+        CU(cudaEventRecord(c->cfg_ev, c->up));
+        c->cfg_ev_used = 1;
         c->dirty_lo = 1 << 30; c->dirty_hi = -1;
+        *uploaded = 1;
     }
-    *uploaded = 1;
     return 0;
 }
 
@@ -391,20 +392,23 @@ static int run_bucket(Ctx *g, int key, struct LC3_Enc *const *encs, const int *i
     }
     Tab *tb = &g->tab[key];
     if (tb->n != n_lanes || memcmp(tb->h, g->tab_tmp, tab_bytes)) {
-        if (ctx_wait(g)) return 1; /* kernels already queued may still read the old table */
+        if (g->tab_ev_used) { CU(cudaEventSynchronize(g->tab_ev)); g->tab_ev_used = 0; } /* short: uploads have their own stream */
         if (tb->cap < tab_bytes) {
             size_t z = 0;
+            if (ctx_wait(g)) return 1; /* the copies being replaced may be in use */
             if (tb->h) { cudaFreeHost(tb->h); tb->h = NULL; }
-            if (tb->d) { cudaFree(tb->d); tb->d = NULL; }
+            for (int k = 0; k < 2; k++) if (tb->d[k]) { cudaFree(tb->d[k]); tb->d[k] = NULL; }
             tb->cap = 0; tb->n = 0;
             if (ensure((void **)&tb->h, &z, tab_bytes, 1)) return 1;
-            z = 0;
-            if (ensure((void **)&tb->d, &z, tab_bytes, 0)) return 1;
+            for (int k = 0; k < 2; k++) { z = 0; if (ensure((void **)&tb->d[k], &z, tab_bytes, 0)) return 1; }
             tb->cap = tab_bytes;
         }
         memcpy(tb->h, g->tab_tmp, tab_bytes);
         tb->n = n_lanes;
-        CU(cudaMemcpyAsync(tb->d, tb->h, tab_bytes, cudaMemcpyHostToDevice, g->up));
+        tb->cur ^= 1;
+        CU(cudaMemcpyAsync(tb->d[tb->cur], tb->h, tab_bytes, cudaMemcpyHostToDevice, g->up));
+        CU(cudaEventRecord(g->tab_ev, g->up));
+        g->tab_ev_used = 1;
         cs->uploads = 1;
     }
 
@@ -416,9 +420,9 @@ static int run_bucket(Ctx *g, int key, struct LC3_Enc *const *encs, const int *i
     b.n_lanes = (int)n_lanes;
     b.n_tiles = (int)((n_lanes + 31) / 32);
     b.max_bytes = max_bytes;
-    b.slot = (const int32_t *)tb->d; b.out_stride = b.slot + n_lanes;
+    b.slot = (const int32_t *)tb->d[tb->cur]; b.out_stride = b.slot + n_lanes;
     b.pcm_off = (const int64_t *)(b.out_stride + n_lanes); b.out_off = b.pcm_off + n_lanes;
-    b.cfg = g->cfg; b.st32 = g->st32; b.st16 = g->st16; b.hist16 = g->hist16; b.hist32 = g->hist32;
+    b.cfg = g->cfg_cur ? g->cfg_b : g->cfg; b.st32 = g->st32; b.st16 = g->st16; b.hist16 = g->hist16; b.hist32 = g->hist32;
     b.pcm = d_pcm; b.out = d_out;
 
     if (any_bfi) { /* [n_frames][n_lanes] flags; rare (the caller marks lost frames): one call at a time */
@@ -601,7 +605,6 @@ static int run_on_device(DevJob *j)
         g->n_active = nb < N_PIPES_MIN ? N_PIPES_MIN : (nb > N_PIPES ? N_PIPES : nb);
     }
     if (flush_pending(g, &cs.uploads)) return 1;
-    cs.uploads = 0; /* flush_pending leaves nothing in flight */
 
     const int pcm_dev = is_device_ptr(j->pcm), out_dev = is_device_ptr(j->out);
     /* this device's streams span rows idx[0] .. idx[n-1] of the caller's buffers; staging keeps the caller's row numbering

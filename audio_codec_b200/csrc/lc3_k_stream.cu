@@ -132,22 +132,7 @@ __global__ void k_reset(i32 *st32, i16 *st16, i16 *hist16, i32 *hist32, const i3
     for (int i = threadIdx.x; i < LC3K_MAX_N; i += blockDim.x) { h[i] = 0; g[i] = 0; }
 }
 
-__global__ void k_attack_reset(i32 *st32, const i32 *slots, int n)
-{
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= n) return;
-    SV<i32> a = slot_view(st32, slots[k], ST32_N);
-    a[ST_ATT_F0] = 0; a[ST_ATT_F1] = 0; a[ST_ATT_DET] = 0; a[ST_ATT_POS] = 0; a[ST_ATT_SCAL] = 0; a[ST_ATT_ACC] = 0;
-}
-
 static int done() { return (int)cudaGetLastError(); }
-
-extern "C" int lc3k_launch_attack_reset(int32_t *st32, const int32_t *slots, int n, void *stream)
-{
-    if (n <= 0) return 0;
-    k_attack_reset<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(st32, slots, n);
-    return done();
-}
 
 extern "C" int lc3k_launch_reset(int32_t *st32, int16_t *st16, int16_t *hist16, int32_t *hist32, const int32_t *slots, int n, void *stream)
 {

@@ -23,14 +23,16 @@ enum {
     /* error protection (fx/setup_enc_lc3.c:155-206): CFG_EP = epmode | epmr << 4 | combined channel coding << 8 (0: off);
      * CFG_SLOT_BYTES = bytes of the channel-coded slot this lane's payload goes into (combined channel coding: the whole
      * frame on channel 0, 0 on channel 1); CFG_N_PCCW / CFG_N_PC = partial-concealment codewords / nibbles */
-    CFG_EP, CFG_SLOT_BYTES, CFG_EP_DATA_BYTES /* payload bytes that go into the slot */, CFG_N_PCCW, CFG_N_PC, CFG_N = 16
+    CFG_EP, CFG_SLOT_BYTES, CFG_EP_DATA_BYTES /* payload bytes that go into the slot */, CFG_N_PCCW, CFG_N_PC,
+    CFG_ATT_GEN /* moves on whenever set_bitrate switched the attack detector off: the pitch pass clears the detector's state when
+                   it differs from ST_ATT_GEN (fx/setup_enc_lc3.c:266-275) */, CFG_N = 16
 };
 
 /* per-slot scalar state (int32 words) */
 enum {
     ST_MEM50_0 = 0, ST_MEM50_1, ST_OLPA_EXP, ST_OLPA_PITCH, ST_LTPF_EXP, ST_LTPF_NC, ST_LTPF_MNC, ST_LTPF_ON,
     ST_LTPF_PITCH, ST_ATT_F0, ST_ATT_F1, ST_ATT_DET, ST_ATT_POS, ST_ATT_SCAL, ST_ATT_ACC, ST_TBITS_OFF,
-    ST_MEM_TBITS, ST_MEM_SPECBITS, ST_X_EXP, ST_RESAMP_EXP, ST32_N = 24
+    ST_MEM_TBITS, ST_MEM_SPECBITS, ST_X_EXP, ST_RESAMP_EXP, ST_ATT_GEN, ST32_N = 24
 };
 
 /* per-slot int16 state arrays (element offsets) */
@@ -113,8 +115,6 @@ int lc3k_launch_back(const LC3K_Batch *b, void *stream);
 int lc3k_launch_fec(const LC3K_Batch *b, void *stream);     /* error protection of the finished payloads, in place in the output (only when a lane has CFG_EP) */
 /* set the listed state slots to their power-on values (fx/setup_enc_lc3.c:38-66) */
 int lc3k_launch_reset(int32_t *st32, int16_t *st16, int16_t *hist16, int32_t *hist32, const int32_t *slots, int n, void *stream);
-/* clear the attack detector's state words of the listed slots (fx/setup_enc_lc3.c:266-275) */
-int lc3k_launch_attack_reset(int32_t *st32, const int32_t *slots, int n, void *stream);
 #ifdef __cplusplus
 }
 #endif

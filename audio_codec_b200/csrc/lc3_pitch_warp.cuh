@@ -111,7 +111,10 @@ template <int BITS, bool PRE, int DMS = 0> LC3_HD void pitch_warp_body(const LC3
     AttackState as;
     as.filter_mem[0] = st[ST_ATT_F0]; as.filter_mem[1] = st[ST_ATT_F1]; as.detected = st[ST_ATT_DET];
     as.position = st[ST_ATT_POS]; as.scaling = st[ST_ATT_SCAL]; as.acc_energy = st[ST_ATT_ACC];
-    if (!attack_handling) { // cleared whenever set_bitrate switches the detector off (setup_enc_lc3.c:252-275)
+    // cleared whenever set_bitrate switched the detector off (setup_enc_lc3.c:252-275): while it is off, and -- for an off/on
+    // toggle with no frame in between -- when the host moved the lane's generation word on
+    const i32 att_gen = cfg[CFG_ATT_GEN];
+    if (!attack_handling || att_gen != st[ST_ATT_GEN]) {
         as.filter_mem[0] = as.filter_mem[1] = 0; as.detected = as.position = as.scaling = as.acc_energy = 0;
     }
     i32 x_exp = st[ST_X_EXP], resamp_exp = st[ST_RESAMP_EXP];
@@ -581,7 +584,7 @@ template <int BITS, bool PRE, int DMS = 0> LC3_HD void pitch_warp_body(const LC3
         if (l == 0) {
             st[ST_ATT_F0] = as.filter_mem[0]; st[ST_ATT_F1] = as.filter_mem[1]; st[ST_ATT_DET] = as.detected;
             st[ST_ATT_POS] = as.position; st[ST_ATT_SCAL] = as.scaling; st[ST_ATT_ACC] = as.acc_energy;
-            st[ST_X_EXP] = x_exp; st[ST_RESAMP_EXP] = resamp_exp;
+            st[ST_X_EXP] = x_exp; st[ST_RESAMP_EXP] = resamp_exp; st[ST_ATT_GEN] = att_gen;
             st[ST_OLPA_EXP] = olpa_exp; st[ST_OLPA_PITCH] = olpa_pitch;
             st[ST_LTPF_EXP] = ltpf_exp; st[ST_LTPF_NC] = ltpf_nc; st[ST_LTPF_MNC] = ltpf_mnc;
             st[ST_LTPF_ON] = ltpf_on; st[ST_LTPF_PITCH] = ltpf_pitch_mem;
