@@ -114,3 +114,38 @@ def test_encoders_on_every_device_in_one_batch():
     out2 = np.zeros_like(out)
     ac.enc_batch(encs2, nf, pcm, nf * N * 2, 16, out2, nf * nb)
     assert np.array_equal(out2, out)
+
+
+def test_set_bitrate_many_and_device_profile():
+    """lc3plus_enc_set_bitrate_many == lc3_enc_set_bitrate on each encoder (first error returned, the rest applied);
+    lc3plus_profile_read_device reports the span of asynchronous calls on the device they ran on."""
+    import audio_codec_b200 as ac
+    fs, dms, N, S, nf = 48000, 100, 480, 5, 6
+    pcm = make_streams(S, 2 * nf * N, fs, N, first_stream=3)
+    encs = ac.EncoderArray([ac.Encoder(fs, 1, dms, 64000) for _ in range(S)])
+    oras = [lc3ref.OracleEnc(fs, 1, dms, 64000) for _ in range(S)]
+    rates = np.array([128000, 32000, 96000, 16000, 320000], dtype=np.int32)
+    ac.profile_enable(1)
+    outs = []
+    for k in range(2):
+        x = np.ascontiguousarray(pcm[:, k * nf * N:(k + 1) * nf * N])
+        if k == 1:
+            ac.set_bitrate_many(encs, rates)
+            for o, r in zip(oras, rates):
+                assert o.set_bitrate(int(r)) == 0
+        out = np.zeros((S, nf * 400), dtype=np.uint8)
+        ac.enc_batch(encs, nf, x, nf * N * 2, 16, out, nf * 400, wait=False)
+        outs.append((out, [o.encode(x[s:s + 1]) for s, o in enumerate(oras)]))
+    ac.sync()
+    prof = ac.profile_read_device(encs.encoders[0].device)
+    ac.profile_enable(0)
+    assert prof["span"] > 0 and prof["calls"] == 2
+    for out, want in outs:
+        for s in range(S):
+            assert np.array_equal(out[s, :want[s].size].reshape(want[s].shape), want[s]), s
+    bad = rates.copy()
+    bad[2] = 1000                                  # illegal: LC3_BITRATE_ERROR for that one, the others still applied
+    with pytest.raises(ac.LC3Error) as ex:
+        ac.set_bitrate_many(encs, bad)
+    assert ex.value.code == 6
+    assert [e.num_bytes for e in encs.encoders] == [160, 40, 120, 20, 400]
