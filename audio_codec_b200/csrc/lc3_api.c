@@ -91,7 +91,7 @@ static pthread_mutex_t g_lock = PTHREAD_MUTEX_INITIALIZER; /* context creation, 
 static char g_err[256];
 static __thread int tl_device = -1;
 static int g_prof = 0;
-static int g_chunk_dev = 5 << 15, g_chunk_host = 25 << 13; /* channel-frames per chunk: input on the device | in host memory */
+static int g_chunk_dev = 5 << 15, g_chunk_host = 25 << 13, g_chunk_forced = 0; /* forced: set by the caller, taken literally */ /* channel-frames per chunk: input on the device | in host memory */
 static unsigned g_call_id = 0;
 
 static int cu_fail(cudaError_t e, const char *what)
@@ -441,6 +441,8 @@ static int run_bucket(Ctx *g, int key, struct LC3_Enc *const *encs, const int *i
 
     /* frames per chunk: about chunk_frames channel-frames each, balanced over the chunks */
     int fc = ((cp && cp->h_pcm) ? g_chunk_host : g_chunk_dev) / (b.n_tiles * 32);
+    if (fc < 8 && !g_chunk_forced) fc = 8; /* very wide buckets: the per-stream kernels load and store their state once per chunk, a
+                                              few frames per chunk would be mostly that (100 000 streams: 72 -> M frames/s) */
     if (fc < 1) fc = 1;
     if (fc > n_frames) fc = n_frames;
     const int ramp = cp && cp->h_pcm && n_frames > fc;
@@ -1011,8 +1013,8 @@ const char *lc3plus_last_error(void) { return g_err; }
 void lc3b_set_error(const char *msg) { snprintf(g_err, sizeof(g_err), "%s", msg); } /* for lc3_k_noalloc.cu */
 void lc3plus_set_chunk_frames(int channel_frames)
 { /* >= 32: both chunk sizes; 0: back to the defaults */
-    if (channel_frames >= 32) g_chunk_dev = g_chunk_host = channel_frames;
-    else if (channel_frames == 0) { g_chunk_dev = 5 << 15; g_chunk_host = 25 << 13; }
+    if (channel_frames >= 32) { g_chunk_dev = g_chunk_host = channel_frames; g_chunk_forced = 1; }
+    else if (channel_frames == 0) { g_chunk_dev = 5 << 15; g_chunk_host = 25 << 13; g_chunk_forced = 0; }
     { const char *e = getenv("LC3PLUS_B200_HOST_CHUNK"); if (channel_frames == 0 && e && atoi(e) >= 32) g_chunk_host = atoi(e); } /* tuning aid */
 }
 

@@ -293,9 +293,9 @@ KS = ("stage", "fir", "scalar", "pitch", "mdct", "sns", "tns", "rate", "quant", 
 class Unit:
     """one GPU's shard: workload, encoders (living on that device), device and pinned host buffers, pass counter"""
 
-    def __init__(self, ac, torch, name, dev, shard, n_shards, S, F):
+    def __init__(self, ac, torch, name, dev, shard, n_shards, S, F, total=0):
         from audio_codec_b200.shard import shard_range
-        lo, hi = shard_range(S * n_shards, shard, n_shards)
+        lo, hi = shard_range(total if total else S * n_shards, shard, n_shards)
         self.dev = dev
         self.w = Workload(name, lo, hi - lo, F)
         torch.cuda.set_device(dev)
@@ -326,6 +326,8 @@ def main():
     ap.add_argument("--streams", type=int, default=0, help="streams per GPU (0: the configuration's)")
     ap.add_argument("--frames", type=int, default=0, help="frames per stream per step (0: the configuration's)")
     ap.add_argument("--chunk", type=int, default=0, help="channel-frames per internal chunk (0: library default); profiling aid")
+    ap.add_argument("--total-streams", type=int, default=0,
+                    help="strong scaling: this many streams in TOTAL, sharded over the GPUs with shard_range (e.g. --config c3 --total-streams 100000)")
     ap.add_argument("--single-process", action="store_true", help="drive --gpus N devices from this one process (no torchrun)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -347,7 +349,7 @@ def main():
     if args.single_process:
         rank, world, n_shards = 0, 1, args.gpus
         assert torch.cuda.device_count() >= args.gpus, "--single-process --gpus N needs N visible devices"
-        units = [Unit(ac, torch, args.config, d, d, n_shards, S, F) for d in range(args.gpus)]
+        units = [Unit(ac, torch, args.config, d, d, n_shards, S, F, args.total_streams) for d in range(args.gpus)]
         torch.cuda.set_device(0)
     else:
         n_shards = world
@@ -355,7 +357,7 @@ def main():
         if world > 1:
             import torch.distributed as dist
             dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-        units = [Unit(ac, torch, args.config, local, rank, world, S, F)]
+        units = [Unit(ac, torch, args.config, local, rank, world, S, F, args.total_streams)]
     u0 = units[0]
 
     def barrier():
@@ -402,6 +404,10 @@ def main():
     dev_s = max_over_ranks(max(spans) / 1e3)
     wall_s = max_over_ranks(wall)
     cf_step = sum(u.w.channel_frames for u in units)             # this process's channel-frames per step
+    if dist is not None and args.total_streams:                  # shards may differ by one stream: sum over the ranks
+        t = torch.tensor([float(cf_step)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t)
+        cf_step = t.item() / world
     frames_total = float(cf_step) * args.steps * world
     value = frames_total / dev_s
 
@@ -505,13 +511,16 @@ def main():
                                 "peak_thread_instr_per_s": int_peak, "frac": per_gpu * wops / int_peak if wops else None}}
     audio_s = sum(ch * u.w.frames * dms / 10000.0 for u in units for fs, dms, ch, bits, br in u.w.spec)   # seconds of audio per step
     line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world * len(units), "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": 1e3 * dev_s / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": 1e3 * dev_s / args.steps, "higher_is_better": True, "scaling": "strong" if args.total_streams else "weak", "vs_baseline": None,
             "dtype": "int16/int32 fixed point", "data": "synthetic",
             "config": config_dict(args.config, u0.w, world * len(units), S),
             "realtime_channels": audio_s * world * args.steps / dev_s, "wall_ms_per_step": 1e3 * wall_s / args.steps,
             "e2e": e2e, "gpu_launches": int(launches), "clocks": sm_clock, "roofline": roofline}
     if args.single_process:
         line["processes"] = 1
+    if args.total_streams:
+        line["config"]["total_streams"] = args.total_streams
+        line["config"]["streams_per_gpu"] = u0.w.S
     line.update(verified)
     if world == 1 and len(units) == 1 and not args.no_cpu_baseline and refbench_path() is not None:
         rate, cores, sample = cpu_reference_rate(u0.w, 12.0)

@@ -159,7 +159,8 @@ void lc3plus_profile_read_device(int device, double *ms);    /* one device's sha
 LC3_Error lc3plus_enc_set_bitrate_many(LC3_Enc *const *encoders, int n, const int *bitrates);
 /* NEW: last CUDA error string seen by the library ("" if none). */
 const char *lc3plus_last_error(void);
-/* NEW: upper bound on channel-frames processed per internal chunk (defaults: 163840 when the PCM is already on the
+/* NEW: upper bound on channel-frames processed per internal chunk, taken literally when set here (defaults, which never cut
+ * a chunk below eight frames per stream: 163840 when the PCM is already on the
  * device, 204800 when it is copied from host memory chunk by chunk); up to three chunks are in flight at once, each on
  * its own CUDA streams with its own work buffers. */
 void lc3plus_set_chunk_frames(int channel_frames);
