@@ -375,7 +375,7 @@ template <int N, int BITS> LC3_HD void mt_store(const LC3K_Batch &b, int f, int 
     const size_t ft = frame_tile(b, f, tile);
     const i32 *y = X + lane * G::S;
     SV<i32> d = tile_view(b.spec, ft, N, lane);
-    for (int e = part; e < N; e += G::PARTS) d[e] = y[mt_ridx(e)];
+    for (int e = part; e < b.yLen; e += G::PARTS) d[e] = y[mt_ridx(e)]; // nothing downstream reads a bin past yLen (400 >> dms_idx)
     const i32 x_exp = BITS == 16 ? 15 : tile_view((const i32 *)b.pout, ft, PO_N, lane)[PO_X_EXP];
     const i32 d_exp = s_add(s_add(s_sub(s_sub(x_exp, 2), mt_shift<N>(mx, mn, lane)), G::FFT_SCALE), 2);
     i32 smax = -31;
