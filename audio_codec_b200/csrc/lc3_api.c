@@ -156,7 +156,11 @@ static int ctx_wait(Ctx *c)
         }
         c->span_open = 0;
     }
-    if (c->failed) { c->failed = 0; bad = 1; }
+    if (c->failed) { /* a call stopped half-way through its queuing: nothing is joined, wait for the whole device */
+        cudaDeviceSynchronize();
+        c->failed = 0; c->pending = 0; c->span_open = 0;
+        bad = 1;
+    }
     return bad;
 }
 
@@ -701,6 +705,7 @@ static void *dev_thread(void *arg)
     DevJob *j = (DevJob *)arg;
     pthread_mutex_lock(&j->g->lock);
     j->rc = run_on_device(j);
+    if (j->rc) j->g->failed = 1; /* whatever was queued before the failure is waited for (ctx_wait) before anything is reused */
     pthread_mutex_unlock(&j->g->lock);
     return NULL;
 }
