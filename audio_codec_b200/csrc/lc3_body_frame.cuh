@@ -190,7 +190,7 @@ LC3_HD i32 back_body(const LC3K_Batch &b, int f, int tile, int lane, const AriTa
 }
 
 // ---- error protection of the lane's finished payload, in place in the caller's output (fx/enc_lc3.c:282-312)
-LC3_HD void fec_body(const LC3K_Batch &b, int f, int tile, int lane)
+LC3_HD void fec_body(const LC3K_Batch &b, int f, int tile, int lane, const FecTabs &T)
 {
     const int li = tile * LC3K_LANES + lane;
     if (li >= b.n_lanes) return;
@@ -198,7 +198,7 @@ LC3_HD void fec_body(const LC3K_Batch &b, int f, int tile, int lane)
     const i32 ep = cfg[CFG_EP], slot_bytes = cfg[CFG_SLOT_BYTES];
     if (ep == 0 || slot_bytes == 0) return; // off, or channel 1 of a jointly coded frame
     u8 *io = b.out + b.out_off[li] + (size_t)(b.frame0 + f) * b.out_stride[li];
-    fec_encode_slot(ep & 15, (ep >> 4) & 15, io, cfg[CFG_EP_DATA_BYTES], slot_bytes, cfg[CFG_N_PCCW]);
+    fec_encode_slot(T, ep & 15, (ep >> 4) & 15, io, cfg[CFG_EP_DATA_BYTES], slot_bytes, cfg[CFG_N_PCCW]);
 }
 
 } // namespace lc3k

@@ -27,8 +27,13 @@ LC3_HD int fec_n_pc(int mode, int n_pccw, int slot_bytes)
     return pc;
 }
 
-LC3_HD u32 gf16_mul(u32 a, u32 b)
-{ // GF(16), field polynomial x^4 + x + 1 (fx/al_fec.c:72-76; the reference looks products up, fx/rom_basop_util.c:1177)
+// Look-up tables the kernel builds once per block in shared memory (the reference looks these up too, fx/rom_basop_util.c:1177,
+// fx/al_fec.c:2177-2182): all 256 GF(16) products, and for each of the three CRC generators the multiple that cancels a given
+// top nibble.  Lane-varying indices, so shared memory, not constant memory.
+struct FecTabs { u8 mul[256]; u32 crc[3][16]; };
+
+LC3_HD u32 gf16_mul_bits(u32 a, u32 b)
+{ // GF(16), field polynomial x^4 + x + 1 (fx/al_fec.c:72-76)
     u32 r = 0;
 #pragma unroll
     for (int i = 0; i < 4; i++) {
@@ -41,34 +46,47 @@ LC3_HD u32 gf16_mul(u32 a, u32 b)
 
 // one step of the reference's table-driven CRC (mask[k], fx/al_fec.c:2177-2182, :2246-2247, is the multiple of the generator
 // whose bits shift..shift+3 equal k): cancel the four bits above `shift`, top one first
-LC3_HD u32 fec_crc_reduce(u32 rem, u32 gen, int shift)
+LC3_HD u32 fec_crc_reduce_bits(u32 rem, u32 gen, int shift)
 {
 #pragma unroll
     for (int bit = 3; bit >= 0; bit--) rem ^= (rem >> (shift + bit)) & 1 ? gen << bit : 0;
     return rem;
 }
+// generator and degree of: crc1 with a two-byte hash, crc1 with three bytes, crc2
+LC3_HD u32 fec_gen(int g) { return g == 0 ? 17989u : (g == 1 ? 4788009u : 107243u); }
+LC3_HD int fec_shift(int g) { return g == 0 ? 14 : (g == 1 ? 22 : 16); }
+// entry i of the tables (i < 256 + 48), for a block-wide fill
+LC3_HD void fec_tabs_fill(FecTabs &T, int i)
+{
+    if (i < 256) T.mul[i] = (u8)gf16_mul_bits((u32)i >> 4, (u32)i & 15);
+    else if (i < 256 + 48) {
+        const int g = (i - 256) >> 4, k = (i - 256) & 15;
+        T.crc[g][k] = fec_crc_reduce_bits((u32)k << fec_shift(g), fec_gen(g), fec_shift(g)) ^ ((u32)k << fec_shift(g));
+    }
+}
+LC3_HD u32 gf16_mul(const FecTabs &T, u32 a, u32 b) { return T.mul[(a << 4) | b]; }
+LC3_HD u32 fec_crc_reduce(const FecTabs &T, u32 rem, int g) { return rem ^ T.crc[g][(rem >> fec_shift(g)) & 15]; }
 
-LC3_HD void fec_crc1(const u8 *data, int n, int epmr, u8 *hash, int hash_size)
+LC3_HD void fec_crc1(const FecTabs &T, const u8 *data, int n, int epmr, u8 *hash, int hash_size)
 { // fx/al_fec.c:2184-2244
-    const int shift = hash_size == 2 ? 14 : 22;
-    const u32 gen = hash_size == 2 ? 17989u : 4788009u;
+    const int g = hash_size == 2 ? 0 : 1, shift = fec_shift(g);
     u32 rem = 0;
-    for (int i = n - 1; i >= 0; i--) rem = fec_crc_reduce((rem << 4) ^ data[i], gen, shift);
-    rem = fec_crc_reduce((rem << 4) ^ ((u32)epmr << 2), gen, shift);
-    for (int i = 0; i < 2 * hash_size - 1; i++) rem = fec_crc_reduce(rem << 4, gen, shift);
+    for (int i = n - 1; i >= 0; i--) rem = fec_crc_reduce(T, (rem << 4) ^ data[i], g);
+    rem = fec_crc_reduce(T, (rem << 4) ^ ((u32)epmr << 2), g);
+    for (int i = 0; i < 2 * hash_size - 1; i++) rem = fec_crc_reduce(T, rem << 4, g);
     rem ^= (u32)epmr << shift;
     for (int i = 0; i < 2 * hash_size; i++) hash[i] = (u8)((rem >> (4 * i)) & 15);
 }
 
-LC3_HD void fec_crc2(const u8 *data, int n, u8 *hash)
+LC3_HD void fec_crc2(const FecTabs &T, const u8 *data, int n, u8 *hash)
 { // fx/al_fec.c:2256-2314 (two-byte hash)
     u32 rem = 0;
-    for (int i = n - 1; i >= 0; i--) rem = fec_crc_reduce((rem << 4) ^ data[i], 107243u, 16);
-    for (int i = 0; i < 4; i++) rem = fec_crc_reduce(rem << 4, 107243u, 16);
+    for (int i = n - 1; i >= 0; i--) rem = fec_crc_reduce(T, (rem << 4) ^ data[i], 2);
+    for (int i = 0; i < 4; i++) rem = fec_crc_reduce(T, rem << 4, 2);
     for (int i = 0; i < 4; i++) hash[i] = (u8)((rem >> (4 * i)) & 15);
 }
 
-LC3_HD void fec_rs16(u8 *buf, int len, int hd, int mode, int signal)
+LC3_HD void fec_rs16(const FecTabs &T, u8 *buf, int len, int hd, int mode, int signal)
 { // fx/al_fec.c:558-612: remainder of (data polynomial * x^(hd-1)) by the generator, lowest coefficient first
     const int deg = hd - 1;
     if (deg <= 0) return;
@@ -79,7 +97,7 @@ LC3_HD void fec_rs16(u8 *buf, int len, int hd, int mode, int signal)
     for (int i = len - deg - 1; i >= 0; i--) {
         sb[0] = buf[i];
         const u32 lc = sb[deg];
-        for (int j = deg - 1; j >= 0; j--) sb[j + 1] = sb[j] ^ gf16_mul(gp[j], lc);
+        for (int j = deg - 1; j >= 0; j--) sb[j + 1] = sb[j] ^ gf16_mul(T, gp[j], lc);
     }
     for (int i = 0; i < deg; i++) buf[i] = (u8)sb[i + 1];
     if (signal && mode > 1) { // signalling polynomials of modes 2..4, degree 12 (fx/al_fec.c:98-101; mode 1's is zero)
@@ -91,7 +109,7 @@ LC3_HD void fec_rs16(u8 *buf, int len, int hd, int mode, int signal)
 }
 
 // fx/al_fec.c:481-556.  io: data_bytes of payload on entry, slot_bytes of protected data on return (global memory).
-LC3_HD void fec_encode_slot(int mode, int epmr, u8 *io, int data_bytes, int slot_bytes, int n_pccw)
+LC3_HD void fec_encode_slot(const FecTabs &T, int mode, int epmr, u8 *io, int data_bytes, int slot_bytes, int n_pccw)
 {
     u8 cw[2 * FEC_SLOT_MAX + 16], out[FEC_SLOT_MAX];
     const int n_cw = fec_n_codewords(slot_bytes), nn = 2 * slot_bytes;
@@ -100,8 +118,8 @@ LC3_HD void fec_encode_slot(int mode, int epmr, u8 *io, int data_bytes, int slot
     for (int i = 0; i < off; i++) cw[i] = 0;
     for (int i = 0; i < data_bytes; i++) { const u32 v = io[i]; cw[j--] = (u8)(v & 15); cw[j--] = (u8)(v >> 4); }
     const int n1 = fec_crc1_bytes(mode, slot_bytes), n2 = (pc_split > 0 && mode > 1) ? fec_crc2_bytes(mode) : 0;
-    if (n2) fec_crc2(cw + off + 2 * data_bytes - pc_split, pc_split, cw + off - 2 * n2);
-    if (n1) fec_crc1(cw + off, 2 * data_bytes - pc_split, epmr, cw + off - 2 * (n1 + n2), n1);
+    if (n2) fec_crc2(T, cw + off + 2 * data_bytes - pc_split, pc_split, cw + off - 2 * n2);
+    if (n1) fec_crc1(T, cw + off, 2 * data_bytes - pc_split, epmr, cw + off - 2 * (n1 + n2), n1);
     off -= 2 * (n1 + n2);
     { // dw0_bitswap, fx/al_fec.c:361-390: the mode request moves next to the first codeword's redundancy
         u8 *dw0 = cw + off;
@@ -114,7 +132,7 @@ LC3_HD void fec_encode_slot(int mode, int epmr, u8 *io, int data_bytes, int slot
     for (int i = 0; i < n_cw; i++) {
         const int hd = fec_hd(mode, i == 0), len = fec_cw_length(n_cw, nn, i);
         for (int k = hd - 1; k < len; k++, dwo++) cw[cwo + k] = cw[dwo];
-        fec_rs16(cw + cwo, len, hd, mode, i < 6);
+        fec_rs16(T, cw + cwo, len, hd, mode, i < 6);
         cwo += len;
     }
     for (int i = 0; i < slot_bytes; i++) out[i] = 0;

@@ -87,9 +87,12 @@ LC3_DBG_READER(back)
 // error protection of the finished payloads (lc3_fec.cuh), lane per channel-frame, in place in the caller's output
 __global__ void __launch_bounds__(128) k_fec(LC3K_Batch b)
 {
+    __shared__ FecTabs T; // GF(16) products and CRC masks, built once per block
+    for (int i = threadIdx.x; i < 256 + 48; i += 128) fec_tabs_fill(T, i);
+    __syncthreads();
     const int warp = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (warp >= b.n_frames * b.n_tiles) return;
-    fec_body(b, warp / b.n_tiles, warp % b.n_tiles, lane);
+    fec_body(b, warp / b.n_tiles, warp % b.n_tiles, lane, T);
 }
 
 static int done() { return (int)cudaGetLastError(); }

@@ -230,7 +230,10 @@ extern "C" int hostsim_encode(void *p, const void *pcm, int bits, int n_frames, 
                 const i32 nb = back_body(b, f, tile, lane, T, LocalBytes{frame}, dst);
                 for (int i = 0; i < nb; i++) dst[i] = frame[i];
             }
-            for (int lane = 0; lane < 32; lane++) fec_body(b, f, tile, lane); // k_fec
+            static FecTabs fec_tabs;
+            static bool fec_tabs_ready = false;
+            if (!fec_tabs_ready) { for (int i = 0; i < 256 + 48; i++) fec_tabs_fill(fec_tabs, i); fec_tabs_ready = true; }
+            for (int lane = 0; lane < 32; lane++) fec_body(b, f, tile, lane, fec_tabs); // k_fec
 
         }
     return 0;
