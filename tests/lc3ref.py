@@ -152,3 +152,37 @@ class OracleEnc(_Base):
     def _enc(self, bits, ptrs, out, n):
         L = oracle_lib()
         return (L.lc3o_enc16 if bits == 16 else L.lc3o_enc24)(self.h, ptrs, C.c_void_p(out), n)
+
+
+class RefDec:
+    """The unmodified reference DECODER (oracle/_ref/liblc3ref.so, fx/lc3.h:334-457): test infrastructure for round trips."""
+
+    def __init__(self, fs, channels=1, dms=100, ep=False):
+        L = ref_lib()
+        L.lc3_dec_get_size.restype = C.c_int
+        self.channels = channels
+        self._mem = C.create_string_buffer(L.lc3_dec_get_size(fs, channels, 1) + 16)
+        self.h = C.c_void_p((C.addressof(self._mem) + 15) & ~15)
+        assert L.lc3_dec_init(self.h, fs, channels, 1) == 0   # LC3_PLC_ADVANCED, the only mode this build supports
+        assert L.lc3_dec_set_frame_dms(self.h, dms) == 0
+        if ep:
+            assert L.lc3_dec_set_ep_enabled(self.h, 1) == 0
+        self._scratch = C.create_string_buffer(L.lc3_dec_get_scratch_size(self.h) + 64)
+        self.frame_len = L.lc3_dec_get_output_samples(self.h)
+        self.delay = L.lc3_dec_get_delay(self.h)
+
+    def decode(self, frames):
+        """frames: uint8 [n_frames, nbytes] -> int16 [channels, n_frames * N]; returns (pcm, number of frames flagged bad)"""
+        L = ref_lib()
+        frames = np.ascontiguousarray(frames, dtype=np.uint8)
+        nf, nb = frames.shape
+        N = self.frame_len
+        out = np.zeros((self.channels, nf * N), dtype=np.int16)
+        ptrs = (C.c_void_p * 2)()
+        bad = 0
+        for f in range(nf):
+            for c in range(self.channels):
+                ptrs[c] = out[c, f * N:].ctypes.data
+            r = L.lc3_dec16(self.h, C.c_void_p(frames[f].ctypes.data), nb, ptrs, self._scratch, 0)
+            bad += r != 0
+        return out, bad

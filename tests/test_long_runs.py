@@ -247,3 +247,32 @@ def test_chunked_pipeline_variants(fs, ch, dms, br, bits, ep, device):
     for s in range(S):
         want = oras[s].encode(pcm[s], bits, bfi[s * nf:(s + 1) * nf])
         assert np.array_equal(out[s], want), s
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("fs,ch,dms,br,ep", [(48000, 1, 100, 128000, 0), (16000, 1, 50, 32000, 0), (48000, 2, 25, 256000, 0),
+                                             (48000, 1, 100, 128000, 4), (32000, 2, 100, 128000, 3)])
+def test_round_trip_through_the_reference_decoder(fs, ch, dms, br, ep):
+    """Size-independent property: what the CUDA encoder writes, the unmodified reference DECODER (oracle/_ref) reads without a
+    frame error -- error-protected slots included, whose CRCs and Reed-Solomon words it checks -- and gives back the input
+    (delayed by the codec delay) at a signal-to-noise ratio a working codec has at these rates."""
+    if not lc3ref.have_ref():
+        pytest.skip("oracle/_ref/liblc3ref.so absent")
+    import audio_codec_b200 as ac
+    N, nf = _frame_len(fs, dms), 1000 // (dms // 25) // 2 + 40
+    pcm = make_streams(ch, nf * N, fs, N, 16, first_stream=3)
+    e = ac.Encoder(fs, ch, dms)
+    assert e.set_ep_mode(ep) == 0
+    e.set_bitrate(br)
+    nb = e.num_bytes
+    out = np.zeros((1, nf, nb), dtype=np.uint8)
+    ac.enc_batch([e], nf, pcm[None], pcm.nbytes, 16, out, nf * nb)
+    dec = lc3ref.RefDec(fs, ch, dms, ep=bool(ep))
+    y, bad = dec.decode(out[0])
+    assert bad == 0
+    d = dec.delay
+    for c in range(ch):
+        x = pcm[c, 20 * N:(nf - 2) * N - d].astype(np.float64)
+        z = y[c, 20 * N + d:(nf - 2) * N].astype(np.float64)
+        snr = 10 * np.log10(np.sum(x * x) / max(np.sum((x - z) ** 2), 1.0))
+        assert snr > 12.0, (c, snr)
