@@ -55,6 +55,7 @@ LC3_HD void qt_setup(const LC3K_Batch &b, int f, int tile, int lane, QuantFrame 
     q.mode = mode;
     q.rateFlag = s_sub(total_bits, s_add(160, s_imult(b.fs_idx, 160))) > 0 ? 2 << 8 : 0;
     q.target = tbits_quant; q.total_bits = total_bits; q.qgain = qgain; q.nbits1 = ro[RO_NBITS1];
+    q.lastnz = ro[RO_LASTNZ]; // the first pass' (lc3_rate_warp.cuh); replaced below when the gain changed
 }
 
 // ---- quantise: thread t = (tile lane, part)
@@ -94,6 +95,14 @@ LC3_HD void qt_analyse(QuantFrame &q, i16 *xq, int nt, QuantWarp &w, const u8 *l
 {
     const i32 mode = q.mode, rateFlag = q.rateFlag;
     const int nt_half = nt >> 1;
+    // Without a gain change (mode -1) this pass repeats the first one (lc3_rate_warp.cuh) bin for bin: nothing is truncated,
+    // the last non-zero pair and the bit count are the ones that pass left in RO_LASTNZ / RO_NBITS1.
+    if (mode < 0) {
+        LC3_LANES(l)
+            if (l == 0) { q.lastnz_out = q.lastnz; q.nBits2 = q.nbits1; q.lsbMode = 0; }
+        LC3_LANES_END
+        return;
+    }
     LC3_LANES(l)
         i32 last = 0;
         for (int i = l; i < nt; i += 32)
@@ -110,10 +119,8 @@ LC3_HD void qt_analyse(QuantFrame &q, i16 *xq, int nt, QuantWarp &w, const u8 *l
             w.tv[2 + (k >> 1)] = (u8)t;
         }
     LC3_LANES_END
-    // Without a gain change (mode -1) this pass repeats the first one (lc3_rate_warp.cuh) bin for bin: nothing is
-    // truncated and the bit count is the one already in RO_NBITS1, so only the last non-zero pair was needed.
     i32 lastnz2 = lastnz, nBits2 = q.nbits1, tot = q.nbits1;
-    if (mode >= 0) {
+    {
         // block-wise: lane l owns tuples [l*T, (l+1)*T); their costs are kept for the prefix pass
         const int ntup = lastnz >> 1, T = (ntup + 31) >> 5;
         LC3_LANES(l)

@@ -172,6 +172,7 @@ LC3_HD void rate_warp_body(const LC3K_Batch &b, int li, RateShared &sh, const u8
             if (l == 0) {
                 SV<i32> ro = tile_view(b.rout, ft, RO_N, tl);
                 ro[RO_QGAIN] = qgain; ro[RO_QGAIN_MIN] = qgain_min; ro[RO_NBITS1] = nBits; ro[RO_TBITS_QUANT] = tbits_quant;
+                ro[RO_LASTNZ] = lastnz; // of the first pass: the final one unless the gain is adjusted (lc3_quant_tile.cuh)
             }
         LC3_LANES_END
     }
