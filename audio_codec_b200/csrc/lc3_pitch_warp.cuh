@@ -736,39 +736,35 @@ LC3_HD u32 hp50_run(const Hp50 &c, const i16 *in, i16 *out, i32 &m0_, i32 &m1_)
     return ovf;
 }
 
+// Everything in registers: the walk goes block by block (HP50_BLOCK samples = one register tile), the NEXT block's samples are
+// fetched before the current block's chain runs, results go straight back to b.r12, and the overflow check and the saturating
+// re-run are per block (the block's inputs are still in registers, its starting state is saved).  No per-lane arrays in
+// local memory: the earlier version kept a frame's samples and results there, and with one warp per scheduler nothing hid
+// those round trips (0.55 -> see DESIGN.md section 4).
 LC3_HD void scalar_body(const LC3K_Batch &b, int tile, int lane)
 {
     const int li = tile * LC3K_LANES + lane;
     if (li >= b.n_lanes) return;
     SV<i32> st = slot_view(b.st32, b.slot[li], ST32_N);
-    const int len = 32 * (b.dms / 25);
+    const int len = 32 * (b.dms / 25), nblk = len / HP50_BLOCK, total = b.n_frames * nblk; // blocks of the chunk
     i32 m0 = st[ST_MEM50_0], m1 = st[ST_MEM50_1];
     const Hp50 c = {rom_hp50_num[0], rom_hp50_num[1], rom_hp50_num[2], rom_hp50_den[0], rom_hp50_den[1]};
-    i16 bufs[2][128], res[128];
+    i16 cur[HP50_BLOCK], nxt[HP50_BLOCK], res[HP50_BLOCK];
+    auto row = [&](int blk) { return tile_view(b.r12, frame_tile(b, blk / nblk, tile), 128, lane) + (blk % nblk) * HP50_BLOCK; };
     {
-        SV<i16> r = tile_view(b.r12, frame_tile(b, 0, tile), 128, lane);
-#pragma unroll 16
-        for (int n = 0; n < len; n++) bufs[0][n] = r[n];
+        SV<i16> r = row(0);
+#pragma unroll
+        for (int j = 0; j < HP50_BLOCK; j++) cur[j] = r[j];
     }
-    for (int f = 0; f < b.n_frames; f++) {
-        const i16 *cur = bufs[f & 1];
-        i16 *nxt = bufs[(f + 1) & 1];
-        SV<i16> r = tile_view(b.r12, frame_tile(b, f, tile), 128, lane);
-        const bool more = f + 1 < b.n_frames;
-        SV<i16> rn = tile_view(b.r12, frame_tile(b, more ? f + 1 : f, tile), 128, lane);
+    for (int blk = 0; blk < total; blk++) {
+        SV<i16> r = row(blk), rn = row(blk + 1 < total ? blk + 1 : blk);
+#pragma unroll
+        for (int j = 0; j < HP50_BLOCK; j++) nxt[j] = rn[j]; // in flight during the chain below
         const i32 s0 = m0, s1 = m1;
-        u32 ovf = 0;
-        for (int n0 = 0; n0 < len; n0 += HP50_BLOCK) {
-            i16 pre[HP50_BLOCK];
+        const u32 ovf = hp50_run(c, cur, res, m0, m1);
+        if ((i32)ovf < 0) { m0 = s0; m1 = s1; hp50_frame_sat(c, cur, res, HP50_BLOCK, m0, m1); }
 #pragma unroll
-            for (int j = 0; j < HP50_BLOCK; j++) pre[j] = rn[n0 + j]; // next frame, in flight during the chain below
-            ovf |= hp50_run(c, cur + n0, res + n0, m0, m1);
-#pragma unroll
-            for (int j = 0; j < HP50_BLOCK; j++) nxt[n0 + j] = pre[j];
-        }
-        if ((i32)ovf < 0) { m0 = s0; m1 = s1; hp50_frame_sat(c, cur, res, len, m0, m1); }
-#pragma unroll 16
-        for (int n = 0; n < len; n++) r[n] = res[n];
+        for (int j = 0; j < HP50_BLOCK; j++) { r[j] = res[j]; cur[j] = nxt[j]; }
     }
     st[ST_MEM50_0] = m0; st[ST_MEM50_1] = m1;
 }
