@@ -20,6 +20,53 @@ template <int L> struct TwSlot {
     static constexpr int v = L == 20 ? 0 : L == 40 ? 1 : L == 60 ? 2 : L == 80 ? 3 : L == 120 ? 4 : L == 160 ? 5 : L == 240 ? 6 : L == 320 ? 7 : 8;
 };
 
+// DCT-IV of one frame in place (fx/dct4_fx.c:16-138): pre-twiddle -> complex FFT(N/2) -> post-twiddle.  The block shift s
+// (the headroom of y: the shift cannot overflow) is applied as the pre-twiddle loads.  Returns the scale of the FFT; the
+// caller adds it and then 2 to the block exponent (dct4_fx.c:93, :136).  Used by the encoder's MDCT below and by the
+// decoder's inverse MDCT (fx/imdct_fx.c:84).
+template <int N, class A, class B> LC3_HD i32 dct4_frame(A y, B w, i32 s)
+{
+    constexpr int M = N >> 1;
+    const i16 *tw = &rom_dct4_twiddle[rom_dct4_twiddle_off[TwSlot<N>::v]];
+    const i16 *sn = (N % 3 == 0) ? rom_sin480 : rom_sin320;
+    constexpr int step = (N % 3 == 0) ? 960 / N : 640 / N;
+    i32 a1, a2, a3, a4;
+    for (int k = 0, lo = 0, hi = N - 2; k < M - 1; k += 2, lo += 2, hi -= 2) {
+        // s is the block headroom: the shift cannot overflow
+        i32 p0 = (i32)((u32)y[lo] << s), p1 = (i32)((u32)y[lo + 1] << s), q0 = (i32)((u32)y[hi] << s), q1 = (i32)((u32)y[hi + 1] << s);
+        cmul_half(a1, a2, q1, p0, tw[2 * k], tw[2 * k + 1]);
+        cmul_half(a3, a4, q0, p1, tw[2 * k + 2], tw[2 * k + 3]);
+        y[lo] = a2; y[lo + 1] = a1;
+        y[hi] = a4; y[hi + 1] = -a3; // cmul_half outputs are below 2^31 in magnitude: no L_negate saturation
+    }
+    const i32 fft_scale = cfft<M>(y, w);
+
+    int lo = 0, hi = N - 2, idx = step;
+    constexpr int M2 = ((M + 1) >> 1) - 1;
+    cmul_half(a3, a4, y[hi], y[hi + 1], sn[2 * idx], sn[2 * idx + 1]);
+    y[hi + 1] = -(y[lo + 1] >> 1);
+    y[lo] = y[lo] >> 1;
+    for (int k = 1; k < M2; k++) {
+        y[lo + 1] = a3; y[hi] = a4;
+        lo += 2; hi -= 2;
+        cmul_half(a1, a2, y[lo + 1], y[lo], sn[2 * idx], sn[2 * idx + 1]);
+        idx += step;
+        cmul_half(a3, a4, y[hi], y[hi + 1], sn[2 * idx], sn[2 * idx + 1]);
+        y[hi + 1] = -a1;
+        y[lo] = a2;
+    }
+    y[lo + 1] = a3; y[hi] = a4;
+    lo += 2; hi -= 2;
+    cmul_half(a3, a4, y[lo + 1], y[lo], sn[2 * idx], sn[2 * idx + 1]);
+    a1 = mpy32x16k(y[hi], 23170) >> 1;
+    a2 = mpy32x16k(y[hi + 1], 23170) >> 1;
+    y[hi] = a1 + a2; // |a1|, |a2| < 2^30
+    y[lo + 1] = a1 - a2;
+    y[hi + 1] = -a3;
+    y[lo] = a4;
+    return fft_scale;
+}
+
 // XS(i): scaled 16-bit input sample i of this frame, i in [-memLen, N) (negative = previous frame).
 // y: N words, receives the spectrum.  w: N words of scratch.  Returns the block exponent.
 template <int N, class XS, class A, class B>
@@ -48,45 +95,7 @@ LC3_HD i32 mdct_frame(XS xs, i32 x_exp, const i16 *win, int wLen, int memLen, A 
     if (N <= 20) y_e = s_add(y_e, 2);
     else if (N <= 120) y_e = s_add(y_e, 1);
 
-    // ---- DCT-IV (fx/dct4_fx.c:16-138); the block shift is applied as the pre-twiddle loads
-    constexpr int M = N >> 1;
-    const i16 *tw = &rom_dct4_twiddle[rom_dct4_twiddle_off[TwSlot<N>::v]];
-    const i16 *sn = (N % 3 == 0) ? rom_sin480 : rom_sin320;
-    constexpr int step = (N % 3 == 0) ? 960 / N : 640 / N;
-    i32 a1, a2, a3, a4;
-    for (int k = 0, lo = 0, hi = N - 2; k < M - 1; k += 2, lo += 2, hi -= 2) {
-        // s is the block headroom: the shift cannot overflow
-        i32 p0 = (i32)((u32)y[lo] << s), p1 = (i32)((u32)y[lo + 1] << s), q0 = (i32)((u32)y[hi] << s), q1 = (i32)((u32)y[hi + 1] << s);
-        cmul_half(a1, a2, q1, p0, tw[2 * k], tw[2 * k + 1]);
-        cmul_half(a3, a4, q0, p1, tw[2 * k + 2], tw[2 * k + 3]);
-        y[lo] = a2; y[lo + 1] = a1;
-        y[hi] = a4; y[hi + 1] = -a3; // cmul_half outputs are below 2^31 in magnitude: no L_negate saturation
-    }
-    y_e = s_add(y_e, cfft<M>(y, w));
-
-    int lo = 0, hi = N - 2, idx = step;
-    constexpr int M2 = ((M + 1) >> 1) - 1;
-    cmul_half(a3, a4, y[hi], y[hi + 1], sn[2 * idx], sn[2 * idx + 1]);
-    y[hi + 1] = -(y[lo + 1] >> 1);
-    y[lo] = y[lo] >> 1;
-    for (int k = 1; k < M2; k++) {
-        y[lo + 1] = a3; y[hi] = a4;
-        lo += 2; hi -= 2;
-        cmul_half(a1, a2, y[lo + 1], y[lo], sn[2 * idx], sn[2 * idx + 1]);
-        idx += step;
-        cmul_half(a3, a4, y[hi], y[hi + 1], sn[2 * idx], sn[2 * idx + 1]);
-        y[hi + 1] = -a1;
-        y[lo] = a2;
-    }
-    y[lo + 1] = a3; y[hi] = a4;
-    lo += 2; hi -= 2;
-    cmul_half(a3, a4, y[lo + 1], y[lo], sn[2 * idx], sn[2 * idx + 1]);
-    a1 = mpy32x16k(y[hi], 23170) >> 1;
-    a2 = mpy32x16k(y[hi + 1], 23170) >> 1;
-    y[hi] = a1 + a2; // |a1|, |a2| < 2^30
-    y[lo + 1] = a1 - a2;
-    y[hi + 1] = -a3;
-    y[lo] = a4;
+    y_e = s_add(y_e, dct4_frame<N>(y, w, s));
     return s_add(y_e, 2);
 }
 

@@ -398,8 +398,9 @@ LC3_HD void sns_quantize(const i16 *scf, i32 *idx, i16 *scf_q)
     }
 }
 
-// fx/sns_interpolate_scf_fx.c:14-91 (encoder side)
-LC3_HD void sns_interp(const i16 *q, i16 *g, i16 *g_exp, int nbands)
+// fx/sns_interpolate_scf_fx.c:14-91.  INV = true: the encoder side (scale factors negated before the linear domain);
+// false: the decoder side
+template <bool INV = true> LC3_HD void sns_interp(const i16 *q, i16 *g, i16 *g_exp, int nbands)
 {
     i16 v[64];
     i32 t = 0, t2 = 0;
@@ -431,7 +432,7 @@ LC3_HD void sns_interp(const i16 *q, i16 *g, i16 *g_exp, int nbands)
     }
     for (i = 0; i < nbands; i++) {
         i32 e;
-        g[i] = (i16)m_invlog2_16(s_neg(v[i]), &e);
+        g[i] = (i16)m_invlog2_16(INV ? s_neg(v[i]) : (i32)v[i], &e);
         g_exp[i] = (i16)e;
     }
 }
