@@ -12,7 +12,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
 
-ERRORS = {0: "LC3_OK", 1: "LC3_ERROR", 3: "LC3_NULL_ERROR", 4: "LC3_SAMPLERATE_ERROR", 5: "LC3_CHANNELS_ERROR",
+ERRORS = {0: "LC3_OK", 1: "LC3_ERROR", 2: "LC3_DECODE_ERROR", 7: "LC3_NUMBYTES_ERROR", 8: "LC3_PLCMODE_ERROR", 3: "LC3_NULL_ERROR", 4: "LC3_SAMPLERATE_ERROR", 5: "LC3_CHANNELS_ERROR",
           6: "LC3_BITRATE_ERROR", 9: "LC3_EPMODE_ERROR", 10: "LC3_FRAMEMS_ERROR", 11: "LC3_ALIGN_ERROR",
           12: "LC3_EPMR_ERROR", 14: "LC3_BITRATE_UNSET_ERROR", 15: "LC3_BITRATE_SET_ERROR", 18: "LC3_BW_WARNING"}
 
@@ -68,6 +68,22 @@ def load_library():
                                                    C.c_int, C.c_uint32, C.c_void_p, C.c_int, C.c_size_t, C.c_int,
                                                    C.c_void_p]
         L.lc3plus_read_switching_file.argtypes = [C.c_char_p, C.c_void_p, C.c_int]
+        # decoder
+        L.lc3_dec_get_size.argtypes = [C.c_int, C.c_int, C.c_int]
+        L.lc3_dec_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
+        for n in ("lc3_dec_set_frame_dms", "lc3_dec_set_ep_enabled"):
+            getattr(L, n).argtypes = [C.c_void_p, C.c_int]
+        for n in ("lc3_dec_get_scratch_size", "lc3_dec_get_output_samples", "lc3_dec_get_delay", "lc3_dec_free",
+                  "lc3plus_dec_get_device"):
+            getattr(L, n).argtypes = [C.c_void_p]
+        for n in ("lc3_dec16", "lc3_dec24"):
+            getattr(L, n).argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+        L.lc3plus_dec_batch.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p,
+                                        C.c_size_t, C.c_int, C.c_void_p]
+        L.lc3plus_dec_kernel_launches.restype = C.c_longlong
+        L.lc3plus_dec_set_chunk_frames.argtypes = [C.c_int]
+        L.lc3plus_dec_profile_enable.argtypes = [C.c_int]
+        L.lc3plus_dec_profile_read.argtypes = [C.c_void_p]
         _LIB = L
     return _LIB
 
@@ -295,3 +311,99 @@ def read_switching_file(path):
     v = np.zeros(max(n, 1), dtype=np.int64)
     L.lc3plus_read_switching_file(os.fsencode(path), v.ctypes.data, n)
     return v[:n]
+
+
+# ---- decoder (include/lc3plus_b200.h): error-free streams, no concealment
+
+class Decoder:
+    """One LC3_Dec: lc3_dec_init -> lc3_dec_set_frame_dms -> lc3_dec16/24 (fx/codec_exe.c:206-215)."""
+
+    def __init__(self, samplerate, channels=1, frame_dms=100, plc_mode=1):
+        L = load_library()
+        size = L.lc3_dec_get_size(samplerate, channels, plc_mode)
+        self._mem = C.create_string_buffer(max(size, 64) + 16)
+        self.h = C.c_void_p((C.addressof(self._mem) + 15) & ~15)
+        self.channels = channels
+        self._live = False
+        r = L.lc3_dec_init(self.h, samplerate, channels, plc_mode)
+        if r:
+            raise LC3Error(r, "lc3_dec_init")
+        self._live = True
+        self._scratch = C.create_string_buffer(16)
+        r = L.lc3_dec_set_frame_dms(self.h, frame_dms)
+        if r:
+            raise LC3Error(r, "lc3_dec_set_frame_dms")
+
+    def close(self):
+        if self._live:
+            load_library().lc3_dec_free(self.h)
+            self._live = False
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def frame_len(self):
+        return load_library().lc3_dec_get_output_samples(self.h)
+
+    @property
+    def delay(self):
+        return load_library().lc3_dec_get_delay(self.h)
+
+    @property
+    def device(self):
+        return load_library().lc3plus_dec_get_device(self.h)
+
+    def dec(self, payload, bits=16, bfi_ext=0):
+        """payload: bytes of one frame -> ([channels, N] samples, return code 0 or 2 = LC3_DECODE_ERROR)"""
+        L = load_library()
+        payload = np.ascontiguousarray(payload, dtype=np.uint8)
+        out = np.zeros((self.channels, self.frame_len), dtype=np.int16 if bits == 16 else np.int32)
+        ptrs = (C.c_void_p * 2)()
+        for c in range(self.channels):
+            ptrs[c] = out[c].ctypes.data
+        r = (L.lc3_dec16 if bits == 16 else L.lc3_dec24)(self.h, payload.ctypes.data, len(payload), ptrs, self._scratch, bfi_ext)
+        if r not in (0, 2):
+            raise LC3Error(r, "lc3_dec")
+        return out, r
+
+
+class DecoderArray:
+    """The `LC3_Dec *const *decoders` argument of lc3plus_dec_batch, built once for a fixed set of decoders."""
+
+    def __init__(self, decoders):
+        self.decoders = list(decoders)
+        self.arr = (C.c_void_p * len(self.decoders))(*[d.h.value for d in self.decoders])
+
+    def __len__(self):
+        return len(self.decoders)
+
+
+def dec_batch(decoders, n_frames, in_bytes, in_stream_stride_bytes, num_bytes, pcm, pcm_stream_stride_bytes, bits=16, bfi=None):
+    """lc3plus_dec_batch.  in_bytes / pcm: numpy arrays or device addresses; num_bytes: int32 [n_streams]; bfi: optional uint8
+    [n_streams*n_frames].  Returns 0 or 2 (LC3_DECODE_ERROR: at least one frame did not decode); raises on anything else."""
+    L = load_library()
+    arr = decoders.arr if isinstance(decoders, DecoderArray) else (C.c_void_p * len(decoders))(*[d.h.value for d in decoders])
+    nb = np.ascontiguousarray(num_bytes, dtype=np.int32)
+    r = L.lc3plus_dec_batch(arr, len(decoders), n_frames, _addr(in_bytes), in_stream_stride_bytes, nb.ctypes.data, _addr(pcm),
+                            pcm_stream_stride_bytes, bits, bfi.ctypes.data if bfi is not None else None)
+    if r not in (0, 2):
+        raise LC3Error(r, "lc3plus_dec_batch")
+    return r
+
+
+def dec_kernel_launches():
+    return int(load_library().lc3plus_dec_kernel_launches())
+
+
+def dec_profile_enable(on=True):
+    load_library().lc3plus_dec_profile_enable(1 if on else 0)
+
+
+def dec_profile_read():
+    ms = (C.c_double * 4)()
+    load_library().lc3plus_dec_profile_read(ms)
+    return dict(zip(("upload", "entropy", "idct", "synth"), list(ms)))

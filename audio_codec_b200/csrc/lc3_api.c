@@ -978,6 +978,20 @@ LC3_Error lc3plus_set_device(int device)
     return LC3_OK;
 }
 int lc3plus_enc_get_device(const LC3_Enc *encoder) { return enc_ok(encoder) ? encoder->device : -1; }
+/* for lc3_dec_api.c: the device a new handle goes to (lc3plus_set_device, else the thread's current device); -1: none */
+int lc3b_pick_device(void)
+{
+    int device = tl_device;
+    if (device < 0) {
+        int n = 0;
+        if (cu_fail(cudaGetDeviceCount(&n), "cudaGetDeviceCount") || n <= 0) {
+            if (!g_err[0] || n <= 0) snprintf(g_err, sizeof(g_err), "no CUDA device: liblc3plus_b200 has no CPU path");
+            return -1;
+        }
+        if (cu_fail(cudaGetDevice(&device), "cudaGetDevice")) return -1;
+    }
+    return device;
+}
 
 long long lc3plus_kernel_launches(void)
 {

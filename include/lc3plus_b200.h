@@ -159,6 +159,55 @@ void lc3plus_profile_read_device(int device, double *ms);    /* one device's sha
 LC3_Error lc3plus_enc_set_bitrate_many(LC3_Enc *const *encoders, int n, const int *bitrates);
 /* NEW: last CUDA error string seen by the library ("" if none). */
 const char *lc3plus_last_error(void);
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * DECODER.  Drop-in for the decoder half of the reference API for ERROR-FREE streams: PCM identical,
+ * sample for sample, to lc3_dec16 / lc3_dec24 of the reference (fx/lc3.h:334-370, fx/dec_lc3.c:15-487) as long as every
+ * frame decodes.  NOT built: packet-loss and partial concealment (fx/plc_*.c, fx/pc_*.c) and the channel decoder
+ * (fx/al_fec.c fec_decoder).  A frame the reference would conceal (bfi_ext != 0, num_bytes == 0, or a payload its bit-error
+ * checks reject) is synthesised from a zero spectrum instead -- the stream's memories stay consistent -- and the call returns
+ * LC3_DECODE_ERROR, as the reference does; from there on the PCM differs from the reference's until the memories have
+ * run out (overlap: one frame; LTPF: while it stays active).  The plc_mode argument is checked and otherwise ignored. */
+typedef struct LC3_Dec LC3_Dec;                          /* fx/lc3.h:129 */
+typedef enum { LC3_PLC_STANDARD = 0, LC3_PLC_ADVANCED = 1 } LC3_PlcMode;                               /* fx/lc3.h:66-70 */
+#define LC3_DEC_MAX_SIZE 256                             /* fx/lc3.h:58 holds the signal memories; here they live on the device */
+LC3_Error lc3_dec_init(LC3_Dec *decoder, int samplerate, int channels, LC3_PlcMode plc_mode);          /* fx/lc3.h:334 */
+LC3_Error lc3_dec16(LC3_Dec *decoder, void *input_bytes, int num_bytes, int16_t **output_samples, void *scratch, int bfi_ext); /* fx/lc3.h:362 */
+LC3_Error lc3_dec24(LC3_Dec *decoder, void *input_bytes, int num_bytes, int32_t **output_samples, void *scratch, int bfi_ext); /* fx/lc3.h:370 */
+int lc3_dec_get_size(int samplerate, int channels, LC3_PlcMode plc_mode);                              /* fx/lc3.h:381 */
+int lc3_dec_get_scratch_size(const LC3_Dec *decoder);    /* fx/lc3.h:390 */
+int lc3_dec_get_output_samples(const LC3_Dec *decoder);  /* fx/lc3.h:398 */
+int lc3_dec_get_delay(const LC3_Dec *decoder);           /* fx/lc3.h:405 */
+LC3_Error lc3_dec_set_frame_dms(LC3_Dec *decoder, int frame_ms);                                       /* fx/lc3.h:415 */
+LC3_Error lc3_dec_set_ep_enabled(LC3_Dec *decoder, int ep_enabled); /* fx/lc3.h:425; LC3_EPMODE_ERROR for ep_enabled != 0 */
+LC3_EpModeRequest lc3_dec_get_ep_mode_request(const LC3_Dec *decoder); /* fx/lc3.h:447; always LC3_EPMR_ZERO */
+int lc3_dec_get_error_report(const LC3_Dec *decoder);    /* fx/lc3.h:457; always 0 */
+int lc3_dec_get_epok_flags(const LC3_Dec *decoder);      /* fx/lc3.h:466; always 0 */
+/* NEW: returns the decoder's device state to the pool.  Optional: re-initialising or abandoning the block leaks nothing. */
+LC3_Error lc3_dec_free(LC3_Dec *decoder);
+int lc3plus_dec_get_device(const LC3_Dec *decoder);
+
+/* NEW (no reference counterpart; replaces the caller's loop fx/codec_exe.c:332-500 around lc3_dec16/24).  Decodes n_frames
+ * consecutive frames of each of n_streams decoders: the same PCM and the same effect on every decoder's state as calling
+ * lc3_dec16 / lc3_dec24 n_frames times on each decoder with bfi_ext = 0.
+ *
+ *   in_bytes            frame f of stream s is read at (uint8_t*)in_bytes + s*in_stream_stride_bytes + f*num_bytes[s];
+ *                       channel payloads are concatenated inside a frame as lc3_enc16 writes them (fx/dec_lc3.c:455).
+ *   num_bytes           [n_streams] bytes per frame of each stream (all frames of a stream in one call have one size; 0 marks
+ *                       every frame of the stream as lost).  20..435 per channel (fx/defines.h:141-142), else LC3_NUMBYTES_ERROR.
+ *   pcm                 samples of stream s start at (char*)pcm + s*pcm_stream_stride_bytes; channels planar: channel c
+ *                       occupies n_frames*N samples from sample c*n_frames*N (N = lc3_dec_get_output_samples).  int16_t for
+ *                       bitdepth 16, int32_t (24-bit) for bitdepth 24.
+ *   bfi_flags           optional [n_streams*n_frames], stream-major: 1 where the frame did not decode.
+ *   in_bytes / pcm may be host or device pointers (device pointers avoid the copies).  The decoders of one call must share
+ *   sample rate, frame duration and device; byte counts and channel counts may differ.  A decoder may appear only once.
+ * Returns LC3_OK, or LC3_DECODE_ERROR when at least one frame did not decode (the PCM is still complete). */
+LC3_Error lc3plus_dec_batch(LC3_Dec *const *decoders, int n_streams, int n_frames, const void *in_bytes, size_t in_stream_stride_bytes,
+                            const int *num_bytes, void *pcm, size_t pcm_stream_stride_bytes, int bitdepth, uint8_t *bfi_flags);
+void lc3plus_dec_set_chunk_frames(int channel_frames);   /* channel-frames per chunk of the decoder's passes (0: default 163840) */
+long long lc3plus_dec_kernel_launches(void);
+void lc3plus_dec_profile_enable(int on);                 /* CUDA-event timing of the first chunk of every call */
+void lc3plus_dec_profile_read(double *ms /* [4]: upload, entropy pass, DCT pass, synthesis pass (+ download) */);
 /* NEW: upper bound on channel-frames processed per internal chunk, taken literally when set here (defaults, which never cut
  * a chunk below eight frames per stream: 163840 when the PCM is already on the
  * device, 204800 when it is copied from host memory chunk by chunk); up to three chunks are in flight at once, each on

@@ -171,18 +171,22 @@ class RefDec:
         self.frame_len = L.lc3_dec_get_output_samples(self.h)
         self.delay = L.lc3_dec_get_delay(self.h)
 
-    def decode(self, frames):
-        """frames: uint8 [n_frames, nbytes] -> int16 [channels, n_frames * N]; returns (pcm, number of frames flagged bad)"""
+    def decode(self, frames, bits=16, codes=None):
+        """frames: uint8 [n_frames, nbytes] -> int16 / int32 [channels, n_frames * N]; returns (pcm, number of frames flagged
+        bad); codes: optional list that receives the per-frame return value of lc3_dec16 / lc3_dec24"""
         L = ref_lib()
         frames = np.ascontiguousarray(frames, dtype=np.uint8)
         nf, nb = frames.shape
         N = self.frame_len
-        out = np.zeros((self.channels, nf * N), dtype=np.int16)
+        out = np.zeros((self.channels, nf * N), dtype=np.int16 if bits == 16 else np.int32)
         ptrs = (C.c_void_p * 2)()
         bad = 0
+        fn = L.lc3_dec16 if bits == 16 else L.lc3_dec24
         for f in range(nf):
             for c in range(self.channels):
                 ptrs[c] = out[c, f * N:].ctypes.data
-            r = L.lc3_dec16(self.h, C.c_void_p(frames[f].ctypes.data), nb, ptrs, self._scratch, 0)
+            r = fn(self.h, C.c_void_p(frames[f].ctypes.data), nb, ptrs, self._scratch, 0)
             bad += r != 0
+            if codes is not None:
+                codes.append(r)
         return out, bad
