@@ -406,4 +406,4 @@ def dec_profile_enable(on=True):
 def dec_profile_read():
     ms = (C.c_double * 4)()
     load_library().lc3plus_dec_profile_read(ms)
-    return dict(zip(("upload", "entropy", "idct", "synth"), list(ms)))
+    return dict(zip(("entropy_chunk0", "idct_chunk0", "synth_chunk0", "span"), list(ms)))

@@ -370,7 +370,6 @@ static LC3_Error dec_batch(LC3_Dec *const *decs, int n_streams, int n_frames, co
         const size_t out_bytes = (size_t)(n_streams - 1) * pcm_stream_stride + (size_t)decs[n_streams - 1]->cfg.channels * n_frames * N * sb;
         const uint8_t *d_in = (const uint8_t *)in;
         void *d_pcm = pcm;
-        if (c->prof) cudaEventRecord(c->pev[0], c->s);
         if (!in_dev) {
             if (ensure(&c->d_in[0], &c->in_cap[0], in_bytes)) goto out;
             if (dfail(cudaMemcpyAsync(c->d_in[0], in, in_bytes, cudaMemcpyHostToDevice, c->s), "payload upload")) goto out;
@@ -409,6 +408,7 @@ static LC3_Error dec_batch(LC3_Dec *const *decs, int n_streams, int n_frames, co
         for (int f0 = 0; f0 < n_frames; f0 += chunk) {
             b.frame0 = f0;
             b.n_frames = n_frames - f0 < chunk ? n_frames - f0 : chunk;
+            if (c->prof && f0 == 0) cudaEventRecord(c->pev[0], c->s);
             int e = lc3d_launch_entropy(&b, c->s);
             if (c->prof && f0 == 0) cudaEventRecord(c->pev[1], c->s);
             if (!e) e = lc3d_launch_idct(&b, c->s);
@@ -424,7 +424,8 @@ static LC3_Error dec_batch(LC3_Dec *const *decs, int n_streams, int n_frames, co
         if (dfail(cudaStreamSynchronize(c->s), "decoder batch")) goto out;
         if (c->prof) {
             float ms;
-            for (int k = 0; k < 4; k++) if (cudaEventElapsedTime(&ms, c->pev[k], c->pev[k + 1]) == cudaSuccess) c->prof_ms[k] += ms;
+            for (int k = 0; k < 3; k++) if (cudaEventElapsedTime(&ms, c->pev[k], c->pev[k + 1]) == cudaSuccess) c->prof_ms[k] += ms;
+            if (cudaEventElapsedTime(&ms, c->pev[0], c->pev[4]) == cudaSuccess) c->prof_ms[3] += ms;
         }
         int any = 0;
         /* device order is [frame][lane]; the caller gets [stream][frame] (a stream is bad in a frame if any channel is) */
@@ -479,7 +480,8 @@ long long lc3plus_dec_kernel_launches(void)
     for (int d = 0; d < LC3D_MAX_DEV; d++) if (g_dctx[d]) n += g_dctx[d]->launches;
     return n;
 }
-/* profiling of the first chunk of every call: ms[4] = upload, entropy, idct, synth (+ download in the last) accumulated */
+/* profiling: ms[4] = the entropy, DCT and synthesis kernels of the FIRST chunk of every call, and the device span of the whole call
+ * (first kernel to the end of the downloads), accumulated */
 void lc3plus_dec_profile_enable(int on)
 {
     for (int d = 0; d < LC3D_MAX_DEV; d++) if (g_dctx[d]) { g_dctx[d]->prof = on; memset(g_dctx[d]->prof_ms, 0, sizeof(g_dctx[d]->prof_ms)); }

@@ -14,16 +14,26 @@
 namespace lc3k {
 
 // ---- bit reader of the side-information end of the frame (read_bit / read_indice, fx/ari_codec.c:1530-1556,
-// fx/dec_entropy.c:284-301): bits run from the last byte towards the first, least significant bit first.  Reads outside
-// the frame (only a corrupt frame gets there) return 0 and raise `oob`.
-template <class B> struct BackReader { B buf; i32 bp, mask, nbytes, oob; };
+// fx/dec_entropy.c:284-301): bits run from the last byte towards the first, least significant bit first.  The reader keeps
+// the count of bits taken and a 32-bit window of the bytes ahead, refilled every 32 bits (four byte loads), instead of the
+// reference's byte pointer and mask, which follow from the count: bp_side = last - (nread >> 3), mask_side = 1 << (nread & 7).
+// Bytes before the start of the frame read as zero; rd_oob() tells whether a bit was TAKEN from there (only a corrupt frame
+// gets that far).
+template <class B> struct BackReader { B buf; i32 last /* index of the frame's last byte */, nread; u32 w; };
+template <class B> LC3_HD void rd_init(BackReader<B> &r, B buf, i32 nbytes) { r.buf = buf; r.last = nbytes - 1; r.nread = 0; r.w = 0; }
+template <class B> LC3_HD i32 rd_bp(const BackReader<B> &r) { return r.last - (r.nread >> 3); }
+template <class B> LC3_HD i32 rd_oob(const BackReader<B> &r) { return r.nread > ((r.last + 1) << 3); }
 template <class B> LC3_HD i32 rd_bit(BackReader<B> &r)
 {
-    i32 byte = 0;
-    if (r.bp >= 0 && r.bp < r.nbytes) byte = r.buf.get(r.bp); else r.oob = 1;
-    const i32 bit = (byte & r.mask) ? 1 : 0;
-    r.mask <<= 1;
-    if (r.mask == 0x100) { r.mask = 1; r.bp--; }
+    if ((r.nread & 31) == 0) {
+        const i32 p = r.last - (r.nread >> 3);
+        u32 w = 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++) if (p - j >= 0) w |= (u32)r.buf.get(p - j) << (8 * j);
+        r.w = w;
+    }
+    const i32 bit = (i32)((r.w >> (r.nread & 31)) & 1u);
+    r.nread++;
     return bit;
 }
 template <class B> LC3_HD i32 rd_bits(BackReader<B> &r, int n)
@@ -153,21 +163,30 @@ template <class B> LC3_HD i32 rdc_decode_tns_order(RangeDec<B> &s, const i16 *cu
     if (s.low >= (s.help << 10)) s.ber = 1;
     return val;
 }
+// range >= help >= 2^6 after the update (range was >= 2^16, freq >= 1): at most two bytes are shifted in
 template <class B> LC3_HD void rdc_update(RangeDec<B> &s, u32 cum, u32 freq)
 {
     s.low -= cum * s.help;
     s.range = s.help * freq;
-    while (s.range < (1u << 16)) {
-        s.low = ((s.low & 0xffffu) << 8) + rdc_byte(s);
-        s.range <<= 8;
-        if (s.ber) { s.range = 0x00ffffff; break; } // past the end of a corrupt frame: the caller stops at the flag
-    }
+#pragma unroll
+    for (int k = 0; k < 2; k++)
+        if (s.range < (1u << 16)) {
+            s.low = ((s.low & 0xffffu) << 8) + rdc_byte(s);
+            s.range <<= 8;
+        }
+    if (s.ber) s.range = 0x00ffffff; // past the end of a corrupt frame: the caller stops at the flag
 }
 
 struct AriOut { i32 bfi, resBits, nf_seed, zero_frame, x_absmax; i16 tns_idx[16]; };
 
 // processAriDecoder_fx for n_pc == 0, mode 0 (fx/ari_codec.c:409-1214).  x: SV<i16>-like, receives yLen bins.
 // lsb_ind: scratch of yLen / 2 words.  res: residual bits, packed.
+//
+// The reference walks the tuples and, per tuple, decodes `lev` escape symbols and one MSB symbol with sign / bit-plane bits
+// from the backward reader in between.  Here ONE loop iteration decodes ONE range-coder symbol (a single call site of the
+// decoder), so the 32 lanes of a warp -- 32 different frames -- stay converged through the decoder whatever their tuples look
+// like; what the symbol means (escape of level lev, or the MSB symbol that ends the tuple) is predicated.  The order inside
+// each of the two streams is the reference's: per tuple, bit planes in rising level, then the signs.
 template <class B, class XQ, class LI>
 LC3_HD void ari_decode(B bytes, BackReader<B> &r, i32 nbbits, int yLen, int fs_idx, int lpc_weighting, int dms, DecSide &si,
                        const AriTabs &T, XQ x, LI lsb_ind, u32 *res, AriOut &o)
@@ -192,11 +211,10 @@ LC3_HD void ari_decode(B bytes, BackReader<B> &r, i32 nbbits, int yLen, int fs_i
             rdc_update(st, (u32)rom_tns_order_cumfreq[lpc_weighting * 8 + ord - 1], (u32)rom_tns_order_freq[lpc_weighting * 8 + ord - 1]);
             if (st.ber) { o.bfi = 1; return; }
             for (int k = 0; k < ord; k++) {
-                if (r.bp < st.bp) { o.bfi = 1; return; }
+                if (rd_bp(r) < st.bp) { o.bfi = 1; return; }
                 const i16 *cum = &rom_tns_coef_cumfreq[k * 17];
                 const i32 v = rdc_decode17(st, [&](int q) { return (u32)cum[q]; });
                 o.tns_idx[8 * n + k] = (i16)v;
-                if (v > 16) { o.bfi = 1; return; }
                 rdc_update(st, (u32)cum[v], (u32)rom_tns_coef_freq[k * 17 + v]);
                 if (st.ber) { o.bfi = 1; return; }
             }
@@ -205,75 +223,51 @@ LC3_HD void ari_decode(B bytes, BackReader<B> &r, i32 nbbits, int yLen, int fs_i
     if (st.ber) { o.bfi = 1; return; }
 
     const int lsbMode = si.lsbMode;
-    int k;
-    for (k = 0; k < si.lastnz; k += 2) {
-        i32 t = c + rateFlag;
-        if (k > nt_half) t += 1 << 8;
-        const u32 *cf = T.cf + 17 * T.lut[t];
-        i32 sym = rdc_decode17(st, [&](int q) { return cf[q] & 0xffffu; });
+    const i32 esc1 = rom_ari_esc_nb[1], esc2 = rom_ari_esc_nb[2], esc3 = rom_ari_esc_nb[3];
+    i32 k = 0, lev = 0, a = 0, bb = 0, t = c + rateFlag, seed = 0, mx = 0, nnz = 0;
+    while (k < si.lastnz) {
+        const i32 tt = t + (lev == 0 ? 0 : (lev == 1 ? esc1 : (lev == 2 ? esc2 : esc3)));
+        const u32 *cf = T.cf + 17 * T.lut[tt];
+        const i32 sym = rdc_decode17(st, [&](int q) { return cf[q] & 0xffffu; });
         rdc_update(st, cf[sym] & 0xffffu, cf[sym] >> 16);
-        i32 a = 0, bb = 0;
-        if (sym == 0) {
-            c = ((c & 0xf) << 4) + 1;
-        } else if (sym < 16) {
-            a = sym & 3; bb = sym >> 2;
-            c = ((c & 0xf) << 4) + a + bb + 1;
-            if (a > 0 && rd_bit(r)) a = -a;
-            if (bb > 0 && rd_bit(r)) bb = -bb;
-        } else {
-            if (!lsbMode) { a = rd_bit(r); bb = rd_bit(r); }
-            cf = T.cf + 17 * T.lut[t + rom_ari_esc_nb[1]];
-            sym = rdc_decode17(st, [&](int q) { return cf[q] & 0xffffu; });
-            rdc_update(st, cf[sym] & 0xffffu, cf[sym] >> 16);
-            if (sym < 16) {
-                const i32 a1 = sym & 3, b1 = sym >> 2;
-                a += a1 << 1; bb += b1 << 1;
-                if (a > 0 && rd_bit(r)) a = -a;
-                if (bb > 0 && rd_bit(r)) bb = -bb;
-                c = ((c & 0xf) << 4) + ((a1 + b1) << 1) + 1;
-            } else {
-                a += rd_bit(r) << 1;
-                bb += rd_bit(r) << 1;
-                int lev;
-                i32 esc_nb = 0;
-                for (lev = 2; lev < 14; lev++) {
-                    esc_nb = imin(lev, 3);
-                    cf = T.cf + 17 * T.lut[t + rom_ari_esc_nb[esc_nb]];
-                    sym = rdc_decode17(st, [&](int q) { return cf[q] & 0xffffu; });
-                    rdc_update(st, cf[sym] & 0xffffu, cf[sym] >> 16);
-                    if (sym < 16 || st.ber) break;
-                    a += rd_bit(r) << lev;
-                    bb += rd_bit(r) << lev;
-                }
-                if (lev == 14 || st.ber) { o.bfi = 1; return; }
-                a += (sym & 3) << lev; bb += (sym >> 2) << lev;
-                if (a > 0 && rd_bit(r)) a = -a;
-                if (bb > 0 && rd_bit(r)) bb = -bb;
-                c = ((c & 0xf) << 4) + esc_nb + 12;
-            }
-            if (lsbMode) lsb_ind[lsb_cnt++] = k;
+        if (sym >= 16) { // escape: one more bit plane of both coefficients (the lowest one is deferred in lsbMode)
+            if (lev > 0 || !lsbMode) { a += rd_bit(r) << lev; bb += rd_bit(r) << lev; }
+            lev++;
+            if (lev == 14 || st.ber) { o.bfi = 1; return; }
+        } else {     // the tuple's MSB symbol
+            const i32 a1 = sym & 3, b1 = sym >> 2;
+            a += a1 << lev; bb += b1 << lev;
+            if (a > 0) { if (rd_bit(r)) a = -a; nnz++; }
+            if (bb > 0) { if (rd_bit(r)) bb = -bb; nnz++; }
+            c = ((c & 0xf) << 4) + (lev == 0 ? a1 + b1 + 1 : (lev == 1 ? ((a1 + b1) << 1) + 1 : imin(lev, 3) + 12));
+            if (lsbMode && lev > 0) lsb_ind[lsb_cnt++] = k;
+            x[k] = (i16)a; x[k + 1] = (i16)bb;
+            const i32 aa = a < 0 ? -a : a, ab = bb < 0 ? -bb : bb;
+            seed = l_mac0(l_mac0(seed, aa, k), ab, k + 1);
+            mx = imax(mx, imax(aa, ab));
+            if (st.bp - rd_bp(r) > 3 || st.ber || rd_oob(r)) { o.bfi = 1; return; }
+            k += 2; lev = 0; a = 0; bb = 0;
+            t = c + rateFlag;
+            if (k > nt_half) t += 1 << 8;
         }
-        x[k] = (i16)a; x[k + 1] = (i16)bb;
-        if (st.bp - r.bp > 3 || st.ber || r.oob) { o.bfi = 1; return; }
     }
     for (; k < yLen; k++) x[k] = 0;
 
-    const i32 nbits_side = nbbits - ((r.bp << 3) + (s_norm(r.mask) - 6));
+    const i32 nbits_side = r.nread; // = nbbits - (8 * bp_side + norm_s(mask_side) - 6) of the reference
     const i32 extra_bits = clz32(st.range) - 6; // norm_ul
     const i32 nbits_ari = (st.bp - 3) << 3;
     i32 n = nbbits - (nbits_ari + extra_bits + nbits_side);
     if (n < 0) { o.bfi = 1; return; }
 
     for (int w = 0; w < 13; w++) res[w] = 0;
-    if (!lsbMode) {
-        i32 cnt = 0;
-        for (k = 0; k < yLen && n > 0; k++)
-            if (x[k] != 0) { res[cnt >> 5] |= (u32)rd_bit(r) << (cnt & 31); cnt++; n--; }
+    if (!lsbMode) { // one residual bit per non-zero coefficient, in bin order, while bits remain (:991-1014)
+        const i32 cnt = imin(n, nnz);
+        for (i32 q = 0; q < cnt; q++) res[q >> 5] |= (u32)rd_bit(r) << (q & 31);
         o.resBits = cnt;
     } else {
         for (int q = 0; q < lsb_cnt; q++) {
             const int p = lsb_ind[q];
-            i32 a = x[p];
+            a = x[p];
             if (n == 0) break;
             i32 bit = rd_bit(r);
             n--;
@@ -288,7 +282,7 @@ LC3_HD void ari_decode(B bytes, BackReader<B> &r, i32 nbbits, int yLen, int fs_i
                 }
             }
             x[p] = (i16)a;
-            i32 bb = x[p + 1];
+            bb = x[p + 1];
             if (n == 0) break;
             bit = rd_bit(r);
             n--;
@@ -304,15 +298,21 @@ LC3_HD void ari_decode(B bytes, BackReader<B> &r, i32 nbbits, int yLen, int fs_i
             }
             x[p + 1] = (i16)bb;
         }
+        // the low bit plane changed the values: noise-filling seed and block maximum from the finished bins
+        seed = 0; mx = 0;
+        for (int i0 = 0; i0 < yLen; i0 += 8) {
+            i32 v[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) v[j] = i0 + j < yLen ? (i32)x[i0 + j] : 0;
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                const i32 av = s_abs(v[j]);
+                seed = l_mac0(seed, av, i0 + j);
+                mx = imax(mx, av);
+            }
+        }
     }
-    if (r.oob) { o.bfi = 1; return; }
-    // noise-filling seed and the block maximum of processAriDecoderScaling_fx (:1217-1256)
-    i32 seed = 0, mx = 0;
-    for (int i = 0; i < yLen; i++) {
-        const i32 av = s_abs(x[i]);
-        seed = l_mac0(seed, av, i);
-        mx = imax(mx, av);
-    }
+    if (rd_oob(r)) { o.bfi = 1; return; }
     o.nf_seed = sx16(seed);
     o.x_absmax = mx;
     o.zero_frame = (si.lastnz == 2 && x[0] == 0 && x[1] == 0 && si.gg_idx == 0 && si.fac_ns_idx == 7) ? 1 : 0;
@@ -421,7 +421,7 @@ template <class B> LC3_HD void dec_frame_body(const LC3D_Batch &b, int f, int ti
     si.tns_order[0] = si.tns_order[1] = 0; si.ltpf[0] = si.ltpf[1] = si.ltpf[2] = 0;
     for (int i = 0; i < 7; i++) si.scf[i] = 0;
     BackReader<B> r;
-    r.buf = bytes; r.nbytes = nbytes; r.bp = (nbbits - 1) >> 3; r.mask = 1; r.oob = 0;
+    rd_init(r, bytes, nbytes);
     i32 bfi = nbytes <= 0 ? 1 : dec_side_info(r, yLen, b.fs_idx, b.bw_bits, dms, si);
     AriOut ao;
     u32 res[13];
@@ -468,25 +468,35 @@ template <class B> LC3_HD void dec_frame_body(const LC3D_Batch &b, int f, int ti
     i32 bits = 0;
     if (nf_on)
         for (int k = nf_start - nf_w; k < nf_start + nf_w; k++) { if (xq[k] != 0) nzeros = -2 * nf_w - 1; else nzeros++; }
-    for (int i = 0; i < yLen; i++) {
-        const i32 q = xq[i];
-        i32 v = (i32)((u32)q << (16 + shift));
-        if (q != 0 && bits < ao.resBits) {
-            if (res_bit(res, bits) == 0) v = l_sub(v, q > 0 ? fac_m : fac_p);
-            else v = l_add(v, q > 0 ? fac_p : fac_m);
-            bits++;
-        }
-        if (nf_on && i >= nf_start && i < nbw) {
-            if (i < nbw - nf_w) { if (xq[i + nf_w] != 0) nzeros = -2 * nf_w - 1; else nzeros++; }
-            else nzeros++;
-            if (nzeros >= 0) {
-                nfseed = sx16(13849 + nfseed * 31821);
-                v = nfseed >= 0 ? nf_val : l_neg(nf_val);
+    // eight bins at a time, their loads (and the noise-filling look-ahead) issued before the first is used: the walk waits
+    // on the latency of its loads, not on arithmetic
+    for (int i0 = 0; i0 < yLen; i0 += 8) {
+        i32 qv[8 + 3];
+#pragma unroll
+        for (int j = 0; j < 8 + 3; j++) qv[j] = i0 + j < yLen ? (i32)xq[i0 + j] : 0;
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const int i = i0 + j;
+            if (i >= yLen) break;
+            const i32 q = qv[j];
+            i32 v = (i32)((u32)q << (16 + shift));
+            if (q != 0 && bits < ao.resBits) {
+                if (res_bit(res, bits) == 0) v = l_sub(v, q > 0 ? fac_m : fac_p);
+                else v = l_add(v, q > 0 ? fac_p : fac_m);
+                bits++;
             }
+            if (nf_on && i >= nf_start && i < nbw) {
+                if (i < nbw - nf_w) { if ((nf_w == 3 ? qv[j + 3] : qv[j + 1]) != 0) nzeros = -2 * nf_w - 1; else nzeros++; }
+                else nzeros++;
+                if (nzeros >= 0) {
+                    nfseed = sx16(13849 + nfseed * 31821);
+                    v = nfseed >= 0 ? nf_val : l_neg(nf_val);
+                }
+            }
+            v = mpy32x16(v, gg);
+            if (i < tf) range_add(r1, v); else range_add(r2, v);
+            d[i] = v;
         }
-        v = mpy32x16(v, gg);
-        if (i < tf) range_add(r1, v); else range_add(r2, v);
-        d[i] = v;
     }
     q_exp = s_add(q_exp, gg_e);
 
@@ -512,19 +522,27 @@ template <class B> LC3_HD void dec_frame_body(const LC3D_Batch &b, int f, int ti
     const int lo0 = tns_start0, hi0 = tns_nf == 2 ? tns_start1 : bw_stop, lo1 = tns_start1, hi1 = bw_stop;
     int band = 0, stop = bo[1];
     Range ry; range_init(ry);
-    for (int i = 0; i < yLen; i++) {
-        i32 v = d[i];
-        if (tns_on) {
-            v = l_shl(v, ts);
-            if (si.tns_order[0] > 0 && i >= lo0 && i < hi0) v = tns_iir(si.tns_order[0], rc[0], state, v);
-            else if (tns_nf == 2 && si.tns_order[1] > 0 && i >= lo1 && i < hi1) v = tns_iir(si.tns_order[1], rc[1], state, v);
+    for (int i0 = 0; i0 < yLen; i0 += 8) {
+        i32 dv[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) dv[j] = i0 + j < yLen ? d[i0 + j] : 0;
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const int i = i0 + j;
+            if (i >= yLen) break;
+            i32 v = dv[j];
+            if (tns_on) {
+                v = l_shl(v, ts);
+                if (si.tns_order[0] > 0 && i >= lo0 && i < hi0) v = tns_iir(si.tns_order[0], rc[0], state, v);
+                else if (tns_nf == 2 && si.tns_order[1] > 0 && i >= lo1 && i < hi1) v = tns_iir(si.tns_order[1], rc[1], state, v);
+            }
+            if (i < shaped) {
+                while (i >= stop) { band++; stop = bo[band + 1]; }
+                v = l_shl(mpy32x16(v, g[band]), g_exp[band]);
+            }
+            range_add(ry, v);
+            d[i] = v;
         }
-        if (i < shaped) {
-            while (i >= stop) { band++; stop = bo[band + 1]; }
-            v = l_shl(mpy32x16(v, g[band]), g_exp[band]);
-        }
-        range_add(ry, v);
-        d[i] = v;
     }
     for (int i = yLen; i < N; i++) d[i] = 0; // fx/imdct_fx.c:72-73
     dout[DO_Q_EXP] = q_exp;

@@ -206,8 +206,8 @@ LC3_Error lc3plus_dec_batch(LC3_Dec *const *decoders, int n_streams, int n_frame
                             const int *num_bytes, void *pcm, size_t pcm_stream_stride_bytes, int bitdepth, uint8_t *bfi_flags);
 void lc3plus_dec_set_chunk_frames(int channel_frames);   /* channel-frames per chunk of the decoder's passes (0: default 163840) */
 long long lc3plus_dec_kernel_launches(void);
-void lc3plus_dec_profile_enable(int on);                 /* CUDA-event timing of the first chunk of every call */
-void lc3plus_dec_profile_read(double *ms /* [4]: upload, entropy pass, DCT pass, synthesis pass (+ download) */);
+void lc3plus_dec_profile_enable(int on);                 /* CUDA-event timing */
+void lc3plus_dec_profile_read(double *ms /* [4]: entropy, DCT, synthesis kernel of the first chunk of every call; device span of the calls */);
 /* NEW: upper bound on channel-frames processed per internal chunk, taken literally when set here (defaults, which never cut
  * a chunk below eight frames per stream: 163840 when the PCM is already on the
  * device, 204800 when it is copied from host memory chunk by chunk); up to three chunks are in flight at once, each on
