@@ -14,34 +14,42 @@
 namespace lc3k {
 
 // ---- bit reader of the side-information end of the frame (read_bit / read_indice, fx/ari_codec.c:1530-1556,
-// fx/dec_entropy.c:284-301): bits run from the last byte towards the first, least significant bit first.  The reader keeps
-// the count of bits taken and a 32-bit window of the bytes ahead, refilled every 32 bits (four byte loads), instead of the
-// reference's byte pointer and mask, which follow from the count: bp_side = last - (nread >> 3), mask_side = 1 << (nread & 7).
-// Bytes before the start of the frame read as zero; rd_oob() tells whether a bit was TAKEN from there (only a corrupt frame
-// gets that far).
-template <class B> struct BackReader { B buf; i32 last /* index of the frame's last byte */, nread; u32 w; };
-template <class B> LC3_HD void rd_init(BackReader<B> &r, B buf, i32 nbytes) { r.buf = buf; r.last = nbytes - 1; r.nread = 0; r.w = 0; }
+// fx/dec_entropy.c:284-301): bits run from the last byte towards the first, least significant bit first.  Instead of the
+// reference's byte pointer and mask the reader keeps the count of bits taken and a 64-bit window of the bits ahead, refilled
+// one aligned 32-bit word at a time; pointer and mask follow from the count: bp_side = last - (nread >> 3), mask_side =
+// 1 << (nread & 7).  Bytes before the start of the frame read as zero; rd_oob() tells whether a bit was TAKEN from there
+// (only a corrupt frame gets that far).  B::get(i) = byte i of the frame, B::word(k) = bytes 4k..4k+3, little-endian.
+template <class B> struct BackReader { B buf; i32 last /* index of the frame's last byte */, nread, avail, next /* bytes [0, next) not in the window yet */; uint64_t w; };
+template <class B> LC3_HD void rd_init(BackReader<B> &r, B buf, i32 nbytes)
+{
+    r.buf = buf; r.last = nbytes - 1; r.nread = 0; r.avail = 0; r.w = 0; r.next = nbytes > 0 ? nbytes : 0;
+    while (r.next & 3) { r.w |= (uint64_t)(u32)buf.get(--r.next) << r.avail; r.avail += 8; } // down to a word boundary
+}
 template <class B> LC3_HD i32 rd_bp(const BackReader<B> &r) { return r.last - (r.nread >> 3); }
 template <class B> LC3_HD i32 rd_oob(const BackReader<B> &r) { return r.nread > ((r.last + 1) << 3); }
-template <class B> LC3_HD i32 rd_bit(BackReader<B> &r)
+LC3_HD u32 bswap32(u32 v)
 {
-    if ((r.nread & 31) == 0) {
-        const i32 p = r.last - (r.nread >> 3);
-        u32 w = 0;
-#pragma unroll
-        for (int j = 0; j < 4; j++) if (p - j >= 0) w |= (u32)r.buf.get(p - j) << (8 * j);
-        r.w = w;
-    }
-    const i32 bit = (i32)((r.w >> (r.nread & 31)) & 1u);
-    r.nread++;
-    return bit;
+#if defined(__CUDA_ARCH__)
+    return __byte_perm(v, 0, 0x0123);
+#else
+    return __builtin_bswap32(v);
+#endif
 }
-template <class B> LC3_HD i32 rd_bits(BackReader<B> &r, int n)
+// the next n bits (0 <= n <= 32), first bit read in bit 0
+template <class B> LC3_HD u32 rd_take(BackReader<B> &r, int n)
 {
-    i32 v = 0;
-    for (int i = 0; i < n; i++) v |= rd_bit(r) << i;
+    if (r.avail < n) { // avail < 32 here: one more word fits
+        u32 word = 0;
+        if (r.next > 0) { r.next -= 4; word = bswap32(r.buf.word(r.next >> 2)); }
+        r.w |= (uint64_t)word << r.avail;
+        r.avail += 32;
+    }
+    const u32 v = (u32)(r.w & (((uint64_t)1 << n) - 1));
+    r.w >>= n; r.avail -= n; r.nread += n;
     return v;
 }
+template <class B> LC3_HD i32 rd_bit(BackReader<B> &r) { return (i32)rd_take(r, 1); }
+template <class B> LC3_HD i32 rd_bits(BackReader<B> &r, int n) { return (i32)rd_take(r, n); }
 
 struct DecSide {
     i32 bw_idx, nfilt, lsbMode, lastnz, gg_idx, fac_ns_idx;
@@ -230,15 +238,22 @@ LC3_HD void ari_decode(B bytes, BackReader<B> &r, i32 nbbits, int yLen, int fs_i
         const u32 *cf = T.cf + 17 * T.lut[tt];
         const i32 sym = rdc_decode17(st, [&](int q) { return cf[q] & 0xffffu; });
         rdc_update(st, cf[sym] & 0xffffu, cf[sym] >> 16);
-        if (sym >= 16) { // escape: one more bit plane of both coefficients (the lowest one is deferred in lsbMode)
-            if (lev > 0 || !lsbMode) { a += rd_bit(r) << lev; bb += rd_bit(r) << lev; }
+        // the iteration's bits from the side stream in ONE take: an escape brings one more bit plane of both coefficients (the
+        // lowest one is deferred in lsbMode), the tuple's MSB symbol the signs of its non-zero coefficients
+        const bool esc = sym >= 16;
+        const i32 a1 = esc ? 0 : sym & 3, b1 = esc ? 0 : sym >> 2;
+        a += a1 << lev; bb += b1 << lev;
+        const int nb_a = esc ? (lev > 0 || !lsbMode) : a > 0, nb_b = esc ? nb_a : bb > 0;
+        const u32 tk = rd_take(r, nb_a + nb_b);
+        const i32 bit_a = nb_a ? (i32)(tk & 1u) : 0, bit_b = nb_b ? (i32)((tk >> nb_a) & 1u) : 0;
+        if (esc) {
+            a += bit_a << lev; bb += bit_b << lev;
             lev++;
             if (lev == 14 || st.ber) { o.bfi = 1; return; }
-        } else {     // the tuple's MSB symbol
-            const i32 a1 = sym & 3, b1 = sym >> 2;
-            a += a1 << lev; bb += b1 << lev;
-            if (a > 0) { if (rd_bit(r)) a = -a; nnz++; }
-            if (bb > 0) { if (rd_bit(r)) bb = -bb; nnz++; }
+        } else {
+            if (bit_a) a = -a;
+            if (bit_b) bb = -bb;
+            nnz += nb_a + nb_b;
             c = ((c & 0xf) << 4) + (lev == 0 ? a1 + b1 + 1 : (lev == 1 ? ((a1 + b1) << 1) + 1 : imin(lev, 3) + 12));
             if (lsbMode && lev > 0) lsb_ind[lsb_cnt++] = k;
             x[k] = (i16)a; x[k + 1] = (i16)bb;
@@ -262,7 +277,7 @@ LC3_HD void ari_decode(B bytes, BackReader<B> &r, i32 nbbits, int yLen, int fs_i
     for (int w = 0; w < 13; w++) res[w] = 0;
     if (!lsbMode) { // one residual bit per non-zero coefficient, in bin order, while bits remain (:991-1014)
         const i32 cnt = imin(n, nnz);
-        for (i32 q = 0; q < cnt; q++) res[q >> 5] |= (u32)rd_bit(r) << (q & 31);
+        for (i32 q = 0; q < cnt; q += 32) res[q >> 5] = rd_take(r, imin(32, cnt - q));
         o.resBits = cnt;
     } else {
         for (int q = 0; q < lsb_cnt; q++) {
@@ -493,7 +508,7 @@ template <class B> LC3_HD void dec_frame_body(const LC3D_Batch &b, int f, int ti
                     v = nfseed >= 0 ? nf_val : l_neg(nf_val);
                 }
             }
-            v = mpy32x16(v, gg);
+            v = mpy32x16k(v, gg); // gg >= 0 (mantissa of 2^x)
             if (i < tf) range_add(r1, v); else range_add(r2, v);
             d[i] = v;
         }
@@ -538,7 +553,7 @@ template <class B> LC3_HD void dec_frame_body(const LC3D_Batch &b, int f, int ti
             }
             if (i < shaped) {
                 while (i >= stop) { band++; stop = bo[band + 1]; }
-                v = l_shl(mpy32x16(v, g[band]), g_exp[band]);
+                v = l_shl(mpy32x16k(v, g[band]), g_exp[band]); // g > 0 (mantissa of 2^x)
             }
             range_add(ry, v);
             d[i] = v;

@@ -17,6 +17,7 @@ using namespace lc3k;
 struct SmemBytesIn {
     const u8 *base; // warp region + 4*lane
     __device__ i32 get(int i) const { return base[(i >> 2) * 132 + (i & 3)]; }
+    __device__ u32 word(int k) const { return *reinterpret_cast<const u32 *>(base + k * 132); }
 };
 
 #define DEC_WARPS 8

@@ -13,7 +13,11 @@ extern "C" {
 
 using namespace lc3k;
 
-struct HostBytes { const u8 *p; i32 get(int i) const { return p[i]; } };
+struct HostBytes {
+    const u8 *p;
+    i32 get(int i) const { return p[i]; }
+    u32 word(int k) const { u32 v; memcpy(&v, p + 4 * k, 4); return v; }
+};
 
 struct DSim {
     LC3DCfg cfg;
