@@ -30,8 +30,8 @@ struct LC3_Dec { /* lives in the caller's block; device state is referenced by s
 typedef struct {
     int device;
     pthread_mutex_t lock;
-    cudaStream_t s, cp;            /* kernels | copies of the other chunk */
-    cudaEvent_t in_ev[2], k_ev[2], out_ev[2];
+    cudaStream_t s, cp, dl;        /* kernels | payload uploads of the chunks ahead | PCM downloads of the chunks behind */
+    cudaEvent_t *in_ev, *k_ev; int n_ev; /* per chunk of a call: its payloads are on the device | its PCM is ready */
     int cap;                       /* slots, multiple of 32 */
     int32_t *st32; int16_t *st16;  /* device state pool, tile-interleaved (lc3_dec_layout.h) */
     int *free_list, n_free, next_fresh;
@@ -127,11 +127,8 @@ static DCtx *dctx_get(int device)
     c->device = device;
     pthread_mutex_init(&c->lock, NULL);
     if (dfail(cudaStreamCreateWithFlags(&c->s, cudaStreamNonBlocking), "cudaStreamCreate") ||
-        dfail(cudaStreamCreateWithFlags(&c->cp, cudaStreamNonBlocking), "cudaStreamCreate")) { free(c); return NULL; }
-    for (int i = 0; i < 2; i++)
-        if (dfail(cudaEventCreateWithFlags(&c->in_ev[i], cudaEventDisableTiming), "cudaEventCreate") ||
-            dfail(cudaEventCreateWithFlags(&c->k_ev[i], cudaEventDisableTiming), "cudaEventCreate") ||
-            dfail(cudaEventCreateWithFlags(&c->out_ev[i], cudaEventDisableTiming), "cudaEventCreate")) { free(c); return NULL; }
+        dfail(cudaStreamCreateWithFlags(&c->cp, cudaStreamNonBlocking), "cudaStreamCreate") ||
+        dfail(cudaStreamCreateWithFlags(&c->dl, cudaStreamNonBlocking), "cudaStreamCreate")) { free(c); return NULL; }
     for (int i = 0; i < 5; i++) if (dfail(cudaEventCreate(&c->pev[i]), "cudaEventCreate")) { free(c); return NULL; }
     if (pool_grow(c, 1024)) { free(c); return NULL; }
     g_dctx[device] = c;
@@ -174,6 +171,20 @@ static int ensure(void **p, size_t *cap, size_t need)
     size_t n = need + need / 4;
     CU(cudaMalloc(p, n));
     *cap = n;
+    return 0;
+}
+static int ensure_events(DCtx *c, int n)
+{
+    if (n <= c->n_ev) return 0;
+    cudaEvent_t *a = (cudaEvent_t *)realloc(c->in_ev, (size_t)n * sizeof(cudaEvent_t));
+    if (a) c->in_ev = a;
+    cudaEvent_t *k = (cudaEvent_t *)realloc(c->k_ev, (size_t)n * sizeof(cudaEvent_t));
+    if (k) c->k_ev = k;
+    if (!a || !k) return 1;
+    for (; c->n_ev < n; c->n_ev++) {
+        CU(cudaEventCreateWithFlags(&c->in_ev[c->n_ev], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&c->k_ev[c->n_ev], cudaEventDisableTiming));
+    }
     return 0;
 }
 static int flush_resets(DCtx *c)
@@ -370,9 +381,14 @@ static LC3_Error dec_batch(LC3_Dec *const *decs, int n_streams, int n_frames, co
         const size_t out_bytes = (size_t)(n_streams - 1) * pcm_stream_stride + (size_t)decs[n_streams - 1]->cfg.channels * n_frames * N * sb;
         const uint8_t *d_in = (const uint8_t *)in;
         void *d_pcm = pcm;
+        /* host buffers, every stream with the same byte and channel count: the chunks' payloads and PCM move as rectangles
+         * (rows = streams) on their own streams, uploads ahead of the kernels and downloads behind them */
+        int rect = (!in_dev || !out_dev) && n_streams > 0;
+        for (int i = 1; i < n_streams && rect; i++)
+            rect = num_bytes[i] == num_bytes[0] && decs[i]->cfg.channels == decs[0]->cfg.channels;
         if (!in_dev) {
             if (ensure(&c->d_in[0], &c->in_cap[0], in_bytes)) goto out;
-            if (dfail(cudaMemcpyAsync(c->d_in[0], in, in_bytes, cudaMemcpyHostToDevice, c->s), "payload upload")) goto out;
+            if (!rect && dfail(cudaMemcpyAsync(c->d_in[0], in, in_bytes, cudaMemcpyHostToDevice, c->s), "payload upload")) goto out;
             d_in = (const uint8_t *)c->d_in[0];
         }
         if (!out_dev) {
@@ -405,9 +421,24 @@ static LC3_Error dec_batch(LC3_Dec *const *decs, int n_streams, int n_frames, co
         for (int k = 0; k < N_DWORK; k++) if (need[k] && ensure(&c->work[0][k], &c->work_cap[0][k], need[k])) goto out;
         b.xq = (int16_t *)c->work[0][W_XQ]; b.spec = (int32_t *)c->work[0][W_SPEC]; b.dout = (int32_t *)c->work[0][W_DOUT];
         b.yrow = (int32_t *)c->work[0][W_YROW]; b.work = (int32_t *)c->work[0][W_WORK];
-        for (int f0 = 0; f0 < n_frames; f0 += chunk) {
+        const int n_chunks = (n_frames + chunk - 1) / chunk, nb0 = num_bytes[0], chn0 = decs[0]->cfg.channels;
+        const size_t in_pitch = n_streams > 1 ? in_stream_stride : (size_t)nb0 * n_frames;
+        const size_t out_pitch = n_streams > 1 ? pcm_stream_stride : (size_t)chn0 * n_frames * N * sb;
+        if (rect) {
+            if (ensure_events(c, n_chunks)) goto out;
+            if (dfail(cudaEventRecord(c->in_ev[0], c->s), "cudaEventRecord") || dfail(cudaStreamWaitEvent(c->cp, c->in_ev[0], 0), "cudaStreamWaitEvent")) goto out; /* after the tables */
+            if (!in_dev && nb0 > 0)
+                for (int k = 0; k < n_chunks; k++) {
+                    const int f0 = k * chunk, nf = n_frames - f0 < chunk ? n_frames - f0 : chunk;
+                    if (dfail(cudaMemcpy2DAsync((uint8_t *)c->d_in[0] + (size_t)f0 * nb0, in_pitch, (const uint8_t *)in + (size_t)f0 * nb0, in_pitch,
+                                                (size_t)nf * nb0, (size_t)n_streams, cudaMemcpyHostToDevice, c->cp), "payload upload") ||
+                        dfail(cudaEventRecord(c->in_ev[k], c->cp), "cudaEventRecord")) goto out;
+                }
+        }
+        for (int f0 = 0, k = 0; f0 < n_frames; f0 += chunk, k++) {
             b.frame0 = f0;
             b.n_frames = n_frames - f0 < chunk ? n_frames - f0 : chunk;
+            if (rect && !in_dev && nb0 > 0 && dfail(cudaStreamWaitEvent(c->s, c->in_ev[k], 0), "cudaStreamWaitEvent")) goto out;
             if (c->prof && f0 == 0) cudaEventRecord(c->pev[0], c->s);
             int e = lc3d_launch_entropy(&b, c->s);
             if (c->prof && f0 == 0) cudaEventRecord(c->pev[1], c->s);
@@ -417,11 +448,19 @@ static LC3_Error dec_batch(LC3_Dec *const *decs, int n_streams, int n_frames, co
             if (c->prof && f0 == 0) cudaEventRecord(c->pev[3], c->s);
             if (e) { dfail((cudaError_t)e, "decoder kernel launch"); goto out; }
             c->launches += 3;
+            if (rect && !out_dev) {
+                if (dfail(cudaEventRecord(c->k_ev[k], c->s), "cudaEventRecord") || dfail(cudaStreamWaitEvent(c->dl, c->k_ev[k], 0), "cudaStreamWaitEvent")) goto out;
+                for (int ch = 0; ch < chn0; ch++) {
+                    const size_t off = ((size_t)ch * n_frames + f0) * N * sb;
+                    if (dfail(cudaMemcpy2DAsync((uint8_t *)pcm + off, out_pitch, (const uint8_t *)d_pcm + off, out_pitch, (size_t)b.n_frames * N * sb,
+                                                (size_t)n_streams, cudaMemcpyDeviceToHost, c->dl), "pcm download")) goto out;
+                }
+            }
         }
-        if (!out_dev && dfail(cudaMemcpyAsync(pcm, d_pcm, out_bytes, cudaMemcpyDeviceToHost, c->s), "pcm download")) goto out;
+        if (!out_dev && !rect && dfail(cudaMemcpyAsync(pcm, d_pcm, out_bytes, cudaMemcpyDeviceToHost, c->s), "pcm download")) goto out;
         if (dfail(cudaMemcpyAsync(c->h_bfi, c->d_bfi, bfi_bytes, cudaMemcpyDeviceToHost, c->s), "flag download")) goto out;
         if (c->prof) cudaEventRecord(c->pev[4], c->s);
-        if (dfail(cudaStreamSynchronize(c->s), "decoder batch")) goto out;
+        if (dfail(cudaStreamSynchronize(c->s), "decoder batch") || dfail(cudaStreamSynchronize(c->dl), "decoder batch")) goto out;
         if (c->prof) {
             float ms;
             for (int k = 0; k < 3; k++) if (cudaEventElapsedTime(&ms, c->pev[k], c->pev[k + 1]) == cudaSuccess) c->prof_ms[k] += ms;
