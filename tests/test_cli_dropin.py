@@ -2,10 +2,11 @@
 fx/codec_exe.c:192-209 setup, :347 bitrate switch, :369 bandwidth, :418/:424 encode).
 
 oracle/_ref/LC3plus         = the unmodified reference, all of it.
-oracle/_ref/LC3plus_dropin  = the same codec_exe.c, source untouched, whose lc3_enc_* symbols are resolved by
-                              audio_codec_b200/liblc3plus_b200.so (decoder symbols still come from the reference).
+oracle/_ref/LC3plus_dropin  = the same codec_exe.c, source untouched, whose lc3_enc_* AND lc3_dec_* symbols are resolved by
+                              audio_codec_b200/liblc3plus_b200.so (first in link order; the rest comes from the reference).
 Both encode the same WAV; the .lc3plus files (header + per-frame length + payload, ETSI/Readme.txt:308-333) must be
-byte-identical.  Needs the GPU: the drop-in has no CPU path.
+byte-identical.  Both decode the same .lc3plus file (no error protection: the library has no channel decoder and no
+concealment); the WAV files must be byte-identical.  Needs the GPU: the drop-in has no CPU path.
 """
 import os
 import subprocess
@@ -66,4 +67,22 @@ def test_reference_cli_on_our_library(tmp_path, fs, ch, bits, ms, rate, extra):
         assert r.returncode == 0, (exe, r.stdout[-2000:], r.stderr[-2000:])
         outs.append(open(out, "rb").read())
     assert len(outs[0]) > 100
+    assert outs[0] == outs[1]
+
+
+@pytest.mark.parametrize("fs,ch,bits,ms,rate,extra", [c for c in CASES if "-epmode" not in c[5]])
+def test_reference_cli_decodes_on_our_library(tmp_path, fs, ch, bits, ms, rate, extra):
+    """fx/codec_exe.c:206-215 decoder setup, :468/:474 lc3_dec16 / lc3_dec24 per frame, delay compensation and WAV writer of the tool"""
+    wav = str(tmp_path / "in.wav")
+    write_wav(wav, fs, ch, bits, fs // 2, seed=fs + ch + bits + 1)
+    lc3 = str(tmp_path / "ref.lc3")
+    r = subprocess.run([REF, "-E", "-q", "-frame_ms", ms] + extra + [wav, lc3, str(rate)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-2000:])
+    outs = []
+    for exe, name in ((REF, "ref.wav"), (DROPIN, "b200.wav")):
+        out = str(tmp_path / name)
+        r = subprocess.run([exe, "-D", "-q", "-bps", str(bits), lc3, out], capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, (exe, r.stdout[-2000:], r.stderr[-2000:])
+        outs.append(open(out, "rb").read())
+    assert len(outs[0]) > 1000
     assert outs[0] == outs[1]
