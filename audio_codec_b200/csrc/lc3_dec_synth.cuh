@@ -18,7 +18,7 @@ struct SynthShared {
     i16 xf[2 * LC3K_MAX_N];                    // time signal of the frame: N output samples, then the new overlap memory
     i16 ola[LC3K_MAX_N];                       // overlap-add memory
     i16 bx[LC3D_MAX_LTPF_X + 2 + LC3K_MAX_N];  // LTPF input: ltpf_mem_x | current frame
-    i16 by[2][LC3D_BY_LEN];                    // LTPF output: ltpf_mem_y | current frame; ping-pong instead of the reference's memmove
+    i16 by[LC3D_BY_LEN];                       // LTPF output: ltpf_mem_y | current frame
     i16 z[128 + 16];                           // transition buffer of a pitch change (ltpf_decoder_fx.c:222-226)
 };
 
@@ -43,6 +43,21 @@ LC3_HD void warp_scale_sig(i16 *x, int n, i32 e)
     LC3_LANES(l)
         for (int k = l; k < n; k += 32) x[k] = (i16)scale_val(x[k], e, t);
     LC3_LANES_END
+}
+
+// x[k] = x[k + n] for k < len (the reference's basop_memmove towards the front), 32 elements at a time through registers: a
+// chunk only reads elements no earlier chunk has written (n > 0), and inside a chunk every lane has read before any writes
+LC3_HD void warp_shift_down(i16 *x, int len, int n)
+{
+    for (int k0 = 0; k0 < len; k0 += 32) {
+        LC3_PERLANE(i16, t, 1);
+        LC3_LANES(l)
+            if (k0 + l < len) LC3_PL(t, 0, l) = x[k0 + l + n];
+        LC3_LANES_END
+        LC3_LANES(l)
+            if (k0 + l < len) x[k0 + l] = LC3_PL(t, 0, l);
+        LC3_LANES_END
+    }
 }
 
 // ltpf_synth_filter (fx/ltpf_decoder_fx.c:268-366).  out[j] depends on out[j - pitch_int + shift - l], l >= 0: the shortest
@@ -97,11 +112,10 @@ template <int BITS> LC3_HD void synth_warp_body(const LC3D_Batch &b, int li, Syn
     LC3_LANES(l)
         for (int k = l; k < ola_len; k += 32) sh.ola[k] = s16[DS16_OLA + k];
         for (int k = l; k < x_len; k += 32) sh.bx[k] = s16[DS16_LTPF_X + k];
-        for (int k = l; k < y_len; k += 32) sh.by[0][k] = s16[DS16_LTPF_Y + k];
+        for (int k = l; k < y_len; k += 32) sh.by[k] = s16[DS16_LTPF_Y + k];
     LC3_LANES_END
     i32 mem_e = st[DST_OLA_EXP], old_e = st[DST_LTPF_E], old_pitch_int = st[DST_LTPF_PITCH_INT], old_pitch_fr = st[DST_LTPF_PITCH_FR];
     i32 old_gain = st[DST_LTPF_GAIN], mem_active = st[DST_LTPF_ACTIVE], old_sf_idx = st[DST_LTPF_SCALE_IDX];
-    int cur = 0; // which half of by holds ltpf_mem_y
 
     for (int f = 0; f < b.n_frames; f++) {
         SV<const i32> dout = tile_view((const i32 *)b.dout, dframe_tile(b, f, tile), DO_N, tl);
@@ -147,32 +161,32 @@ template <int BITS> LC3_HD void synth_warp_body(const LC3D_Batch &b, int li, Syn
         if (sf_idx < 0) ltpf_active = 0;
         if (ltpf_active != 0) gain = rom_ltpf_dec_gain[sf_idx];
 
-        i16 *by = sh.by[cur], *byn = sh.by[cur ^ 1];
+        i16 *by = sh.by;
         const i16 *pcm_src = sh.xf;
         if (ltpf_active == 0 && mem_active == 0) {
             const i32 s = s_sub(old_e, x_e);
             const int keep = y_len - N;
             if (s > 0) {
+                warp_shift_down(by, keep, N);
                 LC3_LANES(l)
-                    for (int k = l; k < keep; k += 32) byn[k] = by[k + N];
                     if (s > 15) {
-                        for (int k = l; k < N; k += 32) byn[keep + k] = 0;
+                        for (int k = l; k < N; k += 32) by[keep + k] = 0;
                         for (int k = l; k < x_len; k += 32) sh.bx[k] = 0;
                     } else {
-                        for (int k = l; k < N; k += 32) byn[keep + k] = (i16)s_shr(sh.xf[k], s);
+                        for (int k = l; k < N; k += 32) by[keep + k] = (i16)s_shr(sh.xf[k], s);
                         for (int k = l; k < x_len; k += 32) sh.bx[k] = (i16)s_shr(sh.xf[k + N - x_len], s);
                     }
                 LC3_LANES_END
             } else {
+                warp_shift_down(by, keep, N);
                 LC3_LANES(l)
-                    if (s < -15) { for (int k = l; k < keep; k += 32) byn[k] = 0; }
-                    else { for (int k = l; k < keep; k += 32) byn[k] = (i16)s_shl(by[k + N], s); }
-                    for (int k = l; k < N; k += 32) byn[keep + k] = sh.xf[k];
+                    if (s < -15) { for (int k = l; k < keep; k += 32) by[k] = 0; }
+                    else if (s < 0) { for (int k = l; k < keep; k += 32) by[k] = (i16)s_shl(by[k], s); }
+                    for (int k = l; k < N; k += 32) by[keep + k] = sh.xf[k];
                     for (int k = l; k < x_len; k += 32) sh.bx[k] = sh.xf[k + N - x_len];
                 LC3_LANES_END
                 old_e = x_e;
             }
-            cur ^= 1;
             old_pitch_int = pitch_int; old_pitch_fr = pitch_fr; old_gain = 0; mem_active = 0;
         } else {
             i16 *x = sh.bx + x_len, *yo = by + y_len;
@@ -215,19 +229,12 @@ template <int BITS> LC3_HD void synth_warp_body(const LC3D_Batch &b, int li, Syn
                     for (int k = N4 + l; k < N; k += 32) yo[k] = x[k];
                 LC3_LANES_END
             }
-            // the frame's output stays at yo[0..N) of the old half until the PCM is written; the memories move on
+            // the frame's output goes back to xf (the PCM is written from there); then the memories move on
             LC3_LANES(l)
-                for (int k = l; k < y_len; k += 32) byn[k] = by[k + N];
+                for (int k = l; k < N; k += 32) sh.xf[k] = yo[k];
             LC3_LANES_END
-            LC3_PERLANE(i16, tmpx, 1);
-            LC3_LANES(l)
-                if (l < x_len) LC3_PL(tmpx, 0, l) = sh.bx[N + l];
-            LC3_LANES_END
-            LC3_LANES(l)
-                if (l < x_len) sh.bx[l] = LC3_PL(tmpx, 0, l);
-            LC3_LANES_END
-            pcm_src = yo;
-            cur ^= 1;
+            warp_shift_down(by, y_len, N);
+            warp_shift_down(sh.bx, x_len, N);
             old_pitch_int = pitch_int; old_pitch_fr = pitch_fr; old_gain = gain; mem_active = ltpf_active;
         }
         old_sf_idx = sf_idx;
@@ -252,7 +259,7 @@ template <int BITS> LC3_HD void synth_warp_body(const LC3D_Batch &b, int li, Syn
     LC3_LANES(l)
         for (int k = l; k < ola_len; k += 32) s16[DS16_OLA + k] = sh.ola[k];
         for (int k = l; k < x_len; k += 32) s16[DS16_LTPF_X + k] = sh.bx[k];
-        for (int k = l; k < y_len; k += 32) s16[DS16_LTPF_Y + k] = sh.by[cur][k];
+        for (int k = l; k < y_len; k += 32) s16[DS16_LTPF_Y + k] = sh.by[k];
     LC3_LANES_END
     LC3_LANE0
         st[DST_OLA_EXP] = mem_e; st[DST_LTPF_E] = old_e; st[DST_LTPF_PITCH_INT] = old_pitch_int; st[DST_LTPF_PITCH_FR] = old_pitch_fr;

@@ -123,7 +123,7 @@ template <int N> __global__ void __launch_bounds__(32 * DEC_WARPS) kd_idct_lane(
 
 #define SYNTH_WARPS 4
 struct SynthSmem { SynthShared sh[SYNTH_WARPS]; i16 win[2 * LC3K_MAX_N]; };
-template <int BITS> __global__ void __launch_bounds__(32 * SYNTH_WARPS) kd_synth(LC3D_Batch b)
+template <int BITS> __global__ void __launch_bounds__(32 * SYNTH_WARPS, 7) kd_synth(LC3D_Batch b)
 {
     extern __shared__ __align__(16) unsigned char ds_smem[];
     SynthSmem &m = *reinterpret_cast<SynthSmem *>(ds_smem);
