@@ -305,33 +305,21 @@ static TabLay tab_layout(int n_lanes, int n_tiles)
     return t;
 }
 
-static LC3_Error dec_batch(LC3_Dec *const *decs, int n_streams, int n_frames, const void *in, size_t in_stream_stride,
-                           const int *num_bytes, void *pcm, size_t pcm_stream_stride, int bitdepth, uint8_t *bfi_out)
+/* One bucket: n_streams decoders that share sample rate, frame duration and device.  rows: the row of each of them in the
+ * caller's buffers and arrays (NULL: decoder i is row i); n_rows: rows of the whole call. */
+static LC3_Error dec_bucket(LC3_Dec *const *decs, const int *rows, int n_streams, int n_rows, int n_frames, const void *in, size_t in_stream_stride,
+                            const int *num_bytes, void *pcm, size_t pcm_stream_stride, int bitdepth, uint8_t *bfi_out, unsigned mark)
 {
-    if (!decs || !in || !pcm || !num_bytes) return LC3_NULL_ERROR;
-    if (bitdepth != 16 && bitdepth != 24) return LC3_ERROR;
-    if (n_streams <= 0 || n_frames <= 0) return LC3_OK;
-    for (int i = 0; i < n_streams; i++) if (!dec_ok(decs[i])) return LC3_NULL_ERROR;
+#define ROW(i) (rows ? rows[i] : (i))
     const LC3DCfg *g = &decs[0]->cfg;
     const int dev = decs[0]->device, N = g->N, sb = bitdepth == 16 ? 2 : 4;
     int n_lanes = 0;
-    for (int i = 0; i < n_streams; i++) {
-        const LC3DCfg *c = &decs[i]->cfg;
-        if (c->fs != g->fs || c->dms != g->dms || decs[i]->device != dev) {
-            lc3b_set_error("lc3plus_dec_batch: the decoders of one call must share sample rate, frame duration and device");
-            return LC3_ERROR;
-        }
-        n_lanes += c->channels;
-    }
+    for (int i = 0; i < n_streams; i++) n_lanes += decs[i]->cfg.channels;
+    (void)mark;
     pthread_mutex_lock(&g_dlock);
     DCtx *c = dctx_get(dev);
-    const unsigned mark = ++g_dcall;
     pthread_mutex_unlock(&g_dlock);
     if (!c) return LC3_ERROR;
-    for (int i = 0; i < n_streams; i++) {
-        if ((unsigned)decs[i]->batch_mark == mark) { lc3b_set_error("lc3plus_dec_batch: a decoder appears twice in one call"); return LC3_ERROR; }
-        decs[i]->batch_mark = (int)mark;
-    }
     LC3_Error ret = LC3_ERROR;
     pthread_mutex_lock(&c->lock);
     const int n_tiles = (n_lanes + 31) / 32;
@@ -351,8 +339,8 @@ static LC3_Error dec_batch(LC3_Dec *const *decs, int n_streams, int n_frames, co
         int li = 0, max_bytes = 0;
         for (int i = 0; i < n_streams; i++) {
             const LC3DCfg *dc = &decs[i]->cfg;
-            const int nb = num_bytes[i];
-            if (nb < 0 || (n_streams > 1 && (size_t)nb * n_frames > in_stream_stride)) { lc3b_set_error("lc3plus_dec_batch: num_bytes does not fit the input stride"); goto out; }
+            const int nb = num_bytes[ROW(i)];
+            if (nb < 0 || (n_rows > 1 && (size_t)nb * n_frames > in_stream_stride)) { lc3b_set_error("lc3plus_dec_batch: num_bytes does not fit the input stride"); goto out; }
             int off = 0;
             for (int ch = 0; ch < dc->channels; ch++, li++) {
                 const int cb = nb / dc->channels + (ch < nb % dc->channels); /* fx/dec_lc3.c:455 */
@@ -364,12 +352,12 @@ static LC3_Error dec_batch(LC3_Dec *const *decs, int n_streams, int n_frames, co
                 for (int k = 0; k < DCFG_N; k++) cfgw[((size_t)(li >> 5) * DCFG_N + k) * 32 + (li & 31)] = w[k];
                 slot[li] = decs[i]->slot[ch];
                 stride[li] = nb;
-                ioff[li] = (int64_t)i * (int64_t)in_stream_stride + off;
-                poff[li] = ((int64_t)i * (int64_t)pcm_stream_stride) / sb + (int64_t)ch * n_frames * N;
+                ioff[li] = (int64_t)ROW(i) * (int64_t)in_stream_stride + off;
+                poff[li] = ((int64_t)ROW(i) * (int64_t)pcm_stream_stride) / sb + (int64_t)ch * n_frames * N;
                 off += cb;
                 if (cb > max_bytes) max_bytes = cb;
             }
-            if (pcm_stream_stride % sb || (n_streams > 1 && pcm_stream_stride < (size_t)dc->channels * n_frames * N * sb)) {
+            if (pcm_stream_stride % sb || (n_rows > 1 && pcm_stream_stride < (size_t)dc->channels * n_frames * N * sb)) {
                 lc3b_set_error("lc3plus_dec_batch: pcm stride too small or misaligned"); goto out;
             }
         }
@@ -377,18 +365,29 @@ static LC3_Error dec_batch(LC3_Dec *const *decs, int n_streams, int n_frames, co
         if (dfail(cudaMemcpyAsync(c->tab_d, c->tab_h, tl.total, cudaMemcpyHostToDevice, c->s), "table upload")) goto out;
 
         const int in_dev = is_dev_ptr(in), out_dev = is_dev_ptr(pcm);
-        const size_t in_bytes = (size_t)(n_streams - 1) * in_stream_stride + (size_t)num_bytes[n_streams - 1] * n_frames;
-        const size_t out_bytes = (size_t)(n_streams - 1) * pcm_stream_stride + (size_t)decs[n_streams - 1]->cfg.channels * n_frames * N * sb;
+        /* staging mirrors the caller's buffers: sized for all rows of the call (a row's own length is at most its stride, or
+         * what the last row needs) */
+        size_t in_bytes = 0, out_bytes = 0;
+        for (int i = 0; i < n_streams; i++) {
+            const size_t ie = (size_t)ROW(i) * in_stream_stride + (size_t)num_bytes[ROW(i)] * n_frames;
+            const size_t oe = (size_t)ROW(i) * pcm_stream_stride + (size_t)decs[i]->cfg.channels * n_frames * N * sb;
+            if (ie > in_bytes) in_bytes = ie;
+            if (oe > out_bytes) out_bytes = oe;
+        }
         const uint8_t *d_in = (const uint8_t *)in;
         void *d_pcm = pcm;
         /* host buffers, every stream with the same byte and channel count: the chunks' payloads and PCM move as rectangles
          * (rows = streams) on their own streams, uploads ahead of the kernels and downloads behind them */
-        int rect = (!in_dev || !out_dev) && n_streams > 0;
+        int rect = (!in_dev || !out_dev) && !rows;
         for (int i = 1; i < n_streams && rect; i++)
             rect = num_bytes[i] == num_bytes[0] && decs[i]->cfg.channels == decs[0]->cfg.channels;
         if (!in_dev) {
             if (ensure(&c->d_in[0], &c->in_cap[0], in_bytes)) goto out;
-            if (!rect && dfail(cudaMemcpyAsync(c->d_in[0], in, in_bytes, cudaMemcpyHostToDevice, c->s), "payload upload")) goto out;
+            if (!rect) /* row by row: the rows of other buckets and devices are not this bucket's business */
+                for (int i = 0; i < n_streams; i++) {
+                    const size_t o = (size_t)ROW(i) * in_stream_stride, len = (size_t)num_bytes[ROW(i)] * n_frames;
+                    if (len && dfail(cudaMemcpyAsync((uint8_t *)c->d_in[0] + o, (const uint8_t *)in + o, len, cudaMemcpyHostToDevice, c->s), "payload upload")) goto out;
+                }
             d_in = (const uint8_t *)c->d_in[0];
         }
         if (!out_dev) {
@@ -421,7 +420,7 @@ static LC3_Error dec_batch(LC3_Dec *const *decs, int n_streams, int n_frames, co
         for (int k = 0; k < N_DWORK; k++) if (need[k] && ensure(&c->work[0][k], &c->work_cap[0][k], need[k])) goto out;
         b.xq = (int16_t *)c->work[0][W_XQ]; b.spec = (int32_t *)c->work[0][W_SPEC]; b.dout = (int32_t *)c->work[0][W_DOUT];
         b.yrow = (int32_t *)c->work[0][W_YROW]; b.work = (int32_t *)c->work[0][W_WORK];
-        const int n_chunks = (n_frames + chunk - 1) / chunk, nb0 = num_bytes[0], chn0 = decs[0]->cfg.channels;
+        const int n_chunks = (n_frames + chunk - 1) / chunk, nb0 = num_bytes[ROW(0)], chn0 = decs[0]->cfg.channels;
         const size_t in_pitch = n_streams > 1 ? in_stream_stride : (size_t)nb0 * n_frames;
         const size_t out_pitch = n_streams > 1 ? pcm_stream_stride : (size_t)chn0 * n_frames * N * sb;
         if (rect) {
@@ -457,7 +456,11 @@ static LC3_Error dec_batch(LC3_Dec *const *decs, int n_streams, int n_frames, co
                 }
             }
         }
-        if (!out_dev && !rect && dfail(cudaMemcpyAsync(pcm, d_pcm, out_bytes, cudaMemcpyDeviceToHost, c->s), "pcm download")) goto out;
+        if (!out_dev && !rect)
+            for (int i = 0; i < n_streams; i++) {
+                const size_t o = (size_t)ROW(i) * pcm_stream_stride, len = (size_t)decs[i]->cfg.channels * n_frames * N * sb;
+                if (dfail(cudaMemcpyAsync((uint8_t *)pcm + o, (const uint8_t *)d_pcm + o, len, cudaMemcpyDeviceToHost, c->s), "pcm download")) goto out;
+            }
         if (dfail(cudaMemcpyAsync(c->h_bfi, c->d_bfi, bfi_bytes, cudaMemcpyDeviceToHost, c->s), "flag download")) goto out;
         if (c->prof) cudaEventRecord(c->pev[4], c->s);
         if (dfail(cudaStreamSynchronize(c->s), "decoder batch") || dfail(cudaStreamSynchronize(c->dl), "decoder batch")) goto out;
@@ -468,17 +471,61 @@ static LC3_Error dec_batch(LC3_Dec *const *decs, int n_streams, int n_frames, co
         }
         int any = 0;
         /* device order is [frame][lane]; the caller gets [stream][frame] (a stream is bad in a frame if any channel is) */
-        if (bfi_out) memset(bfi_out, 0, (size_t)n_streams * n_frames);
+        if (bfi_out) for (int i = 0; i < n_streams; i++) memset(bfi_out + (size_t)ROW(i) * n_frames, 0, (size_t)n_frames);
         for (int f = 0; f < n_frames; f++) {
             int l2 = 0;
             for (int i = 0; i < n_streams; i++)
                 for (int ch = 0; ch < decs[i]->cfg.channels; ch++, l2++)
-                    if (c->h_bfi[(size_t)f * n_lanes + l2]) { any = 1; if (bfi_out) bfi_out[(size_t)i * n_frames + f] = 1; }
+                    if (c->h_bfi[(size_t)f * n_lanes + l2]) { any = 1; if (bfi_out) bfi_out[(size_t)ROW(i) * n_frames + f] = 1; }
         }
         ret = any ? LC3_DECODE_ERROR : LC3_OK;
     }
 out:
     pthread_mutex_unlock(&c->lock);
+    return ret;
+#undef ROW
+}
+
+/* Decoders of different sample rates, frame durations or devices in one call: grouped (in order of first appearance) and
+ * decoded group by group. */
+static LC3_Error dec_batch(LC3_Dec *const *decs, int n_streams, int n_frames, const void *in, size_t in_stream_stride,
+                           const int *num_bytes, void *pcm, size_t pcm_stream_stride, int bitdepth, uint8_t *bfi_out)
+{
+    if (!decs || !in || !pcm || !num_bytes) return LC3_NULL_ERROR;
+    if (bitdepth != 16 && bitdepth != 24) return LC3_ERROR;
+    if (n_streams <= 0 || n_frames <= 0) return LC3_OK;
+    for (int i = 0; i < n_streams; i++) if (!dec_ok(decs[i])) return LC3_NULL_ERROR;
+    pthread_mutex_lock(&g_dlock);
+    const unsigned mark = ++g_dcall;
+    pthread_mutex_unlock(&g_dlock);
+    int uniform = 1;
+    for (int i = 0; i < n_streams; i++) {
+        if ((unsigned)decs[i]->batch_mark == mark) { lc3b_set_error("lc3plus_dec_batch: a decoder appears twice in one call"); return LC3_ERROR; }
+        decs[i]->batch_mark = (int)mark;
+        if (decs[i]->cfg.fs != decs[0]->cfg.fs || decs[i]->cfg.dms != decs[0]->cfg.dms || decs[i]->device != decs[0]->device) uniform = 0;
+    }
+    if (uniform) return dec_bucket(decs, NULL, n_streams, n_streams, n_frames, in, in_stream_stride, num_bytes, pcm, pcm_stream_stride, bitdepth, bfi_out, mark);
+    if (is_dev_ptr(in) || is_dev_ptr(pcm)) {
+        for (int i = 1; i < n_streams; i++)
+            if (decs[i]->device != decs[0]->device) { lc3b_set_error("lc3plus_dec_batch: device buffers with decoders of several devices: make one call per device"); return LC3_ERROR; }
+    }
+    LC3_Dec **list = (LC3_Dec **)malloc((size_t)n_streams * sizeof(*list));
+    int *rows = (int *)malloc((size_t)n_streams * sizeof(int));
+    unsigned char *done = (unsigned char *)calloc((size_t)n_streams, 1);
+    if (!list || !rows || !done) { free(list); free(rows); free(done); return LC3_ERROR; }
+    LC3_Error ret = LC3_OK;
+    for (int i0 = 0; i0 < n_streams; i0++) {
+        if (done[i0]) continue;
+        int n = 0;
+        for (int i = i0; i < n_streams; i++)
+            if (!done[i] && decs[i]->cfg.fs == decs[i0]->cfg.fs && decs[i]->cfg.dms == decs[i0]->cfg.dms && decs[i]->device == decs[i0]->device) {
+                list[n] = decs[i]; rows[n] = i; n++; done[i] = 1;
+            }
+        const LC3_Error r = dec_bucket(list, rows, n, n_streams, n_frames, in, in_stream_stride, num_bytes, pcm, pcm_stream_stride, bitdepth, bfi_out, mark);
+        if (r == LC3_DECODE_ERROR) ret = r;
+        else if (r != LC3_OK) { ret = r; break; }
+    }
+    free(list); free(rows); free(done);
     return ret;
 }
 

@@ -12,8 +12,9 @@ the GPU encoder (bit-exact with the reference encoder, tests/test_gpu_parity.py)
             around the synchronous call)
   verified  PCM of the last timed step of both legs == the unmodified reference decoder's (oracle/_ref/refbench_dec, same
             payloads, same number of passes) on a sample of streams
-  roofline  integer-issue fraction: reference decoder's weighted ops per frame (profiles/wmops_dec.json, concealment
-            bookkeeping excluded) x frames/s over the measured integer issue peak; kernel ms of the first chunk
+  roofline  integer-issue fraction: reference decoder's weighted ops per frame (profiles/wmops_dec.json; the count includes
+            the concealment bookkeeping it runs on good frames) x frames/s over the measured integer issue peak; kernel ms of
+            the first chunk of every call
   cpu_baseline  the reference decoder on all host cores (oracle/_ref/refbench_dec), bounded sample
 """
 import argparse
@@ -30,7 +31,6 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 CONFIGS = {"c1": (48000, 100, 128000, 4096, 1000), "c3": (16000, 50, 32000, 12500, 1000)}
-PLC_WMOPS_STAGES = ("PLC::Update", "PLC::Main", "Partial Concealment")  # bookkeeping the reference runs on good frames; not built here
 
 
 def refdec(payloads, fs, dms, nb, nf, threads, out=None, repeat=1):
@@ -53,8 +53,28 @@ def main():
     ap.add_argument("--streams", type=int, default=0)
     ap.add_argument("--frames", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--gpus", type=int, default=1, help="under torchrun: one process per GPU, each decoding its own S streams (weak scaling, no collective)")
     args = ap.parse_args()
     import torch
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if dist is None:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
     import audio_codec_b200 as ac
     import bench
     from audio_codec_b200.synth import make_streams_fast
@@ -83,19 +103,20 @@ def main():
     th.start()
     ac.dec_profile_enable(True)
     n0 = ac.dec_kernel_launches()
-    torch.cuda.synchronize()
+    barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         rc = ac.dec_batch(decs, nf, d_bytes.data_ptr(), nf * nb, nbs, d_out.data_ptr(), nf * N * 2, 16)
         assert rc == 0
+    barrier()
     wall = time.perf_counter() - t0
     prof = ac.dec_profile_read()
     launches = ac.dec_kernel_launches() - n0
     ac.dec_profile_enable(False)
     stop.set(); th.join()
     clocks = bench.summarize_clocks(rows)
-    span_s = prof["span"] / 1e3
-    value = S * nf * args.steps / span_s
+    span_s = max_over_ranks(prof["span"] / 1e3)
+    value = world * S * nf * args.steps / span_s
     out_dev = d_out.cpu().numpy()
     for d in decs.decoders:
         d.close()
@@ -107,11 +128,12 @@ def main():
     decs = ac.DecoderArray([ac.Decoder(fs, 1, dms) for _ in range(S)])
     for _ in range(args.warmup):
         ac.dec_batch(decs, nf, t_in.numpy(), nf * nb, nbs, t_out.numpy(), nf * N * 2, 16)
+    barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         ac.dec_batch(decs, nf, t_in.numpy(), nf * nb, nbs, t_out.numpy(), nf * N * 2, 16)
-    e2e_s = time.perf_counter() - t0
-    e2e = S * nf * args.steps / e2e_s
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    e2e = world * S * nf * args.steps / e2e_s
     out_e2e = t_out.numpy()
 
     # ---- both legs against the reference decoder, same payloads, same number of passes
@@ -127,7 +149,7 @@ def main():
         verified = len(idx) * nf
 
     cpu = None
-    if have_ref and not args.no_cpu_baseline:
+    if have_ref and not args.no_cpu_baseline and world == 1:
         cores = os.cpu_count() or 1
         ns = min(S, max(cores * 2, 32))
         rate, secs, _, _ = refdec(np.ascontiguousarray(payloads[:ns, :200]), fs, dms, nb, 200, cores)
@@ -150,15 +172,18 @@ def main():
     except (OSError, KeyError):
         pass
     line = {"metric": "decoded LC3plus channel-frames per second (bit-exact with the reference decoder, error-free streams)", "value": value,
-            "unit": "frames/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": span_s * 1e3 / args.steps,
+            "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": span_s * 1e3 / args.steps,
             "wall_ms_per_step": wall * 1e3 / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int16/int32 fixed point",
             "data": "synthetic (audio_codec_b200.synth) encoded by the GPU encoder", "path": "decoder",
-            "config": {"workload": f"{args.config} geometry, decode: {S} streams x {nf} frames/step, {fs} Hz, {dms / 10} ms, {nb} bytes/frame",
+            "config": {"workload": f"{args.config} geometry, decode: {S} streams per GPU x {nf} frames/step, {fs} Hz, {dms / 10} ms, {nb} bytes/frame",
                        "inputs": "larger than L2 (payloads %.0f MB, PCM %.0f MB per step)" % (S * nf * nb / 1e6, S * nf * N * 2 / 1e6)},
             "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": S * nf * nb, "d2h_bytes_per_step": S * nf * N * 2,
-                    "pcie_GBps": S * nf * args.steps * (nb + N * 2) / e2e_s / 1e9},
+                    "pcie_GBps": world * S * nf * args.steps * (nb + N * 2) / e2e_s / 1e9},
             "gpu_launches": launches, "verified_frames": verified, "roofline": roof, "cpu_baseline": cpu, "clocks": clocks}
-    print(json.dumps(line))
+    if rank == 0:
+        print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":

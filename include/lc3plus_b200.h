@@ -199,8 +199,9 @@ int lc3plus_dec_get_device(const LC3_Dec *decoder);
  *                       occupies n_frames*N samples from sample c*n_frames*N (N = lc3_dec_get_output_samples).  int16_t for
  *                       bitdepth 16, int32_t (24-bit) for bitdepth 24.
  *   bfi_flags           optional [n_streams*n_frames], stream-major: 1 where the frame did not decode.
- *   in_bytes / pcm may be host or device pointers (device pointers avoid the copies).  The decoders of one call must share
- *   sample rate, frame duration and device; byte counts and channel counts may differ.  A decoder may appear only once.
+ *   in_bytes / pcm may be host or device pointers (device pointers avoid the copies).  Decoders may differ in sample rate,
+ *   frame duration, byte count and channel count (they are grouped internally; with host buffers and one configuration the
+ *   copies of the chunks overlap the kernels) and, with host buffers, in device.  A decoder may appear only once.
  * Returns LC3_OK, or LC3_DECODE_ERROR when at least one frame did not decode (the PCM is still complete). */
 LC3_Error lc3plus_dec_batch(LC3_Dec *const *decoders, int n_streams, int n_frames, const void *in_bytes, size_t in_stream_stride_bytes,
                             const int *num_bytes, void *pcm, size_t pcm_stream_stride_bytes, int bitdepth, uint8_t *bfi_flags);

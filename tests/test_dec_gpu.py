@@ -116,6 +116,52 @@ def test_dec_stereo_and_mixed_byte_counts():
         assert bad == 0 and np.array_equal(ref, out[s]), s
 
 
+def test_dec_mixed_configurations_in_one_call():
+    """BASELINE config c5's geometry for the decoder: sample rates, frame durations and byte counts mixed in one call, streams of
+    the groups interleaved; also spread over two devices when the box has them (host buffers)"""
+    if not lc3ref.have_ref():
+        pytest.skip("reference library absent")
+    import torch
+    import audio_codec_b200 as ac
+    cfgs = [(48000, 100, 128000), (16000, 50, 32000), (32000, 25, 96000), (8000, 100, 24000), (24000, 50, 64000)]
+    per, ms = 7, 300                       # 300 ms of every stream: 30 / 60 / 120 frames
+    frames, meta = [], []
+    for k, (fs, dms, br) in enumerate(cfgs):
+        N = fs // 100 * dms // 100
+        nf = ms * 10 // dms
+        pcm = make_streams(per, nf * N, fs, N, 16, first_stream=3 * k, silence_frames=5)
+        f = gpu_encode(fs, dms, br, pcm)
+        for s in range(per):
+            frames.append(f[s]); meta.append((fs, dms, nf, N))
+    order = [k * per + s for s in range(per) for k in range(len(cfgs))]      # interleave the groups
+    frames = [frames[i] for i in order]; meta = [meta[i] for i in order]
+    S = len(frames)
+    # one call needs one frame count: decode in steps of 10 ms worth of frames per stream?  No: the call takes n_frames for all
+    # streams, so streams of different frame durations are given the same NUMBER of frames (30) here
+    nf = 30
+    in_stride = max(f.shape[1] for f in frames) * nf
+    out_stride = 480 * nf * 2
+    buf = np.zeros((S, in_stride), dtype=np.uint8)
+    nbs = np.zeros(S, np.int32)
+    for i, f in enumerate(frames):
+        nbs[i] = f.shape[1]
+        buf[i, :nf * f.shape[1]] = f[:nf].reshape(-1)
+    ndev = torch.cuda.device_count()
+    decs = []
+    for i, (fs, dms, _, _) in enumerate(meta):
+        ac.set_device(i % 2 if ndev > 1 else -1)
+        decs.append(ac.Decoder(fs, 1, dms))
+    ac.set_device(-1)
+    out = np.zeros((S, out_stride // 2), dtype=np.int16)
+    bfi = np.ones((S, nf), dtype=np.uint8)
+    rc = ac.dec_batch(decs, nf, buf, in_stride, nbs, out, out_stride, 16, bfi)
+    assert rc == 0 and not bfi.any()
+    for i, (fs, dms, _, N) in enumerate(meta):
+        ref, bad = lc3ref.RefDec(fs, 1, dms).decode(frames[i][:nf], 16)
+        assert bad == 0 and np.array_equal(ref[0], out[i, :nf * N]), (i, fs, dms)
+        assert not out[i, nf * N:].any()
+
+
 def test_dec_single_frame_api_equals_reference():
     if not lc3ref.have_ref():
         pytest.skip("reference library absent")
