@@ -136,9 +136,7 @@ def test_dec_mixed_configurations_in_one_call():
     order = [k * per + s for s in range(per) for k in range(len(cfgs))]      # interleave the groups
     frames = [frames[i] for i in order]; meta = [meta[i] for i in order]
     S = len(frames)
-    # one call needs one frame count: decode in steps of 10 ms worth of frames per stream?  No: the call takes n_frames for all
-    # streams, so streams of different frame durations are given the same NUMBER of frames (30) here
-    nf = 30
+    nf = 30   # a call decodes the same NUMBER of frames of every stream, whatever their duration
     in_stride = max(f.shape[1] for f in frames) * nf
     out_stride = 480 * nf * 2
     buf = np.zeros((S, in_stride), dtype=np.uint8)
@@ -160,6 +158,36 @@ def test_dec_mixed_configurations_in_one_call():
         ref, bad = lc3ref.RefDec(fs, 1, dms).decode(frames[i][:nf], 16)
         assert bad == 0 and np.array_equal(ref[0], out[i, :nf * N]), (i, fs, dms)
         assert not out[i, nf * N:].any()
+
+
+@pytest.mark.parametrize("fs,dms,rates", [(16000, 100, (24000, 64000, 16000, 32000)), (48000, 100, (48000, 160000, 32000, 64000)),
+                                          (32000, 50, (40000, 128000, 32000)), (24000, 25, (64000, 200000, 96000))])
+def test_dec_byte_count_switching_between_calls(fs, dms, rates):
+    """the stream's frame size changes from call to call (the encoder switched bitrate, fx/codec_exe.c:340-349): the decoder follows
+    update_dec_bitrate (fx/dec_lc3.c:477-482) -- LTPF scale index, gain offset, TNS weighting -- with the LTPF memories carried
+    through the change (fade-out with the old index when the new rate switches the filter off)"""
+    if not lc3ref.have_ref():
+        pytest.skip("reference library absent")
+    import audio_codec_b200 as ac
+    N = fs // 100 * dms // 100
+    S, seg = 12, 20 * (100 // dms)
+    total = seg * len(rates)
+    pcm = make_streams(S, total * N, fs, N, 16, first_stream=5, silence_frames=3)
+    pcm[S // 2:] = make_bursts(S - S // 2, total * N, fs, 16, seed=11)
+    encs = [ac.Encoder(fs, 1, dms, rates[0]) for _ in range(S)]
+    decs = [ac.Decoder(fs, 1, dms) for _ in range(S)]
+    refs = [lc3ref.RefDec(fs, 1, dms) for _ in range(S)]
+    for k, br in enumerate(rates):
+        for e in encs:
+            e.set_bitrate(br)
+        nb = encs[0].num_bytes
+        fr = np.zeros((S, seg, nb), dtype=np.uint8)
+        ac.enc_batch(encs, seg, np.ascontiguousarray(pcm[:, k * seg * N:(k + 1) * seg * N]), seg * N * 2, 16, fr, seg * nb)
+        out = np.zeros((S, seg * N), dtype=np.int16)
+        assert ac.dec_batch(decs, seg, fr, seg * nb, np.full(S, nb, np.int32), out, seg * N * 2, 16) == 0
+        for s in range(S):
+            ref, bad = refs[s].decode(fr[s], 16)
+            assert bad == 0 and np.array_equal(ref[0], out[s]), (k, br, s)
 
 
 def test_dec_single_frame_api_equals_reference():
