@@ -11,7 +11,7 @@
 #include <stdint.h>
 
 enum { /* same numbering as LC3_Error, fx/lc3.h:102-126 */
-    LC3O_OK = 0, LC3O_ERROR = 1, LC3O_NULL_ERROR = 3, LC3O_SAMPLERATE_ERROR = 4, LC3O_CHANNELS_ERROR = 5,
+    LC3O_OK = 0, LC3O_ERROR = 1, LC3O_DECODE_ERROR = 2, LC3O_NULL_ERROR = 3, LC3O_SAMPLERATE_ERROR = 4, LC3O_CHANNELS_ERROR = 5,
     LC3O_BITRATE_ERROR = 6, LC3O_FRAMEMS_ERROR = 10, LC3O_BITRATE_UNSET_ERROR = 14, LC3O_BITRATE_SET_ERROR = 15,
     LC3O_BW_WARNING = 18
 };
@@ -45,4 +45,17 @@ int lc3o_enc16(lc3o_enc *e, int16_t **in, uint8_t *out, int *num_bytes);
 int lc3o_enc24(lc3o_enc *e, int32_t **in, uint8_t *out, int *num_bytes);
 int lc3o_enc16_trace(lc3o_enc *e, int16_t **in, uint8_t *out, int *num_bytes, lc3o_trace *tr);
 int lc3o_encode_stream16(lc3o_enc *e, const int16_t *pcm, long ch_stride, int n_frames, uint8_t *out);
+
+/* ---- decoder for good frames (oracle/lc3o_dec.c; fx/dec_lc3.c without concealment and channel decoding).
+ * Parity status: PINNED against the compiled reference decoder and the committed digests of its output
+ * (tests/test_oracle_dec.py, tests/golden/dec_golden.json). */
+typedef struct lc3o_dec lc3o_dec;
+lc3o_dec *lc3o_dec_new(int samplerate, int channels);
+void lc3o_dec_free(lc3o_dec *d);
+int lc3o_dec_set_frame_dms(lc3o_dec *d, int dms);
+int lc3o_dec_get_output_samples(const lc3o_dec *d);
+int lc3o_dec_get_delay(const lc3o_dec *d);
+/* LC3O_OK, or LC3O_DECODE_ERROR when the payload is not a valid frame (zero spectrum synthesised) */
+int lc3o_dec16(lc3o_dec *d, const uint8_t *in, int num_bytes, int16_t **out);
+int lc3o_dec24(lc3o_dec *d, const uint8_t *in, int num_bytes, int32_t **out);
 #endif

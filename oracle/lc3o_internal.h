@@ -36,6 +36,7 @@ void o_cfft(i32 *x, int len, i16 *scale);
 
 /* ---- lc3o_mdct.c (fx/mdct_fx.c, fx/dct4_fx.c) */
 void o_mdct(const i16 *x, i16 x_exp, int N, const i16 *w, int wLen, i16 *mem, int memLen, i32 *y, i16 *y_e);
+void o_dct4(i32 *p, i16 *p_e, int L);   /* dct_IV, fx/dct4_fx.c:16-138 (shared with the decoder's inverse MDCT) */
 
 /* ---- lc3o_pitch.c (fx/resamp12k8_fx.c, fx/olpa_fx.c, fx/ltpf_coder_fx.c) */
 typedef struct {
@@ -68,6 +69,9 @@ i16 o_bw_detect(const i32 *en, i16 en_exp, int fs_idx, int dms_idx);
 void o_sns_compute(i32 *en, i16 en_exp, int fs_idx, int nbands, i16 *scf, int attack, i16 att_damping);
 void o_sns_quantize(const i16 *scf, i32 idx[7], i16 *scf_q);
 void o_sns_interp(const i16 *scf_q, i16 *g, i16 *g_exp, int nbands);
+void o_sns_interp_dir(const i16 *scf_q, i16 *g, i16 *g_exp, int nbands, int inv_scf); /* inv_scf 0: the decoder side */
+void o_idct16(const i16 *in, i16 *out);                 /* fx/dct2_fx.c:111-206 */
+void o_pvq_unit_norm(i16 *xq, const i16 *y, i16 kmax);  /* fx/pvq_dec_fx.c:67-117 */
 void o_mdct_shape(i32 *d, const i16 *g, const i16 *g_exp, const i16 *bands, int nbands);
 
 /* ---- lc3o_tns.c (fx/tns_coder_fx.c, fx/levinson_fx.c) */

@@ -19,7 +19,7 @@ static inline void cmul_half(i32 *re, i32 *im, i32 a, i32 b, i16 c, i16 d)
 }
 
 /* fx/dct4_fx.c:16-138 */
-static void o_dct4(i32 *p, i16 *p_e, int L)
+void o_dct4(i32 *p, i16 *p_e, int L)
 {
     int M = L >> 1;
     const i16 *tw = &rom_dct4_twiddle[rom_dct4_twiddle_off[tw_slot(L)]];

@@ -147,7 +147,7 @@ static void dct16(const i16 *in, i16 *out)
 }
 
 /* fx/dct2_fx.c:111-206 */
-static void idct16(const i16 *in, i16 *out)
+void o_idct16(const i16 *in, i16 *out)
 {
     i16 a[16], b[16];
     a[8] = rot(in[1], 1136, in[15], -11529);  a[9] = rot(in[9], 8956, in[7], -7350);
@@ -276,7 +276,7 @@ static void pvq_search(const i16 *x, i16 *y_far, i16 *y_near, i16 *yA, i16 *yB)
 }
 
 /* fx/pvq_dec_fx.c:67-117 : unit-energy normalisation of an integer pulse vector, Q14 */
-static void pvq_unit_norm(i16 *xq, const i16 *y, i16 kmax)
+void o_pvq_unit_norm(i16 *xq, const i16 *y, i16 kmax)
 {
     i32 yy = l_mult0(y[0], y[0]);
     for (int i = 1; i < 16; i++) yy = l_mac0(yy, y[i], y[i]);
@@ -347,7 +347,7 @@ void o_sns_quantize(const i16 *scf, i32 idx[7], i16 *scf_q)
         y[2][i] = ynear[i];
         y[3][i] = yfar[i];
     }
-    for (int j = 0; j < 4; j++) pvq_unit_norm(shp[j], y[j], rom_sns_kval[j * 2]);
+    for (int j = 0; j < 4; j++) o_pvq_unit_norm(shp[j], y[j], rom_sns_kval[j * 2]);
 
     i32 best = I32_MAX_;
     int bj = 0, bg = 0;
@@ -361,7 +361,7 @@ void o_sns_quantize(const i16 *scf, i32 idx[7], i16 *scf_q)
             if (l_sub(mse, best) < 0) { best = mse; bj = j; bg = g; }
         }
     i16 rec[16];
-    idct16(shp[bj], rec);
+    o_idct16(shp[bj], rec);
     for (i = 0; i < 16; i++) scf_q[i] = s_add(scf_q[i], s_mult_r(rom_sns_gain[bj * 8 + bg], rec[i]));
 
     u32 ix; i16 ls;
@@ -382,7 +382,7 @@ void o_sns_quantize(const i16 *scf, i32 idx[7], i16 *scf_q)
 }
 
 /* fx/sns_interpolate_scf_fx.c:14-91 (encoder side: inv_scf = 1) */
-void o_sns_interp(const i16 *q, i16 *g, i16 *g_exp, int nbands)
+void o_sns_interp_dir(const i16 *q, i16 *g, i16 *g_exp, int nbands, int inv_scf)
 {
     i16 v[64], tmp[64], t = 0, t2 = 0;
     int i;
@@ -412,8 +412,9 @@ void o_sns_interp(const i16 *q, i16 *g, i16 *g_exp, int nbands)
         for (i = 0; i < k; i++) v[i] = s_mac_r(l_mult(v[2 * i], 16384), v[2 * i + 1], 16384);
         for (; i < nbands; i++) v[i] = v[k + i];
     }
-    for (i = 0; i < nbands; i++) g[i] = o_invlog2_16(s_neg(v[i]), &g_exp[i]);
+    for (i = 0; i < nbands; i++) g[i] = o_invlog2_16(inv_scf ? s_neg(v[i]) : v[i], &g_exp[i]);
 }
+void o_sns_interp(const i16 *q, i16 *g, i16 *g_exp, int nbands) { o_sns_interp_dir(q, g, g_exp, nbands, 1); }
 
 /* fx/mdct_shaping_fx.c:14-35 */
 void o_mdct_shape(i32 *d, const i16 *g, const i16 *g_exp, const i16 *bo, int nbands)

@@ -46,6 +46,14 @@ def oracle_lib():
         for n in ("lc3o_enc16", "lc3o_enc24"):
             getattr(_ora, n).argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         _ora.lc3o_enc16_trace.argtypes = [C.c_void_p] * 5
+        _ora.lc3o_dec_new.restype = C.c_void_p
+        _ora.lc3o_dec_new.argtypes = [C.c_int, C.c_int]
+        _ora.lc3o_dec_free.argtypes = [C.c_void_p]
+        _ora.lc3o_dec_set_frame_dms.argtypes = [C.c_void_p, C.c_int]
+        _ora.lc3o_dec_get_output_samples.argtypes = [C.c_void_p]
+        _ora.lc3o_dec_get_delay.argtypes = [C.c_void_p]
+        for n in ("lc3o_dec16", "lc3o_dec24"):
+            getattr(_ora, n).argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
     return _ora
 
 
@@ -186,6 +194,43 @@ class RefDec:
             for c in range(self.channels):
                 ptrs[c] = out[c, f * N:].ctypes.data
             r = fn(self.h, C.c_void_p(frames[f].ctypes.data), nb, ptrs, self._scratch, 0)
+            bad += r != 0
+            if codes is not None:
+                codes.append(r)
+        return out, bad
+
+
+class OracleDec:
+    """Our plain-C restatement of the decoder for good frames (oracle/lc3o_dec.c): test infrastructure.  Same interface as RefDec."""
+
+    def __init__(self, fs, channels=1, dms=100):
+        L = oracle_lib()
+        self.channels = channels
+        self.h = C.c_void_p(L.lc3o_dec_new(fs, channels))
+        assert self.h.value
+        assert L.lc3o_dec_set_frame_dms(self.h, dms) == 0
+        self.frame_len = L.lc3o_dec_get_output_samples(self.h)
+        self.delay = L.lc3o_dec_get_delay(self.h)
+
+    def __del__(self):
+        try:
+            oracle_lib().lc3o_dec_free(self.h)
+        except Exception:
+            pass
+
+    def decode(self, frames, bits=16, codes=None):
+        L = oracle_lib()
+        frames = np.ascontiguousarray(frames, dtype=np.uint8)
+        nf, nb = frames.shape
+        N = self.frame_len
+        out = np.zeros((self.channels, nf * N), dtype=np.int16 if bits == 16 else np.int32)
+        ptrs = (C.c_void_p * 2)()
+        bad = 0
+        fn = L.lc3o_dec16 if bits == 16 else L.lc3o_dec24
+        for f in range(nf):
+            for c in range(self.channels):
+                ptrs[c] = out[c, f * N:].ctypes.data
+            r = fn(self.h, C.c_void_p(frames[f].ctypes.data), nb, ptrs)
             bad += r != 0
             if codes is not None:
                 codes.append(r)
