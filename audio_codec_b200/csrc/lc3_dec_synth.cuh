@@ -65,11 +65,17 @@ LC3_HD void warp_shift_down(i16 *x, int len, int n)
 // ltpf_decoder_fx.c:66-88), so 16 (8 kHz) or 32 consecutive outputs are independent of each other and are computed by the
 // lanes side by side.  The fade factor alpha advances by a constant step from 0 or 0x7FFF and stays inside [0, 0x7FFF]
 // over the 2.5 ms it runs (step * length <= 32760), so alpha of sample j is alpha0 + j * step without saturation.
-LC3_HD void ltpf_synth(i16 *out, const i16 *in, int length, int pitch_int, int pitch_fr, i32 gain, int sf, int fs_idx, int fade)
+// The filter lengths are fixed per sample rate (ILEN interpolation taps, TLEN + 1 tilt taps): the taps live in registers and
+// the tap loops unroll.  The taps are ROM values above -32768, so L_mult's single saturating case (-32768 x -32768) cannot
+// occur and the product is a plain multiply-and-double; the accumulations keep the reference's saturating adds.
+template <int ILEN, int TLEN>
+LC3_HD void ltpf_synth_n(i16 *out, const i16 *in, int length, int pitch_int, int pitch_fr, i32 gain, int sf, int fs_idx, int fade)
 {
-    const i16 *ifl = &rom_ltpf_dec_inter[(fs_idx * 4 + pitch_fr) * 12];
-    const i16 *tfl = &rom_ltpf_dec_tilt[(fs_idx * 4 + sf) * 11];
-    const int ilen = rom_ltpf_dec_inter_len[fs_idx], tlen = rom_ltpf_dec_tilt_len[fs_idx];
+    i32 ifl[ILEN], tfl[TLEN + 1];
+#pragma unroll
+    for (int q = 0; q < ILEN; q++) ifl[q] = rom_ltpf_dec_inter[(fs_idx * 4 + pitch_fr) * 12 + q];
+#pragma unroll
+    for (int q = 0; q <= TLEN; q++) tfl[q] = rom_ltpf_dec_tilt[(fs_idx * 4 + sf) * 11 + q];
     const int x0off = -pitch_int + rom_ltpf_dec_inter_shift[fs_idx];
     i32 alpha0 = 0, step = 0;
     if (fade != 0) {
@@ -83,15 +89,26 @@ LC3_HD void ltpf_synth(i16 *out, const i16 *in, int length, int pitch_int, int p
             const int j = j0 + l;
             if (l < C && j < length) {
                 const i16 *x0 = out + j + x0off, *y0 = in + j;
-                i32 s = l_mult(x0[0], ifl[0]);
-                for (int q = 1; q < ilen; q++) s = l_mac(s, x0[-q], ifl[q]);
-                for (int q = 0; q < tlen; q++) s = l_msu(s, y0[-q], tfl[q]);
-                const i32 v = s_msu_r(s, y0[-tlen], tfl[tlen]);
+                i32 s = (x0[0] * ifl[0]) * 2;
+#pragma unroll
+                for (int q = 1; q < ILEN; q++) s = l_add(s, (x0[-q] * ifl[q]) * 2);
+#pragma unroll
+                for (int q = 0; q <= TLEN; q++) s = l_sub(s, (y0[-q] * tfl[q]) * 2);
+                const i32 v = l_round(s);
                 i32 k = s_mult_r(gain, v);
                 if (fade != 0) k = s_mult_r(k, alpha0 + j * step);
                 out[j] = (i16)s_add(in[j], k);
             }
         LC3_LANES_END
+    }
+}
+LC3_HD void ltpf_synth(i16 *out, const i16 *in, int length, int pitch_int, int pitch_fr, i32 gain, int sf, int fs_idx, int fade)
+{ // inter_filter_len / tilt_filter_len of fx/constants.c:2497, :2514
+    switch (fs_idx) {
+    case 0: case 1: ltpf_synth_n<4, 2>(out, in, length, pitch_int, pitch_fr, gain, sf, fs_idx, fade); break;
+    case 2: ltpf_synth_n<6, 4>(out, in, length, pitch_int, pitch_fr, gain, sf, fs_idx, fade); break;
+    case 3: ltpf_synth_n<8, 6>(out, in, length, pitch_int, pitch_fr, gain, sf, fs_idx, fade); break;
+    default: ltpf_synth_n<12, 10>(out, in, length, pitch_int, pitch_fr, gain, sf, fs_idx, fade); break;
     }
 }
 
