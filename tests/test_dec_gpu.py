@@ -264,6 +264,31 @@ def test_dec_lost_stream_and_argument_checks():
     assert L.lc3_dec_get_size(48000, 2, 1) > 0 and L.lc3_dec_get_size(48000, 3, 1) == 0
 
 
+@pytest.mark.parametrize("fs,dms,br,S,nf", [(48000, 100, 128000, 48, 2500), (48000, 100, 64000, 48, 2200), (16000, 50, 32000, 64, 4000),
+                                            (32000, 25, 96000, 40, 6000), (44100, 100, 96000, 24, 2100)])
+def test_dec_long_runs_equal_reference(fs, dms, br, S, nf):
+    """2000+ frames per stream in chunks of three calls (the exponents of the overlap and LTPF memories wander over a long run),
+    against the reference decoder run by oracle/_ref/refbench_dec on the same payloads"""
+    exe = os.path.join(os.path.dirname(HERE), "oracle", "_ref", "refbench_dec")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/refbench_dec not built")
+    import subprocess
+    import tempfile
+    N = (48000 if fs == 44100 else fs) // 100 * dms // 100
+    pcm = make_streams_fast(S, nf * N, fs, N, 16, n_unique=S)
+    pcm[S // 2:] = make_bursts(S - S // 2, nf * N, fs, 16, seed=21)
+    frames = gpu_encode(fs, dms, br, pcm)
+    out, rc = gpu_decode(fs, dms, frames, 16, cuts=(nf // 3, nf // 3 * 2 + 1))
+    assert rc == 0
+    with tempfile.TemporaryDirectory() as d:
+        frames.tofile(os.path.join(d, "in.bin"))
+        r = subprocess.run([exe, os.path.join(d, "in.bin"), str(fs), str(dms), str(frames.shape[2]), str(S), str(nf), str(min(S, os.cpu_count() or 1)),
+                            os.path.join(d, "out.pcm")], capture_output=True, text=True, check=True).stdout.split()
+        assert int(r[4]) == 0
+        ref = np.fromfile(os.path.join(d, "out.pcm"), dtype=np.int16).reshape(S, nf * N)
+    assert np.array_equal(ref, out[:, 0])
+
+
 def test_dec_full_size_round_trip_c1():
     """BASELINE.json config c1 geometry (4096 streams x 48 kHz / 10 ms / 128 kbps), 100 frames: encode -> decode on the device,
     a sample of streams against the reference decoder, every stream against the delayed input (a codec at 128 kbps keeps the
