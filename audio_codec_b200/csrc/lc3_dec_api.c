@@ -6,7 +6,8 @@
  * (fx/al_fec.c fec_decoder) are not built: a payload the reference would conceal is synthesised as a zero spectrum, flagged
  * per frame, and the call returns LC3_DECODE_ERROR; lc3_dec_set_ep_enabled(1) is refused.
  *
- * One context per device, as the encoder's (lc3_api.c), but synchronous: a call returns when its PCM is in place. */
+ * One context per device, as the encoder's (lc3_api.c), but synchronous: a call returns when its PCM is in place.  Inside a
+ * call with host buffers the payload uploads run ahead of the kernels and the PCM downloads behind them, chunk by chunk. */
 #include <cuda_runtime_api.h>
 #include <pthread.h>
 #include <stdio.h>
@@ -37,8 +38,8 @@ typedef struct {
     int *free_list, n_free, next_fresh;
     int32_t *reset_list; int n_reset, cap_reset;
     void *d_list; size_t list_cap;
-    size_t work_cap[2][N_DWORK]; void *work[2][N_DWORK];
-    size_t in_cap[2], out_cap[2], bfi_cap; void *d_in[2], *d_out[2]; uint8_t *d_bfi, *h_bfi; size_t hbfi_cap;
+    size_t work_cap[N_DWORK]; void *work[N_DWORK];   /* per-chunk work buffers (the chunks of a call run one after another) */
+    size_t in_cap, out_cap, bfi_cap; void *d_in, *d_out; uint8_t *d_bfi, *h_bfi; size_t hbfi_cap; /* staging that mirrors host buffers */
     unsigned char *tab_h, *tab_d; size_t tab_cap;
     long long launches;
     double prof_ms[4]; int prof; cudaEvent_t pev[5];
@@ -382,17 +383,17 @@ static LC3_Error dec_bucket(LC3_Dec *const *decs, const int *rows, int n_streams
         for (int i = 1; i < n_streams && rect; i++)
             rect = num_bytes[i] == num_bytes[0] && decs[i]->cfg.channels == decs[0]->cfg.channels;
         if (!in_dev) {
-            if (ensure(&c->d_in[0], &c->in_cap[0], in_bytes)) goto out;
+            if (ensure(&c->d_in, &c->in_cap, in_bytes)) goto out;
             if (!rect) /* row by row: the rows of other buckets and devices are not this bucket's business */
                 for (int i = 0; i < n_streams; i++) {
                     const size_t o = (size_t)ROW(i) * in_stream_stride, len = (size_t)num_bytes[ROW(i)] * n_frames;
-                    if (len && dfail(cudaMemcpyAsync((uint8_t *)c->d_in[0] + o, (const uint8_t *)in + o, len, cudaMemcpyHostToDevice, c->s), "payload upload")) goto out;
+                    if (len && dfail(cudaMemcpyAsync((uint8_t *)c->d_in + o, (const uint8_t *)in + o, len, cudaMemcpyHostToDevice, c->s), "payload upload")) goto out;
                 }
-            d_in = (const uint8_t *)c->d_in[0];
+            d_in = (const uint8_t *)c->d_in;
         }
         if (!out_dev) {
-            if (ensure(&c->d_out[0], &c->out_cap[0], out_bytes)) goto out;
-            d_pcm = c->d_out[0];
+            if (ensure(&c->d_out, &c->out_cap, out_bytes)) goto out;
+            d_pcm = c->d_out;
         }
         const size_t bfi_bytes = (size_t)n_frames * n_lanes;
         if (ensure((void **)&c->d_bfi, &c->bfi_cap, bfi_bytes)) goto out;
@@ -417,9 +418,9 @@ static LC3_Error dec_bucket(LC3_Dec *const *decs, const int *rows, int n_streams
         if (chunk > n_frames) chunk = n_frames;
         const size_t ftl = (size_t)chunk * n_tiles * 32;
         const size_t need[N_DWORK] = {ftl * N * 2, ftl * N * 4, ftl * DO_N * 4, ftl * N * 4, N < 160 ? ftl * N * 4 : 0};
-        for (int k = 0; k < N_DWORK; k++) if (need[k] && ensure(&c->work[0][k], &c->work_cap[0][k], need[k])) goto out;
-        b.xq = (int16_t *)c->work[0][W_XQ]; b.spec = (int32_t *)c->work[0][W_SPEC]; b.dout = (int32_t *)c->work[0][W_DOUT];
-        b.yrow = (int32_t *)c->work[0][W_YROW]; b.work = (int32_t *)c->work[0][W_WORK];
+        for (int k = 0; k < N_DWORK; k++) if (need[k] && ensure(&c->work[k], &c->work_cap[k], need[k])) goto out;
+        b.xq = (int16_t *)c->work[W_XQ]; b.spec = (int32_t *)c->work[W_SPEC]; b.dout = (int32_t *)c->work[W_DOUT];
+        b.yrow = (int32_t *)c->work[W_YROW]; b.work = (int32_t *)c->work[W_WORK];
         const int n_chunks = (n_frames + chunk - 1) / chunk, nb0 = num_bytes[ROW(0)], chn0 = decs[0]->cfg.channels;
         const size_t in_pitch = n_streams > 1 ? in_stream_stride : (size_t)nb0 * n_frames;
         const size_t out_pitch = n_streams > 1 ? pcm_stream_stride : (size_t)chn0 * n_frames * N * sb;
@@ -429,7 +430,7 @@ static LC3_Error dec_bucket(LC3_Dec *const *decs, const int *rows, int n_streams
             if (!in_dev && nb0 > 0)
                 for (int k = 0; k < n_chunks; k++) {
                     const int f0 = k * chunk, nf = n_frames - f0 < chunk ? n_frames - f0 : chunk;
-                    if (dfail(cudaMemcpy2DAsync((uint8_t *)c->d_in[0] + (size_t)f0 * nb0, in_pitch, (const uint8_t *)in + (size_t)f0 * nb0, in_pitch,
+                    if (dfail(cudaMemcpy2DAsync((uint8_t *)c->d_in + (size_t)f0 * nb0, in_pitch, (const uint8_t *)in + (size_t)f0 * nb0, in_pitch,
                                                 (size_t)nf * nb0, (size_t)n_streams, cudaMemcpyHostToDevice, c->cp), "payload upload") ||
                         dfail(cudaEventRecord(c->in_ev[k], c->cp), "cudaEventRecord")) goto out;
                 }

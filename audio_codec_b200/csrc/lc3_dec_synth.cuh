@@ -15,7 +15,7 @@ namespace lc3k {
 #define LC3D_BY_LEN (LC3D_MAX_LTPF_Y + 3 + LC3K_MAX_N)
 struct SynthShared {
     WarpRed red;
-    i16 xf[2 * LC3K_MAX_N];                    // time signal of the frame: N output samples, then the new overlap memory
+    i16 xf[2 * LC3K_MAX_N];                    // time signal of the frame: N samples (after the LTPF: the output), then the new overlap memory
     i16 ola[LC3K_MAX_N];                       // overlap-add memory
     i16 bx[LC3D_MAX_LTPF_X + 2 + LC3K_MAX_N];  // LTPF input: ltpf_mem_x | current frame
     i16 by[LC3D_BY_LEN];                       // LTPF output: ltpf_mem_y | current frame
@@ -179,7 +179,6 @@ template <int BITS> LC3_HD void synth_warp_body(const LC3D_Batch &b, int li, Syn
         if (ltpf_active != 0) gain = rom_ltpf_dec_gain[sf_idx];
 
         i16 *by = sh.by;
-        const i16 *pcm_src = sh.xf;
         if (ltpf_active == 0 && mem_active == 0) {
             const i32 s = s_sub(old_e, x_e);
             const int keep = y_len - N;
@@ -261,14 +260,14 @@ template <int BITS> LC3_HD void synth_warp_body(const LC3D_Batch &b, int li, Syn
             const i32 scale = s_sub(15, x_e);
             i16 *dst = (i16 *)b.pcm + b.pcm_off[li] + (size_t)(b.frame0 + f) * N;
             LC3_LANES(l)
-                for (int k = l; k < N; k += 32) dst[k] = (i16)l_round(l_shr(l_dep_h(pcm_src[k]), scale));
+                for (int k = l; k < N; k += 32) dst[k] = (i16)l_round(l_shr(l_dep_h(sh.xf[k]), scale));
             LC3_LANES_END
         } else {
             const i32 scale = s_sub(s_sub(31 + 16, 24), x_e);
             const i32 offset = l_shr(32768, s_sub(16, scale));
             i32 *dst = (i32 *)b.pcm + b.pcm_off[li] + (size_t)(b.frame0 + f) * N;
             LC3_LANES(l)
-                for (int k = l; k < N; k += 32) dst[k] = l_shr(l_add(l_dep_h(pcm_src[k]), offset), scale);
+                for (int k = l; k < N; k += 32) dst[k] = l_shr(l_add(l_dep_h(sh.xf[k]), offset), scale);
             LC3_LANES_END
         }
     }
