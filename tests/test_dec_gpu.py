@@ -289,6 +289,29 @@ def test_dec_long_runs_equal_reference(fs, dms, br, S, nf):
     assert np.array_equal(ref, out[:, 0])
 
 
+def test_dec_reinit_resets_state_and_returns_slots():
+    """the reference owns no memory, so callers re-initialise a decoder block without telling anybody: the block's device
+    state must start over and its old slots must go back to the pool (5000 re-initialisations stay inside the first pool)"""
+    import audio_codec_b200 as ac
+    L = ac.load_library()
+    fs, dms, br, nf, N = 24000, 100, 48000, 12, 240
+    pcm = make_streams(1, nf * N, fs, N, 16, first_stream=4)
+    frames = gpu_encode(fs, dms, br, pcm)
+    nb = frames.shape[2]
+    d = ac.Decoder(fs, 1, dms)
+    out1 = np.zeros((1, nf * N), np.int16)
+    assert ac.dec_batch([d], nf, frames, nf * nb, np.array([nb], np.int32), out1, nf * N * 2, 16) == 0
+    for _ in range(5000):
+        assert L.lc3_dec_init(d.h, fs, 1, 1) == 0
+    assert L.lc3_dec_set_frame_dms(d.h, dms) == 0
+    out2 = np.zeros((1, nf * N), np.int16)
+    assert ac.dec_batch([d], nf, frames, nf * nb, np.array([nb], np.int32), out2, nf * N * 2, 16) == 0
+    assert np.array_equal(out1, out2)
+    out3 = np.zeros((1, nf * N), np.int16)      # without re-initialising, the second pass continues the stream: different PCM
+    assert ac.dec_batch([d], nf, frames, nf * nb, np.array([nb], np.int32), out3, nf * N * 2, 16) == 0
+    assert not np.array_equal(out1, out3)
+
+
 def test_dec_full_size_round_trip_c1():
     """BASELINE.json config c1 geometry (4096 streams x 48 kHz / 10 ms / 128 kbps), 100 frames: encode -> decode on the device,
     a sample of streams against the reference decoder, every stream against the delayed input (a codec at 128 kbps keeps the
