@@ -15,18 +15,11 @@ namespace lc3k {
 
 // ---- bit reader of the side-information end of the frame (read_bit / read_indice, fx/ari_codec.c:1530-1556,
 // fx/dec_entropy.c:284-301): bits run from the last byte towards the first, least significant bit first.  Instead of the
-// reference's byte pointer and mask the reader keeps the count of bits taken and a 64-bit window of the bits ahead, refilled
-// one aligned 32-bit word at a time; pointer and mask follow from the count: bp_side = last - (nread >> 3), mask_side =
+// reference's byte pointer and mask the reader keeps the count of bits taken and two 32-bit words of the bits ahead (a take
+// is one funnel shift), refilled one aligned word at a time; pointer and mask follow from the count: bp_side = last - (nread >> 3), mask_side =
 // 1 << (nread & 7).  Bytes before the start of the frame read as zero; rd_oob() tells whether a bit was TAKEN from there
 // (only a corrupt frame gets that far).  B::get(i) = byte i of the frame, B::word(k) = bytes 4k..4k+3, little-endian.
-template <class B> struct BackReader { B buf; i32 last /* index of the frame's last byte */, nread, avail, next /* bytes [0, next) not in the window yet */; uint64_t w; };
-template <class B> LC3_HD void rd_init(BackReader<B> &r, B buf, i32 nbytes)
-{
-    r.buf = buf; r.last = nbytes - 1; r.nread = 0; r.avail = 0; r.w = 0; r.next = nbytes > 0 ? nbytes : 0;
-    while (r.next & 3) { r.w |= (uint64_t)(u32)buf.get(--r.next) << r.avail; r.avail += 8; } // down to a word boundary
-}
-template <class B> LC3_HD i32 rd_bp(const BackReader<B> &r) { return r.last - (r.nread >> 3); }
-template <class B> LC3_HD i32 rd_oob(const BackReader<B> &r) { return r.nread > ((r.last + 1) << 3); }
+template <class B> struct BackReader { B buf; i32 last /* index of the frame's last byte */, nread, pos /* bit position in cur */, next /* bytes [0, next) not loaded yet */; u32 cur, nxt; };
 LC3_HD u32 bswap32(u32 v)
 {
 #if defined(__CUDA_ARCH__)
@@ -35,17 +28,41 @@ LC3_HD u32 bswap32(u32 v)
     return __builtin_bswap32(v);
 #endif
 }
+LC3_HD u32 funnel_r(u32 lo, u32 hi, int sh) // bits [sh, sh + 32) of hi:lo, 0 <= sh < 32
+{
+#if defined(__CUDA_ARCH__)
+    return __funnelshift_r(lo, hi, sh);
+#else
+    return (u32)((((uint64_t)hi << 32) | lo) >> sh);
+#endif
+}
+template <class B> LC3_HD u32 rd_word(BackReader<B> &r) // the next 32 bits of the stream: four bytes going down, the highest in bits 0..7
+{
+    if (r.next <= 0) return 0;
+    r.next -= 4;
+    return bswap32(r.buf.word(r.next >> 2));
+}
+template <class B> LC3_HD void rd_init(BackReader<B> &r, B buf, i32 nbytes)
+{
+    r.buf = buf; r.last = nbytes - 1; r.nread = 0; r.next = nbytes > 0 ? nbytes : 0;
+    // the frame's top (nbytes & 3) bytes form a partial first word, placed at the TOP of cur with the position past the missing
+    // low part; from there on the words are aligned
+    u32 part = 0;
+    int k = 0;
+    while (r.next & 3) { part |= (u32)buf.get(--r.next) << (8 * k); k++; }
+    if (k) { r.cur = part << (32 - 8 * k); r.pos = 32 - 8 * k; }
+    else { r.cur = rd_word(r); r.pos = 0; }
+    r.nxt = rd_word(r);
+}
+template <class B> LC3_HD i32 rd_bp(const BackReader<B> &r) { return r.last - (r.nread >> 3); }
+template <class B> LC3_HD i32 rd_oob(const BackReader<B> &r) { return r.nread > ((r.last + 1) << 3); }
 // the next n bits (0 <= n <= 32), first bit read in bit 0
 template <class B> LC3_HD u32 rd_take(BackReader<B> &r, int n)
 {
-    if (r.avail < n) { // avail < 32 here: one more word fits
-        u32 word = 0;
-        if (r.next > 0) { r.next -= 4; word = bswap32(r.buf.word(r.next >> 2)); }
-        r.w |= (uint64_t)word << r.avail;
-        r.avail += 32;
-    }
-    const u32 v = (u32)(r.w & (((uint64_t)1 << n) - 1));
-    r.w >>= n; r.avail -= n; r.nread += n;
+    const u32 f = funnel_r(r.cur, r.nxt, r.pos);
+    const u32 v = n ? f & (0xffffffffu >> (32 - n)) : 0u;
+    r.pos += n; r.nread += n;
+    if (r.pos >= 32) { r.cur = r.nxt; r.nxt = rd_word(r); r.pos -= 32; }
     return v;
 }
 template <class B> LC3_HD i32 rd_bit(BackReader<B> &r) { return (i32)rd_take(r, 1); }
@@ -131,11 +148,13 @@ template <class B> LC3_HD i32 dec_side_info(BackReader<B> &r, int yLen, int fs_i
 }
 
 // ---- range decoder (ac_dec_init_fx / ac_decode_* / ac_dec_update_fx, fx/ari_codec.c:1559-1803)
-template <class B> struct RangeDec { u32 low, range, help; i32 ber, bp, nbytes; B p; };
+template <class B> struct RangeDec { u32 low, range, help, wbuf /* bytes of the current aligned word still to come */; i32 ber, bp, nbytes; B p; };
 template <class B> LC3_HD u32 rdc_byte(RangeDec<B> &s)
 {
-    u32 v = 0;
-    if (s.bp < s.nbytes) v = (u32)s.p.get(s.bp); else s.ber = 1;
+    if ((s.bp & 3) == 0 && s.bp < s.nbytes) s.wbuf = s.p.word(s.bp >> 2); // the frame's storage is whole words
+    const u32 v = s.bp < s.nbytes ? s.wbuf & 0xffu : 0u;
+    if (s.bp >= s.nbytes) s.ber = 1;
+    s.wbuf >>= 8;
     s.bp++;
     return v;
 }
@@ -200,7 +219,7 @@ LC3_HD void ari_decode(B bytes, BackReader<B> &r, i32 nbbits, int yLen, int fs_i
                        const AriTabs &T, XQ x, LI lsb_ind, u32 *res, AriOut &o)
 {
     RangeDec<B> st;
-    st.p = bytes; st.bp = 0; st.nbytes = nbbits >> 3;
+    st.p = bytes; st.bp = 0; st.nbytes = nbbits >> 3; st.wbuf = 0;
     const i32 rateFlag = nbbits > 160 + fs_idx * 160 ? 2 << 8 : 0;
     const i32 nt_half = yLen >> 1;
     i32 c = 0, lsb_cnt = 0;
@@ -231,10 +250,9 @@ LC3_HD void ari_decode(B bytes, BackReader<B> &r, i32 nbbits, int yLen, int fs_i
     if (st.ber) { o.bfi = 1; return; }
 
     const int lsbMode = si.lsbMode;
-    const i32 esc1 = rom_ari_esc_nb[1], esc2 = rom_ari_esc_nb[2], esc3 = rom_ari_esc_nb[3];
     i32 k = 0, lev = 0, a = 0, bb = 0, t = c + rateFlag, seed = 0, mx = 0, nnz = 0;
     while (k < si.lastnz) {
-        const i32 tt = t + (lev == 0 ? 0 : (lev == 1 ? esc1 : (lev == 2 ? esc2 : esc3)));
+        const i32 tt = t + (imin(lev, 3) << 10); // rom_ari_esc_nb[q] = q << 10
         const u32 *cf = T.cf + 17 * T.lut[tt];
         const i32 sym = rdc_decode17(st, [&](int q) { return cf[q] & 0xffffu; });
         rdc_update(st, cf[sym] & 0xffffu, cf[sym] >> 16);

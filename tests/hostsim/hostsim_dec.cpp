@@ -15,8 +15,9 @@ using namespace lc3k;
 
 struct HostBytes {
     const u8 *p;
+    int n;
     i32 get(int i) const { return p[i]; }
-    u32 word(int k) const { u32 v; memcpy(&v, p + 4 * k, 4); return v; }
+    u32 word(int k) const { u32 v = 0; const int m = n - 4 * k; if (m > 0) memcpy(&v, p + 4 * k, m < 4 ? m : 4); return v; } // never past the frame
 };
 
 struct DSim {
@@ -106,7 +107,7 @@ extern "C" int hostsim_dec_decode(void *p, const uint8_t *in, int nbytes, int bi
             for (int l = 0; l < 32; l++) {
                 const int li = tile * 32 + l;
                 if (li >= b.n_lanes) continue;
-                dec_frame_body(b, f, tile, l, T, HostBytes{in + in_off[li] + (size_t)f * nbytes});
+                dec_frame_body(b, f, tile, l, T, HostBytes{in + in_off[li] + (size_t)f * nbytes, nbytes});
             }
             switch (N) {
             case 480: run_idct_tile<480>(b, f, tile); break;
