@@ -35,7 +35,7 @@ typedef struct {
     cudaEvent_t *in_ev, *k_ev; int n_ev; /* per chunk of a call: its payloads are on the device | its PCM is ready */
     int cap;                       /* slots, multiple of 32 */
     int32_t *st32; int16_t *st16;  /* device state pool, tile-interleaved (lc3_dec_layout.h) */
-    int *free_list, n_free, next_fresh;
+    int *free_list, n_free, cap_free, next_fresh;
     int32_t *reset_list; int n_reset, cap_reset;
     void *d_list; size_t list_cap;
     size_t work_cap[N_DWORK]; void *work[N_DWORK];   /* per-chunk work buffers (the chunks of a call run one after another) */
@@ -143,12 +143,11 @@ static int slot_alloc(DCtx *c)
 }
 static int slot_free(DCtx *c, int slot)
 {
-    static int cap_free[LC3D_MAX_DEV];
-    if (c->n_free >= cap_free[c->device]) {
-        int nc = cap_free[c->device] ? cap_free[c->device] * 2 : 1024;
+    if (c->n_free >= c->cap_free) {
+        int nc = c->cap_free ? c->cap_free * 2 : 1024;
         int *n = (int *)realloc(c->free_list, (size_t)nc * sizeof(int));
         if (!n) return 1;
-        c->free_list = n; cap_free[c->device] = nc;
+        c->free_list = n; c->cap_free = nc;
     }
     c->free_list[c->n_free++] = slot;
     return 0;
@@ -309,14 +308,13 @@ static TabLay tab_layout(int n_lanes, int n_tiles)
 /* One bucket: n_streams decoders that share sample rate, frame duration and device.  rows: the row of each of them in the
  * caller's buffers and arrays (NULL: decoder i is row i); n_rows: rows of the whole call. */
 static LC3_Error dec_bucket(LC3_Dec *const *decs, const int *rows, int n_streams, int n_rows, int n_frames, const void *in, size_t in_stream_stride,
-                            const int *num_bytes, void *pcm, size_t pcm_stream_stride, int bitdepth, uint8_t *bfi_out, unsigned mark)
+                            const int *num_bytes, void *pcm, size_t pcm_stream_stride, int bitdepth, uint8_t *bfi_out)
 {
 #define ROW(i) (rows ? rows[i] : (i))
     const LC3DCfg *g = &decs[0]->cfg;
     const int dev = decs[0]->device, N = g->N, sb = bitdepth == 16 ? 2 : 4;
     int n_lanes = 0;
     for (int i = 0; i < n_streams; i++) n_lanes += decs[i]->cfg.channels;
-    (void)mark;
     pthread_mutex_lock(&g_dlock);
     DCtx *c = dctx_get(dev);
     pthread_mutex_unlock(&g_dlock);
@@ -505,7 +503,7 @@ static LC3_Error dec_batch(LC3_Dec *const *decs, int n_streams, int n_frames, co
         decs[i]->batch_mark = (int)mark;
         if (decs[i]->cfg.fs != decs[0]->cfg.fs || decs[i]->cfg.dms != decs[0]->cfg.dms || decs[i]->device != decs[0]->device) uniform = 0;
     }
-    if (uniform) return dec_bucket(decs, NULL, n_streams, n_streams, n_frames, in, in_stream_stride, num_bytes, pcm, pcm_stream_stride, bitdepth, bfi_out, mark);
+    if (uniform) return dec_bucket(decs, NULL, n_streams, n_streams, n_frames, in, in_stream_stride, num_bytes, pcm, pcm_stream_stride, bitdepth, bfi_out);
     if (is_dev_ptr(in) || is_dev_ptr(pcm)) {
         for (int i = 1; i < n_streams; i++)
             if (decs[i]->device != decs[0]->device) { lc3b_set_error("lc3plus_dec_batch: device buffers with decoders of several devices: make one call per device"); return LC3_ERROR; }
@@ -522,7 +520,7 @@ static LC3_Error dec_batch(LC3_Dec *const *decs, int n_streams, int n_frames, co
             if (!done[i] && decs[i]->cfg.fs == decs[i0]->cfg.fs && decs[i]->cfg.dms == decs[i0]->cfg.dms && decs[i]->device == decs[i0]->device) {
                 list[n] = decs[i]; rows[n] = i; n++; done[i] = 1;
             }
-        const LC3_Error r = dec_bucket(list, rows, n, n_streams, n_frames, in, in_stream_stride, num_bytes, pcm, pcm_stream_stride, bitdepth, bfi_out, mark);
+        const LC3_Error r = dec_bucket(list, rows, n, n_streams, n_frames, in, in_stream_stride, num_bytes, pcm, pcm_stream_stride, bitdepth, bfi_out);
         if (r == LC3_DECODE_ERROR) ret = r;
         else if (r != LC3_OK) { ret = r; break; }
     }
