@@ -312,6 +312,41 @@ def test_dec_reinit_resets_state_and_returns_slots():
     assert not np.array_equal(out1, out3)
 
 
+def test_dec_concurrent_calls_from_threads():
+    """four host threads decode their own streams at the same time (ctypes releases the GIL): the per-device context serialises
+    the calls; initialisations of new decoders run alongside"""
+    import threading
+    import audio_codec_b200 as ac
+    fs, dms, br, S, nf, N = 16000, 100, 32000, 24, 30, 160
+    pcm = make_streams(4 * S, nf * N, fs, N, 16, silence_frames=2)
+    frames = gpu_encode(fs, dms, br, pcm)
+    nb = frames.shape[2]
+    outs, errs = [None] * 4, []
+
+    def work(t):
+        try:
+            for rep in range(3):
+                decs = [ac.Decoder(fs, 1, dms) for _ in range(S)]
+                o = np.zeros((S, nf * N), dtype=np.int16)
+                fr = np.ascontiguousarray(frames[t * S:(t + 1) * S])
+                assert ac.dec_batch(decs, nf, fr, nf * nb, np.full(S, nb, np.int32), o, nf * N * 2, 16) == 0
+                outs[t] = o
+                for d in decs:
+                    d.close()
+        except Exception as e:   # noqa: BLE001
+            errs.append(e)
+    th = [threading.Thread(target=work, args=(t,)) for t in range(4)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    assert not errs, errs
+    for t in range(4):
+        for s in (0, S // 2, S - 1):
+            ref, bad = CheckDec(fs, 1, dms).decode(frames[t * S + s], 16)
+            assert bad == 0 and np.array_equal(ref[0], outs[t][s]), (t, s)
+
+
 def test_dec_full_size_round_trip_c1():
     """BASELINE.json config c1 geometry (4096 streams x 48 kHz / 10 ms / 128 kbps), 100 frames: encode -> decode on the device,
     a sample of streams against the reference decoder, every stream against the delayed input (a codec at 128 kbps keeps the
