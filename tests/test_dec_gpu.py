@@ -347,6 +347,23 @@ def test_dec_concurrent_calls_from_threads():
             assert bad == 0 and np.array_equal(ref[0], outs[t][s]), (t, s)
 
 
+@pytest.mark.parametrize("item,fs,br", [("thetest8", 8000, 32000), ("thetest16", 16000, 32000), ("thetest24", 24000, 48000),
+                                        ("thetest32", 32000, 48000), ("thetest44", 44100, 64000), ("thetest48", 48000, 64000)])
+def test_dec_etsi_items_equal_reference(item, fs, br):
+    """the ETSI package's own test items (tests/golden/etsi_full.npz: speech and music, about 10 s each) at the package's bitrates
+    (ETSI/testvec/testvecCheck.pl), no frame erasures: real pitch contours drive every LTPF transition"""
+    z = np.load(os.path.join(HERE, "golden", "etsi_full.npz"))
+    N = (48000 if fs == 44100 else fs) // 100
+    x = z[item]
+    nf = len(x) // N
+    pcm = np.ascontiguousarray(x[:nf * N][None, :])
+    frames = gpu_encode(fs, 100, br, pcm)
+    for bits in (16, 24):
+        out, rc = gpu_decode(fs, 100, frames, bits, cuts=(nf // 2,))
+        ref, bad = CheckDec(fs, 1, 100).decode(frames[0], bits)
+        assert rc == 0 and bad == 0 and np.array_equal(ref[0], out[0, 0]), bits
+
+
 def test_dec_full_size_round_trip_c1():
     """BASELINE.json config c1 geometry (4096 streams x 48 kHz / 10 ms / 128 kbps), 100 frames: encode -> decode on the device,
     a sample of streams against the reference decoder, every stream against the delayed input (a codec at 128 kbps keeps the
