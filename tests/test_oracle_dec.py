@@ -57,6 +57,22 @@ def test_oracle_decoder_equals_reference_with_switching_and_stereo(fs, dms, rate
             assert bad_a == 0 and bad_b == 0 and np.array_equal(a, b), (bits, k, br)
 
 
+@pytest.mark.parametrize("item,fs,br", [("thetest8", 8000, 32000), ("thetest16", 16000, 32000), ("thetest24", 24000, 48000),
+                                        ("thetest32", 32000, 48000), ("thetest44", 44100, 64000), ("thetest48", 48000, 64000)])
+def test_oracle_decoder_equals_reference_on_etsi_items(item, fs, br):
+    """the ETSI package's own test items (speech and music) at the package's bitrates, no frame erasures"""
+    if not lc3ref.have_ref():
+        pytest.skip("reference library absent")
+    z = np.load(os.path.join(HERE, "golden", "etsi_full.npz"))
+    N = (48000 if fs == 44100 else fs) // 100
+    nf = min(len(z[item]) // N, 500)
+    frames = lc3ref.RefEnc(fs, 1, 100, br).encode(np.ascontiguousarray(z[item][:nf * N][None, :]))
+    for bits in (16, 24):
+        a, bad_a = lc3ref.RefDec(fs, 1, 100).decode(frames, bits)
+        b, bad_b = lc3ref.OracleDec(fs, 1, 100).decode(frames, bits)
+        assert bad_a == 0 and bad_b == 0 and np.array_equal(a, b), bits
+
+
 def test_oracle_decoder_flags_bad_frames_like_the_reference():
     if not lc3ref.have_ref():
         pytest.skip("reference library absent")
