@@ -147,14 +147,17 @@ template <int BITS> LC3_HD void synth_warp_body(const LC3D_Batch &b, int li, Syn
         if (sd > 0) { y_s = s_sub(y_s, sd); y_e = s_add(y_e, sd); }
         else { mem_s = s_add(mem_s, sd); mem_e = s_sub(mem_e, sd); }
         mem_s = imax(mem_s, -31); y_s = imax(y_s, -31);
+        // the two shift counts are the same for the whole frame: split once (l_shl_plan == l_shl for every value and count,
+        // tests/hostsim/primcheck.cpp); the window ROM holds no -32768 (tests/test_rom_bounds.py), so Mpy_32_16 cannot saturate
+        const ShlPlan pm = shl_plan(mem_s), py = shl_plan(y_s);
         LC3_LANES(l)
             for (int i = l; i < o; i += 32)
-                sh.xf[i] = (i16)l_round(l_sub(l_shl(l_dep_h(sh.ola[i]), mem_s), mpy32x16(l_shl(y[m + i + z], y_s), win[4 * m - 1 - i - z])));
+                sh.xf[i] = (i16)l_round(l_sub(l_shl_plan(l_dep_h(sh.ola[i]), pm), mpy32x16k(l_shl_plan(y[m + i + z], py), win[4 * m - 1 - i - z])));
             for (int i = l; i < m; i += 32) {
-                sh.xf[i + o] = (i16)l_round(l_add(l_shl(l_dep_h(sh.ola[i + o]), mem_s), mpy32x16(l_shl(y[2 * m - 1 - i], y_s), win[3 * m - 1 - i])));
-                const i32 v = l_shl(y[i], y_s);
-                sh.xf[3 * m - z + i] = (i16)l_round(l_neg(mpy32x16(v, win[m - 1 - i])));
-                sh.xf[3 * m - z - 1 - i] = (i16)l_round(l_neg(mpy32x16(v, win[m + i])));
+                sh.xf[i + o] = (i16)l_round(l_add(l_shl_plan(l_dep_h(sh.ola[i + o]), pm), mpy32x16k(l_shl_plan(y[2 * m - 1 - i], py), win[3 * m - 1 - i])));
+                const i32 v = l_shl_plan(y[i], py);
+                sh.xf[3 * m - z + i] = (i16)l_round(l_neg(mpy32x16k(v, win[m - 1 - i])));
+                sh.xf[3 * m - z - 1 - i] = (i16)l_round(l_neg(mpy32x16k(v, win[m + i])));
             }
         LC3_LANES_END
         LC3_LANES(l)

@@ -44,8 +44,15 @@ def test_product_and_oracle_rom_identical():
 
 def test_constants_used_with_unchecked_multiply_are_not_minus_one():
     """mpy32x16k / mpy32x32k skip the (-1 x -1) saturation test: their constant operands must differ from the minimum."""
-    for name in ("rom_hp50_num", "rom_hp50_den", "rom_ltpf_inter_filt", "rom_tns_quant_pts"):
+    for name in ("rom_hp50_num", "rom_hp50_den", "rom_ltpf_inter_filt", "rom_tns_quant_pts", "rom_win"):
         assert -32768 not in _tab(name), name
+    # decoder-only tables (tools/gen_rom_dec.py): the LTPF synthesis taps multiply without L_mult's -32768 x -32768 case
+    import re
+    txt = open(os.path.join(ROOT, "audio_codec_b200", "csrc", "rom_dec_tables.inc")).read()
+    for name in ("rom_ltpf_dec_inter", "rom_ltpf_dec_tilt"):
+        body = re.search(r"ROM_TAB\(\w+, %s, \d+\) = \{(.*?)\};" % name, txt, re.S).group(1)
+        assert -32768 not in [int(v) for v in re.findall(r"-?\d+", body)], name
+    assert txt == open(os.path.join(ROOT, "oracle", "rom_dec_tables.inc")).read()
 
 
 def test_tns_subdivisions_tile_the_filter_bins():
