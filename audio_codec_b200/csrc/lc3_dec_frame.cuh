@@ -427,10 +427,11 @@ LC3_HD void sns_decode(const i32 *idx, i16 *scf_q)
 // IIRLattice (fx/tns_decoder_fx.c:117-134)
 LC3_HD i32 tns_iir(int order, const i16 *rc, i32 *state, i32 x)
 {
-    x = l_sub(x, mpy32x16(state[order - 1], rc[order - 1]));
+    // rc: rom_tns_quant_pts entries, none of them -32768 (tests/test_rom_bounds.py): Mpy_32_16 cannot saturate
+    x = l_sub(x, mpy32x16k(state[order - 1], rc[order - 1]));
     for (int i = order - 2; i >= 0; i--) {
-        x = l_sub(x, mpy32x16(state[i], rc[i]));
-        state[i + 1] = l_add(state[i], mpy32x16(x, rc[i]));
+        x = l_sub(x, mpy32x16k(state[i], rc[i]));
+        state[i + 1] = l_add(state[i], mpy32x16k(x, rc[i]));
     }
     state[0] = x;
     return x;
@@ -554,6 +555,8 @@ template <class B> LC3_HD void dec_frame_body(const LC3D_Batch &b, int f, int ti
     // bins of filter j: [lo_j, hi_j)
     const int lo0 = tns_start0, hi0 = tns_nf == 2 ? tns_start1 : bw_stop, lo1 = tns_start1, hi1 = bw_stop;
     int band = 0, stop = bo[1];
+    i32 gsh = imin(-(i32)g_exp[0], 31); // the band exponents are <= 0 after the common one went into q_exp: plain right shifts
+    const ShlPlan pts = shl_plan(ts);
     Range ry; range_init(ry);
     for (int i0 = 0; i0 < yLen; i0 += 8) {
         i32 dv[8];
@@ -565,13 +568,13 @@ template <class B> LC3_HD void dec_frame_body(const LC3D_Batch &b, int f, int ti
             if (i >= yLen) break;
             i32 v = dv[j];
             if (tns_on) {
-                v = l_shl(v, ts);
+                v = l_shl_plan(v, pts);
                 if (si.tns_order[0] > 0 && i >= lo0 && i < hi0) v = tns_iir(si.tns_order[0], rc[0], state, v);
                 else if (tns_nf == 2 && si.tns_order[1] > 0 && i >= lo1 && i < hi1) v = tns_iir(si.tns_order[1], rc[1], state, v);
             }
             if (i < shaped) {
-                while (i >= stop) { band++; stop = bo[band + 1]; }
-                v = l_shl(mpy32x16k(v, g[band]), g_exp[band]); // g > 0 (mantissa of 2^x)
+                while (i >= stop) { band++; stop = bo[band + 1]; gsh = imin(-(i32)g_exp[band], 31); }
+                v = mpy32x16k(v, g[band]) >> gsh; // g > 0 (mantissa of 2^x)
             }
             range_add(ry, v);
             d[i] = v;

@@ -260,17 +260,18 @@ template <int BITS> LC3_HD void synth_warp_body(const LC3D_Batch &b, int li, Syn
 
         // ---- output scaling (fx/dec_lc3.c:289-311)
         if (BITS == 16) {
-            const i32 scale = s_sub(15, x_e);
+            const ShlPlan po = shl_plan(-s_sub(15, x_e)); // L_shr by scale = L_shl by -scale, the same for the whole frame
             i16 *dst = (i16 *)b.pcm + b.pcm_off[li] + (size_t)(b.frame0 + f) * N;
             LC3_LANES(l)
-                for (int k = l; k < N; k += 32) dst[k] = (i16)l_round(l_shr(l_dep_h(sh.xf[k]), scale));
+                for (int k = l; k < N; k += 32) dst[k] = (i16)l_round(l_shl_plan(l_dep_h(sh.xf[k]), po));
             LC3_LANES_END
         } else {
             const i32 scale = s_sub(s_sub(31 + 16, 24), x_e);
             const i32 offset = l_shr(32768, s_sub(16, scale));
+            const ShlPlan po = shl_plan(-scale);
             i32 *dst = (i32 *)b.pcm + b.pcm_off[li] + (size_t)(b.frame0 + f) * N;
             LC3_LANES(l)
-                for (int k = l; k < N; k += 32) dst[k] = l_shr(l_add(l_dep_h(sh.xf[k]), offset), scale);
+                for (int k = l; k < N; k += 32) dst[k] = l_shl_plan(l_add(l_dep_h(sh.xf[k]), offset), po);
             LC3_LANES_END
         }
     }
