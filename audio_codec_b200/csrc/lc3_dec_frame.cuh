@@ -555,7 +555,7 @@ template <class B> LC3_HD void dec_frame_body(const LC3D_Batch &b, int f, int ti
     // bins of filter j: [lo_j, hi_j)
     const int lo0 = tns_start0, hi0 = tns_nf == 2 ? tns_start1 : bw_stop, lo1 = tns_start1, hi1 = bw_stop;
     int band = 0, stop = bo[1];
-    i32 gsh = imin(-(i32)g_exp[0], 31); // the band exponents are <= 0 after the common one went into q_exp: plain right shifts
+    i32 gsh = imin(-(i32)g_exp[0], 31), gcur = g[0]; // the band exponents are <= 0 after the common one went into q_exp: plain right shifts
     const ShlPlan pts = shl_plan(ts);
     Range ry; range_init(ry);
     for (int i0 = 0; i0 < yLen; i0 += 8) {
@@ -573,8 +573,8 @@ template <class B> LC3_HD void dec_frame_body(const LC3D_Batch &b, int f, int ti
                 else if (tns_nf == 2 && si.tns_order[1] > 0 && i >= lo1 && i < hi1) v = tns_iir(si.tns_order[1], rc[1], state, v);
             }
             if (i < shaped) {
-                while (i >= stop) { band++; stop = bo[band + 1]; gsh = imin(-(i32)g_exp[band], 31); }
-                v = mpy32x16k(v, g[band]) >> gsh; // g > 0 (mantissa of 2^x)
+                while (i >= stop) { band++; stop = bo[band + 1]; gsh = imin(-(i32)g_exp[band], 31); gcur = g[band]; }
+                v = mpy32x16k(v, gcur) >> gsh; // g > 0 (mantissa of 2^x)
             }
             range_add(ry, v);
             d[i] = v;
