@@ -504,10 +504,17 @@ template <class B> LC3_HD void dec_frame_body(const LC3D_Batch &b, int f, int ti
         for (int k = nf_start - nf_w; k < nf_start + nf_w; k++) { if (xq[k] != 0) nzeros = -2 * nf_w - 1; else nzeros++; }
     // eight bins at a time, their loads (and the noise-filling look-ahead) issued before the first is used: the walk waits
     // on the latency of its loads, not on arithmetic
+    i32 qn[8]; // the group after the current one, loaded while the current one is processed
+#pragma unroll
+    for (int j = 0; j < 8; j++) qn[j] = j < yLen ? (i32)xq[j] : 0;
     for (int i0 = 0; i0 < yLen; i0 += 8) {
         i32 qv[8 + 3];
 #pragma unroll
-        for (int j = 0; j < 8 + 3; j++) qv[j] = i0 + j < yLen ? (i32)xq[i0 + j] : 0;
+        for (int j = 0; j < 8; j++) qv[j] = qn[j];
+#pragma unroll
+        for (int j = 0; j < 8; j++) qn[j] = i0 + 8 + j < yLen ? (i32)xq[i0 + 8 + j] : 0;
+#pragma unroll
+        for (int j = 0; j < 3; j++) qv[8 + j] = qn[j];
 #pragma unroll
         for (int j = 0; j < 8; j++) {
             const int i = i0 + j;
@@ -558,10 +565,15 @@ template <class B> LC3_HD void dec_frame_body(const LC3D_Batch &b, int f, int ti
     i32 gsh = imin(-(i32)g_exp[0], 31), gcur = g[0]; // the band exponents are <= 0 after the common one went into q_exp: plain right shifts
     const ShlPlan pts = shl_plan(ts);
     Range ry; range_init(ry);
+    i32 dn[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) dn[j] = j < yLen ? d[j] : 0;
     for (int i0 = 0; i0 < yLen; i0 += 8) {
         i32 dv[8];
 #pragma unroll
-        for (int j = 0; j < 8; j++) dv[j] = i0 + j < yLen ? d[i0 + j] : 0;
+        for (int j = 0; j < 8; j++) dv[j] = dn[j];
+#pragma unroll
+        for (int j = 0; j < 8; j++) dn[j] = i0 + 8 + j < yLen ? d[i0 + 8 + j] : 0; // not yet written by this walk: it stores at i < i0 + 8
 #pragma unroll
         for (int j = 0; j < 8; j++) {
             const int i = i0 + j;
