@@ -163,20 +163,22 @@ template <class B> LC3_HD void rdc_init(RangeDec<B> &s)
     s.low = 0; s.range = 0x00ffffff; s.ber = 0;
     for (int i = 0; i < 3; i++) s.low = (s.low << 8) + rdc_byte(s);
 }
-// binary search over a cumulative-frequency row of 17 entries (spectrum models, TNS coefficients); CF(r) = row entry r
+// Symbol search in a cumulative-frequency row of 17 entries (spectrum models, TNS coefficients); CF(r) = row entry r.
+// The reference bisects in four dependent steps (ac_decode_fx, fx/ari_codec.c:1589-1648): the result is the LARGEST r <= 15
+// with low >= help * CF(r), because every row rises monotonically from 0 (tests/test_rom_bounds.py).  The same r is found here
+// in two rounds of three independent comparisons (quarter, then position inside it): half the chain of dependent table
+// loads, which is what a lane waits for in this loop.  r = 15 then goes on to the escape entry and the range check as there.
 template <class B, class CF> LC3_HD i32 rdc_decode17(RangeDec<B> &s, CF cf)
 {
     s.help = s.range >> 10;
-    i32 val = 0;
-    if (s.low >= s.help * cf(8)) val = 8;
-    if (s.low >= s.help * cf(val + 4)) val += 4;
-    if (s.low >= s.help * cf(val + 2)) val += 2;
-    if (s.low >= s.help * cf(val + 1)) {
-        val += 1;
-        if (val == 15) {
-            if (s.low >= s.help * cf(16)) val = 16;
-            if (s.low >= (s.help << 10)) s.ber = 1;
-        }
+    const u32 low = s.low, h = s.help;
+    const u32 c4 = cf(4), c8 = cf(8), c12 = cf(12);
+    const i32 base = 4 * ((low >= h * c4) + (low >= h * c8) + (low >= h * c12));
+    const u32 d1 = cf(base + 1), d2 = cf(base + 2), d3 = cf(base + 3);
+    i32 val = base + (low >= h * d1) + (low >= h * d2) + (low >= h * d3);
+    if (val == 15) {
+        if (low >= h * cf(16)) val = 16;
+        if (low >= (h << 10)) s.ber = 1;
     }
     return val;
 }

@@ -72,3 +72,14 @@ def test_tns_subdivisions_tile_the_filter_bins():
                 hi = [hi_t[base + nsub * j + sd] for sd in range(nsub)]
                 assert lo[0] <= start[j] and hi[-1] >= stop, (dms_idx, bw, j, lo, hi, start[j], stop)
                 assert all(hi[sd] >= lo[sd + 1] for sd in range(nsub - 1)), (dms_idx, bw, j, lo, hi)
+
+
+def test_cumulative_frequency_rows_rise_monotonically_from_zero():
+    """the decoder finds a symbol as the largest r with low >= help * cumfreq[r] in two rounds of comparisons instead of the
+    reference's four-step bisection (lc3_dec_frame.cuh rdc_decode17): the two agree because every row is non-decreasing from 0"""
+    for name, rows in (("rom_ari_cumfreq", 64), ("rom_tns_coef_cumfreq", 8)):
+        v = _tab(name)
+        assert len(v) == rows * 17
+        for r in range(rows):
+            row = v[r * 17:(r + 1) * 17]
+            assert row[0] == 0 and all(a <= b for a, b in zip(row, row[1:])), (name, r)
