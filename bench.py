@@ -331,6 +331,7 @@ def main():
     ap.add_argument("--single-process", action="store_true", help="drive --gpus N devices from this one process (no torchrun)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-decoder", action="store_true", help="skip the short decoder leg (key \"decoder\" of the c1 line)")
     ap.add_argument("--no-alone", action="store_true", help="skip the kernels-alone pass (roofline.kernel_ms_alone)")
     args = ap.parse_args()
     if args.warmup < 3:
@@ -529,6 +530,12 @@ def main():
             r3, _, s3 = cpu_reference_rate(u0.w, 6.0, o3=True)
             line["cpu_baseline"]["value_O3"] = r3
             line["cpu_baseline"]["sample_O3"] = s3
+    if world == 1 and len(units) == 1 and args.config == "c1" and not args.no_decoder:
+        try:   # a short leg of the decoder (row f4) beside the headline, which stays the encoder's; never fatal for the line
+            import bench_dec
+            line["decoder"] = bench_dec.quick_leg()
+        except Exception as e:   # noqa: BLE001
+            line["decoder"] = {"error": repr(e)[:200]}
     print(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()

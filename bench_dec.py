@@ -45,6 +45,49 @@ def refdec(payloads, fs, dms, nb, nf, threads, out=None, repeat=1):
     return float(r[2]), float(r[1]), int(r[4]), pcm
 
 
+def quick_leg(S=4096, nf=100, fs=48000, dms=100, br=128000, steps=5, warmup=2):
+    """A short decoder leg for bench.py's JSON line (key "decoder"): S streams x nf frames per step, device-resident, after the
+    encoder's own run; four streams of a fresh one-call decode are checked against the decoder oracle (oracle/lc3o_dec.c)."""
+    import torch
+    import audio_codec_b200 as ac
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import lc3ref
+    from audio_codec_b200.synth import make_streams_fast
+    N = fs // 100 * dms // 100
+    pcm = make_streams_fast(S, nf * N, fs, N, 16)
+    encs = ac.EncoderArray([ac.Encoder(fs, 1, dms, br) for _ in range(S)])
+    nb = encs.encoders[0].num_bytes
+    d_pcm = torch.from_numpy(pcm).cuda()
+    d_bytes = torch.zeros((S, nf * nb), dtype=torch.uint8, device="cuda")
+    ac.enc_batch(encs, nf, d_pcm.data_ptr(), nf * N * 2, 16, d_bytes.data_ptr(), nf * nb)
+    for e in encs.encoders:
+        e.close()
+    nbs = np.full(S, nb, np.int32)
+    d_out = torch.zeros((S, nf * N), dtype=torch.int16, device="cuda")
+    decs = ac.DecoderArray([ac.Decoder(fs, 1, dms) for _ in range(S)])
+    assert ac.dec_batch(decs, nf, d_bytes.data_ptr(), nf * nb, nbs, d_out.data_ptr(), nf * N * 2, 16) == 0
+    idx = [0, 7, S // 2, S - 1]
+    got = d_out[idx].cpu().numpy()
+    payloads = d_bytes[idx].cpu().numpy().reshape(len(idx), nf, nb)
+    for k in range(len(idx)):
+        ref, bad = lc3ref.OracleDec(fs, 1, dms).decode(payloads[k], 16)
+        assert bad == 0 and np.array_equal(ref[0], got[k]), "decoder leg differs from the decoder oracle"
+    for _ in range(warmup):
+        ac.dec_batch(decs, nf, d_bytes.data_ptr(), nf * nb, nbs, d_out.data_ptr(), nf * N * 2, 16)
+    ac.dec_profile_enable(True)
+    n0 = ac.dec_kernel_launches()
+    for _ in range(steps):
+        ac.dec_batch(decs, nf, d_bytes.data_ptr(), nf * nb, nbs, d_out.data_ptr(), nf * N * 2, 16)
+    span = ac.dec_profile_read()["span"] / 1e3
+    launches = ac.dec_kernel_launches() - n0
+    ac.dec_profile_enable(False)
+    for d in decs.decoders:
+        d.close()
+    return {"metric": "decoded channel-frames per second, device-resident (SURVEY.md 8 row f4; full bench: bench_dec.py)", "value": S * nf * steps / span,
+            "unit": "frames/s", "steps": steps, "warmup": warmup, "ms_per_step": span * 1e3 / steps, "gpu_launches": launches,
+            "verified_frames": len(idx) * nf, "workload": f"{S} streams x {nf} frames/step, {fs} Hz, {dms / 10} ms, {nb} bytes/frame"}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--steps", type=int, default=10)
